@@ -1,0 +1,104 @@
+"""Pins oracle/go_oracle.c to the reference: it must reproduce every fixture that
+oracle/make_golden.py recorded from the reference's own Python (CPU only)."""
+import numpy as np
+import pytest
+
+from oracle import go_oracle
+from tests import golden_util as gu
+
+ALL = ["board", "ones", "turns_since", "liberties", "capture_size", "self_atari_size",
+       "liberties_after", "ladder_capture", "ladder_escape", "sensibleness", "zeros", "legal"]
+
+
+@pytest.mark.parametrize("name", gu.FEATURE_FILES)
+def test_features_match_reference(name):
+    g = gu.load_features(name)
+    assert g["feature_list"] == ALL
+    got = go_oracle.features(g["board"], g["age"], g["ko"], g["player"], ALL)
+    assert got.shape == g["planes"].shape
+    bad = np.argwhere(got != g["planes"])
+    assert bad.size == 0, "first mismatches (pos, plane, x, y): %s" % bad[:5].tolist()
+
+
+@pytest.mark.parametrize("name", gu.FEATURE_FILES)
+def test_legal_move_order_matches_reference(name):
+    g = gu.load_features(name)
+    moves, n_noneye = go_oracle.legal_moves(g["board"], g["ko"], g["player"])
+    for i, m in enumerate(moves):
+        assert len(m) == g["n_legal"][i]
+        assert np.array_equal(m, g["legal_moves"][i, :len(m)])
+    assert np.array_equal(n_noneye, g["n_noneye"])
+
+
+def test_feature_subsets_and_orders():
+    g = gu.load_features("features_playouts_9.npz")
+    for fl in (["board", "sensibleness", "capture_size"], ["legal"], ["zeros", "ones", "board", "board"],
+               ["LADDER_ESCAPE", "Liberties"]):
+        got = go_oracle.features(g["board"], g["age"], g["ko"], g["player"], fl)
+        assert np.array_equal(got, gu.select_planes(g["planes"], fl))
+
+
+def test_reference_unit_test_queries():
+    """Every is_legal / is_eye / ladder query the reference's own tests make (incl. the 8
+    ladder scenarios of tests/test_ladders.py and the ko / eye cases of test_gamestate.py)."""
+    k = gu.load_kat()
+    assert int(k["reference_tests_run"]) == 31
+    L = go_oracle.lib()
+    n = len(k["kind"])
+    counts = [0, 0, 0, 0]
+    for i in range(n):
+        S = int(k["size"][i])
+        board = np.ascontiguousarray(k["board"][i, :S * S]).reshape(S, S)
+        kind, a0, a1, want = int(k["kind"][i]), int(k["arg0"][i]), int(k["arg1"][i]), int(k["result"][i])
+        ko, player = int(k["ko"][i]), int(k["player"][i])
+        if kind == 0:
+            if a0 < 0:
+                continue
+            # is_legal on one point: get_legal_moves applies the same predicate to every point
+            lm, _ = go_oracle.legal_moves(board[None], [ko], [player])
+            got = int(a0 in set(lm[0].tolist()))
+        elif kind == 1:
+            # is_eye(pos, owner): sensibleness for owner == player separates eye / non-eye among legal
+            # moves; query it directly through the legal-move split with `owner` to move
+            lm, nne = go_oracle.legal_moves(board[None], [-1], [a1])
+            eyes = set(lm[0][nne[0]:].tolist())
+            legal = set(lm[0].tolist())
+            if a0 not in legal:
+                # an illegal point can still be asked about; only eyeish empties can be eyes and an
+                # eyeish empty is illegal only as suicide-free ko: skip those (none in the recording)
+                assert want == 0 or board.reshape(-1)[a0] == 0
+                if want == 0:
+                    counts[kind] += 1
+                    continue
+            got = int(a0 in eyes)
+        else:
+            got = int(go_oracle.ladder_query(board, ko, player, a0, a1, escape=(kind == 3)))
+        assert got == want, (i, kind, S, a0, a1)
+        counts[kind] += 1
+    assert counts[2] >= 50 and counts[3] >= 40 and counts[0] > 500 and counts[1] > 100
+
+
+def test_do_move_replay_matches_reference():
+    """Board, stone ages, ko and side to move after every move of the 7 SGF games."""
+    r = gu.load_replay()
+    for gi in range(len(r["names"])):
+        moves, colors = r["moves_%d" % gi], r["colors_%d" % gi]
+        ns = int(r["nsetup_%d" % gi])
+        played, board, age, ko, player = go_oracle.replay(19, moves, colors, every=True)
+        assert played == len(moves)
+        assert np.array_equal(board[ns:], r["board_%d" % gi])
+        assert np.array_equal(age[ns:], r["age_%d" % gi])
+        assert np.array_equal(ko[ns:], r["ko_%d" % gi])
+        assert np.array_equal(player[ns:], r["player_%d" % gi])
+
+
+def test_playout_generator_positions_are_consistent():
+    """The oracle's own playout generator (synthetic inputs for the GPU tests) makes
+    positions whose recorded move is legal and sensible."""
+    b, a, ko, pl, mv = go_oracle.random_playouts(300, size=19, seed=7, with_moves=True)
+    f = go_oracle.features(b, a, ko, pl, ["sensibleness", "board"])
+    for i in range(300):
+        if mv[i] >= 0:
+            assert f[i, 0].reshape(-1)[mv[i]] == 1
+    assert (ko >= 0).sum() >= 0
+    assert set(np.unique(pl)) <= {-1, 1}
