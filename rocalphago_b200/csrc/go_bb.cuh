@@ -1,0 +1,500 @@
+// go_bb.cuh -- warp-per-position bitboard Go engine (rules, feature planes, ladder reader).
+//
+// Replaces, for the device, the group/liberty bookkeeping of the reference's
+// AlphaGo/go.py (GameState, go.py:9-581) and the feature functions of
+// AlphaGo/preprocessing/preprocessing.py:14-205.  It is NOT a translation: the
+// reference keeps Python sets per point and deep-copies the state for every
+// look-ahead; here a position is two 19-row bitboards spread over the lanes of
+// one warp (lane r owns row x = r, bit y of its word is point (x, y)), groups
+// and liberties are fixed points of shift/shuffle dilations, and look-ahead
+// copies are register moves.
+//
+// All control flow in this file is WARP-UNIFORM: every branch depends only on
+// values that are identical in all 32 lanes (ballots, reductions, broadcast
+// scalars).  That is what lets the same source also be compiled as plain C++
+// with a 32-row array standing in for the warp (RAG_HOSTSIM; used only by
+// tests/hostsim to check this file's logic against the oracle on machines
+// without a GPU -- it is never linked into the product library).
+//
+// Point index inside this file: q = x*32 + y  ("q-index"; x = q >> 5, y = q & 31).
+// The reference's flat index p = x*S + y (util.py:11-13) is used only at the I/O edge.
+#pragma once
+#include <stdint.h>
+
+#if defined(__CUDACC__) && !defined(RAG_HOSTSIM)
+#define RAG_DEVICE_BUILD 1
+#define RAG_FN __device__ __forceinline__
+#define RAG_FN_NOINLINE __device__ __noinline__
+#else
+#define RAG_DEVICE_BUILD 0
+#define RAG_FN static inline
+#define RAG_FN_NOINLINE static
+#endif
+
+namespace rag {
+
+constexpr int kMaxBoard = 19;
+constexpr int kLadderDepth = 80;          // remaining_attempts default, go.py:329,396
+constexpr unsigned kFullMask = 0xffffffffu;
+
+// Canonical plane numbering (DEFAULT_FEATURES order, preprocessing.py:260-263, then `legal`).
+enum Plane {
+    kPlaneBoard = 0, kPlaneOnes = 3, kPlaneTurnsSince = 4, kPlaneLiberties = 12,
+    kPlaneCaptureSize = 20, kPlaneSelfAtari = 28, kPlaneLibertiesAfter = 36,
+    kPlaneLadderCapture = 44, kPlaneLadderEscape = 45, kPlaneSensibleness = 46,
+    kPlaneZeros = 47, kPlaneLegal = 48, kNumPlanes = 49
+};
+
+// ------------------------------------------------------------------ BB: a board-sized bit set
+#if RAG_DEVICE_BUILD
+
+struct BB { uint32_t w; };                       // this lane's row
+
+struct Geo {                                     // per-warp constants
+    int S;                                       // board size (<= 19)
+    uint32_t lane;                               // threadIdx.x & 31
+    uint32_t rowmask;                            // (1<<S)-1 on lanes < S, else 0
+};
+
+RAG_FN Geo make_geo(int S) {
+    Geo g; g.S = S; g.lane = threadIdx.x & 31u;
+    g.rowmask = (g.lane < (uint32_t)S) ? ((1u << S) - 1u) : 0u;
+    return g;
+}
+
+RAG_FN BB bb_zero() { return BB{0u}; }
+RAG_FN BB bb_board(const Geo& g) { return BB{g.rowmask}; }
+RAG_FN BB operator&(BB a, BB b) { return BB{a.w & b.w}; }
+RAG_FN BB operator|(BB a, BB b) { return BB{a.w | b.w}; }
+RAG_FN BB operator^(BB a, BB b) { return BB{a.w ^ b.w}; }
+RAG_FN BB andnot(BB a, BB b) { return BB{a.w & ~b.w}; }             // a & ~b
+RAG_FN bool bb_any(BB a) { return __any_sync(kFullMask, a.w != 0u) != 0; }
+RAG_FN bool bb_equal(BB a, BB b) { return __all_sync(kFullMask, a.w == b.w) != 0; }
+RAG_FN int bb_count(BB a) { return (int)__reduce_add_sync(kFullMask, (unsigned)__popc(a.w)); }
+RAG_FN BB bb_single(int q, const Geo& g) { return BB{(g.lane == (uint32_t)(q >> 5)) ? (1u << (q & 31)) : 0u}; }
+RAG_FN bool bb_test(BB a, int q) { return ((__shfl_sync(kFullMask, a.w, q >> 5) >> (q & 31)) & 1u) != 0u; }
+// lowest point in x-major order, or -1
+RAG_FN int bb_first(BB a) {
+    unsigned rows = __ballot_sync(kFullMask, a.w != 0u);
+    if (rows == 0u) return -1;
+    int x = __ffs(rows) - 1;
+    uint32_t w = __shfl_sync(kFullMask, a.w, x);
+    return (x << 5) | (__ffs(w) - 1);
+}
+// 4-neighbourhood of a set (without the set itself); go.py:103-116
+RAG_FN BB bb_nbrs(BB a, const Geo& g) {
+    uint32_t up = __shfl_up_sync(kFullMask, a.w, 1);        // row x-1
+    uint32_t dn = __shfl_down_sync(kFullMask, a.w, 1);      // row x+1
+    if (g.lane == 0u) up = 0u;
+    if (g.lane == 31u) dn = 0u;
+    return BB{(up | dn | (a.w << 1) | (a.w >> 1)) & g.rowmask};
+}
+// value at (x,y) taken from (x-1,y) / (x+1,y); rows outside the board read as `fill`
+RAG_FN BB bb_from_north(BB a, const Geo& g, bool fill) {
+    uint32_t v = __shfl_up_sync(kFullMask, a.w, 1);
+    if (g.lane == 0u) v = fill ? kFullMask : 0u;
+    return BB{v & g.rowmask};
+}
+RAG_FN BB bb_from_south(BB a, const Geo& g, bool fill) {
+    uint32_t v = __shfl_down_sync(kFullMask, a.w, 1);
+    if (g.lane == (uint32_t)(g.S - 1)) v = fill ? kFullMask : 0u;
+    return BB{v & g.rowmask};
+}
+RAG_FN BB bb_from_west(BB a, const Geo& g, bool fill) { return BB{((a.w << 1) | (fill ? 1u : 0u)) & g.rowmask}; }
+RAG_FN BB bb_from_east(BB a, const Geo& g, bool fill) {
+    return BB{((a.w >> 1) | (fill ? (1u << (g.S - 1)) : 0u)) & g.rowmask};
+}
+// planes: 32 words per plane, word r = row r
+RAG_FN void plane_or(uint32_t* planes, int k, BB a, const Geo& g) { planes[k * 32 + g.lane] |= a.w; }
+RAG_FN BB bb_load(const uint32_t* rows32, const Geo& g) { return BB{rows32[g.lane] & g.rowmask}; }
+RAG_FN void bb_store(uint32_t* rows32, BB a, const Geo& g) { rows32[g.lane] = a.w; }
+
+#else  // ------------------------------------------------------------- host stand-in for one warp
+
+struct BB { uint32_t w[32]; };
+struct Geo { int S; uint32_t rowmask; };
+
+RAG_FN Geo make_geo(int S) { Geo g; g.S = S; g.rowmask = (1u << S) - 1u; return g; }
+RAG_FN uint32_t rm(const Geo& g, int r) { return r < g.S ? g.rowmask : 0u; }
+RAG_FN BB bb_zero() { BB r; for (int i = 0; i < 32; i++) r.w[i] = 0; return r; }
+RAG_FN BB bb_board(const Geo& g) { BB r; for (int i = 0; i < 32; i++) r.w[i] = rm(g, i); return r; }
+RAG_FN BB operator&(BB a, BB b) { for (int i = 0; i < 32; i++) a.w[i] &= b.w[i]; return a; }
+RAG_FN BB operator|(BB a, BB b) { for (int i = 0; i < 32; i++) a.w[i] |= b.w[i]; return a; }
+RAG_FN BB operator^(BB a, BB b) { for (int i = 0; i < 32; i++) a.w[i] ^= b.w[i]; return a; }
+RAG_FN BB andnot(BB a, BB b) { for (int i = 0; i < 32; i++) a.w[i] &= ~b.w[i]; return a; }
+RAG_FN bool bb_any(BB a) { for (int i = 0; i < 32; i++) if (a.w[i]) return true; return false; }
+RAG_FN bool bb_equal(BB a, BB b) { for (int i = 0; i < 32; i++) if (a.w[i] != b.w[i]) return false; return true; }
+RAG_FN int bb_count(BB a) { int c = 0; for (int i = 0; i < 32; i++) c += __builtin_popcount(a.w[i]); return c; }
+RAG_FN BB bb_single(int q, const Geo&) { BB r = bb_zero(); r.w[q >> 5] = 1u << (q & 31); return r; }
+RAG_FN bool bb_test(BB a, int q) { return (a.w[q >> 5] >> (q & 31)) & 1u; }
+RAG_FN int bb_first(BB a) {
+    for (int i = 0; i < 32; i++) if (a.w[i]) return (i << 5) | __builtin_ctz(a.w[i]);
+    return -1;
+}
+RAG_FN BB bb_nbrs(BB a, const Geo& g) {
+    BB r;
+    for (int i = 0; i < 32; i++) {
+        uint32_t up = i > 0 ? a.w[i - 1] : 0u, dn = i < 31 ? a.w[i + 1] : 0u;
+        r.w[i] = (up | dn | (a.w[i] << 1) | (a.w[i] >> 1)) & rm(g, i);
+    }
+    return r;
+}
+RAG_FN BB bb_from_north(BB a, const Geo& g, bool fill) {
+    BB r; for (int i = 0; i < 32; i++) r.w[i] = (i > 0 ? a.w[i - 1] : (fill ? kFullMask : 0u)) & rm(g, i); return r;
+}
+RAG_FN BB bb_from_south(BB a, const Geo& g, bool fill) {
+    BB r;
+    for (int i = 0; i < 32; i++) r.w[i] = ((i == g.S - 1) ? (fill ? kFullMask : 0u) : (i < 31 ? a.w[i + 1] : 0u)) & rm(g, i);
+    return r;
+}
+RAG_FN BB bb_from_west(BB a, const Geo& g, bool fill) {
+    BB r; for (int i = 0; i < 32; i++) r.w[i] = ((a.w[i] << 1) | (fill ? 1u : 0u)) & rm(g, i); return r;
+}
+RAG_FN BB bb_from_east(BB a, const Geo& g, bool fill) {
+    BB r; for (int i = 0; i < 32; i++) r.w[i] = ((a.w[i] >> 1) | (fill ? (1u << (g.S - 1)) : 0u)) & rm(g, i); return r;
+}
+RAG_FN void plane_or(uint32_t* planes, int k, BB a, const Geo&) { for (int i = 0; i < 32; i++) planes[k * 32 + i] |= a.w[i]; }
+RAG_FN BB bb_load(const uint32_t* rows32, const Geo& g) { BB r; for (int i = 0; i < 32; i++) r.w[i] = rows32[i] & rm(g, i); return r; }
+RAG_FN void bb_store(uint32_t* rows32, BB a, const Geo&) { for (int i = 0; i < 32; i++) rows32[i] = a.w[i]; }
+
+#endif
+
+// ------------------------------------------------------------------ groups and liberties
+
+// Connected component(s) of `mask` containing `seed` (seed must lie inside mask).
+// Device-side twin of group_sets[x][y] (go.py:49,125-157): a fixed point of dilation.
+RAG_FN BB bb_flood(BB seed, BB mask, const Geo& g) {
+    BB cur = seed;
+    for (;;) {
+        BB nx = (cur | bb_nbrs(cur, g)) & mask;
+        nx = (nx | bb_nbrs(nx, g)) & mask;
+        if (bb_equal(nx, cur)) return cur;
+        cur = nx;
+    }
+}
+
+RAG_FN int q_neighbor(int q, int dir, int S) {
+    // reference order (x-1,y),(x+1,y),(x,y-1),(x,y+1) (go.py:108); -1 when off board
+    int x = q >> 5, y = q & 31;
+    if (dir == 0) return x > 0 ? q - 32 : -1;
+    if (dir == 1) return x + 1 < S ? q + 32 : -1;
+    if (dir == 2) return y > 0 ? q - 1 : -1;
+    return y + 1 < S ? q + 1 : -1;
+}
+
+RAG_FN int q_diagonal(int q, int i, int S) {
+    // reference order (x-1,y-1),(x+1,y+1),(x+1,y-1),(x-1,y+1) (go.py:122-123)
+    int x = (q >> 5) + ((i == 1 || i == 2) ? 1 : -1);
+    int y = (q & 31) + ((i == 1 || i == 3) ? 1 : -1);
+    if (x < 0 || y < 0 || x >= S || y >= S) return -1;
+    return (x << 5) | y;
+}
+
+// ------------------------------------------------------------------ do_move  (go.py:521-581)
+
+// Mover `M` plays q against `O`.  Returns false (nothing changed) when the move is not
+// legal by go.py:267-285 (occupied, ko, suicide; superko is not enforced on this path).
+// Captures are resolved in the reference's neighbour order so that the ko point, including
+// the "stale ko" of SURVEY H3, comes out the same (go.py:542-561).
+RAG_FN bool bb_play(const Geo& g, BB& M, BB& O, int& ko, int q, int* captured) {
+    if (q == ko) return false;
+    BB pt = bb_single(q, g);
+    if (bb_any((M | O) & pt)) return false;
+    BB M2 = M | pt, O2 = O;
+    int newko = -1, ncap = 0;
+    BB ptn = bb_nbrs(pt, g);
+    if (bb_any(ptn & O)) {
+        for (int d = 0; d < 4; d++) {
+            int nq = q_neighbor(q, d, g.S);
+            if (nq < 0 || !bb_test(O2, nq)) continue;
+            BB grp = bb_flood(bb_single(nq, g), O2, g);
+            BB empty = andnot(bb_board(g), M2 | O2);
+            if (bb_any(bb_nbrs(grp, g) & empty)) continue;
+            O2 = andnot(O2, grp);                                   // _remove_group, go.py:163-184
+            int sz = bb_count(grp);
+            ncap += sz;
+            if (sz == 1) {                                          // go.py:553-561
+                // recapture would take exactly the played stone: it is alone and its only
+                // liberty is the point just emptied
+                bool alone = !bb_any(ptn & M);
+                BB e2 = andnot(bb_board(g), M2 | O2);
+                if (alone && bb_count(ptn & e2) == 1) newko = nq;
+            }
+        }
+    }
+    BB me = bb_flood(pt, M2, g);
+    if (!bb_any(bb_nbrs(me, g) & andnot(bb_board(g), M2 | O2))) return false;   // suicide, go.py:219-240
+    M = M2; O = O2; ko = newko;
+    if (captured) *captured = ncap;
+    return true;
+}
+
+// ------------------------------------------------------------------ eyes  (go.py:287-327)
+
+struct EyeStack { uint16_t pos[kMaxBoard * kMaxBoard]; uint8_t idx[kMaxBoard * kMaxBoard]; uint8_t bad[kMaxBoard * kMaxBoard]; };
+
+RAG_FN bool q_interior(int q, int S) { int x = q >> 5, y = q & 31; return x > 0 && y > 0 && x + 1 < S && y + 1 < S; }
+
+// is_eye(q, owner) with owner's stones in `own`; `eyeish` = empty points whose 4-neighbours are
+// all `own` (go.py:287-297), precomputed bit-parallel.  Exact DFS incl. the ancestor-stack rule (H6).
+RAG_FN_NOINLINE bool bb_is_eye(const Geo& g, BB opp, BB empty, BB eyeish, int q, EyeStack& st) {
+    if (!bb_test(eyeish, q)) return false;
+    int depth = 0;
+    st.pos[0] = (uint16_t)q; st.idx[0] = 0; st.bad[0] = 0;
+    for (;;) {
+        int p = st.pos[depth];
+        int allow = q_interior(p, g.S) ? 1 : 0;
+        bool ret_valid = false, ret = false;
+        if (st.idx[depth] == 4) { ret_valid = true; ret = true; }
+        else {
+            int d = q_diagonal(p, st.idx[depth]++, g.S);
+            if (d < 0) continue;
+            bool badinc = false;
+            if (bb_test(opp, d)) badinc = true;
+            else if (bb_test(empty, d)) {
+                bool on_stack = false;
+                for (int k = 0; k < depth; k++) on_stack = on_stack || (st.pos[k] == d);
+                if (!on_stack) {
+                    if (!bb_test(eyeish, d)) badinc = true;
+                    else { depth++; st.pos[depth] = (uint16_t)d; st.idx[depth] = 0; st.bad[depth] = 0; continue; }
+                }
+            }
+            if (badinc && ++st.bad[depth] > allow) { ret_valid = true; ret = false; }
+        }
+        while (ret_valid) {                        // return `ret` from frame `depth`
+            if (depth == 0) return ret;
+            depth--;
+            ret_valid = false;
+            if (!ret) {
+                int pa = st.pos[depth];
+                if (++st.bad[depth] > (q_interior(pa, g.S) ? 1 : 0)) { ret_valid = true; ret = false; }
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------ per-position analysis
+
+struct Analysis {
+    BB empty, legal, sensible;
+    BB own_atari, opp_atari;       // stones of groups with exactly one liberty
+    BB opp_lib2;                   // opponent stones of groups with exactly two liberties
+};
+
+// Fills the canonical planes that need no look-ahead (everything but 44/45) and returns the
+// masks the ladder reader starts from.  `planes` = kNumPlanes x 32 words, zeroed by the caller.
+// own/opp are relative to the side to move (preprocessing.py:19-20); age0..2 = bits of
+// min(stone_ages, 7) (preprocessing.py:33-36); ko_q = q-index of the ko point or -1.
+RAG_FN_NOINLINE Analysis bb_features(const Geo& g, BB own, BB opp, BB age0, BB age1, BB age2, int ko_q,
+                                     uint32_t* planes, EyeStack& est) {
+    Analysis A;
+    const BB board = bb_board(g);
+    const BB stones = own | opp;
+    const BB empty = andnot(board, stones);
+    A.empty = empty;
+
+    // board / ones (preprocessing.py:14-22, 214-217); zeros stays clear
+    plane_or(planes, kPlaneBoard + 0, own, g);
+    plane_or(planes, kPlaneBoard + 1, opp, g);
+    plane_or(planes, kPlaneBoard + 2, empty, g);
+    plane_or(planes, kPlaneOnes, board, g);
+
+    // turns_since (preprocessing.py:25-37)
+    for (int k = 0; k < 8; k++) {
+        BB m = stones;
+        m = (k & 1) ? (m & age0) : andnot(m, age0);
+        m = (k & 2) ? (m & age1) : andnot(m, age1);
+        m = (k & 4) ? (m & age2) : andnot(m, age2);
+        plane_or(planes, kPlaneTurnsSince + k, m, g);
+    }
+
+    // liberties (preprocessing.py:40-56): one flood per group
+    BB lib1 = bb_zero(), lib2 = bb_zero();
+    {
+        BB rem = stones;
+        for (;;) {
+            int s = bb_first(rem);
+            if (s < 0) break;
+            BB grp = bb_flood(bb_single(s, g), bb_test(own, s) ? own : opp, g);
+            int L = bb_count(bb_nbrs(grp, g) & empty);
+            int k = (L < 8 ? L : 8) - 1;
+            if (k >= 0) plane_or(planes, kPlaneLiberties + k, grp, g);
+            if (L == 1) lib1 = lib1 | grp;
+            if (L == 2) lib2 = lib2 | grp;
+            rem = andnot(rem, grp);
+        }
+    }
+    A.own_atari = own & lib1;
+    A.opp_atari = opp & lib1;
+    A.opp_lib2 = opp & lib2;
+
+    // legality (go.py:219-285): an empty point is playable iff it has an empty neighbour, or
+    // joins an own group that keeps another liberty, or takes the last liberty of an enemy group
+    BB legal = empty & (bb_nbrs(empty, g) | bb_nbrs(andnot(own, A.own_atari), g) | bb_nbrs(A.opp_atari, g));
+    if (ko_q >= 0) legal = andnot(legal, bb_single(ko_q, g));
+    A.legal = legal;
+    plane_or(planes, kPlaneLegal, legal, g);
+
+    // sensibleness (preprocessing.py:190-196): legal and not an own true eye
+    BB eyeish = empty & bb_from_north(own, g, true) & bb_from_south(own, g, true) &
+                bb_from_west(own, g, true) & bb_from_east(own, g, true);
+    BB eyes = bb_zero();
+    {
+        BB rem = eyeish & legal;
+        for (;;) {
+            int q = bb_first(rem);
+            if (q < 0) break;
+            BB pt = bb_single(q, g);
+            if (bb_is_eye(g, opp, empty, eyeish, q, est)) eyes = eyes | pt;
+            rem = andnot(rem, pt);
+        }
+    }
+    A.sensible = andnot(legal, eyes);
+    plane_or(planes, kPlaneSensibleness, A.sensible, g);
+
+    // candidate-move planes (preprocessing.py:59-169).
+    // Quiet moves -- no own neighbour, no capturable neighbour -- in one bit-parallel pass:
+    // captures nothing, group = the stone alone, liberties = its empty neighbours.
+    BB touching = bb_nbrs(own, g) | bb_nbrs(A.opp_atari, g);
+    {
+        BB quiet = andnot(legal, touching);
+        BB a = bb_from_north(empty, g, false), b = bb_from_south(empty, g, false);
+        BB c = bb_from_west(empty, g, false), d = bb_from_east(empty, g, false);
+        BB s1 = a ^ b ^ c, c1 = (a & b) | (c & (a ^ b));          // a+b+c = s1 + 2*c1
+        BB s0 = s1 ^ d, c2 = s1 & d;                               // +d
+        BB two = c1 ^ c2, four = c1 & c2;                          // count = s0 + 2*two + 4*four
+        BB n1 = andnot(andnot(s0, two), four), n2 = andnot(andnot(two, s0), four);
+        BB n3 = andnot(s0 & two, four), n4 = four;
+        plane_or(planes, kPlaneCaptureSize + 0, quiet, g);
+        plane_or(planes, kPlaneLibertiesAfter + 0, quiet & n1, g);
+        plane_or(planes, kPlaneLibertiesAfter + 1, quiet & n2, g);
+        plane_or(planes, kPlaneLibertiesAfter + 2, quiet & n3, g);
+        plane_or(planes, kPlaneLibertiesAfter + 3, quiet & n4, g);
+        plane_or(planes, kPlaneSelfAtari + 0, quiet & n1, g);
+    }
+    // The rest one by one: merged group and captured stones by flood fill.
+    {
+        BB rem = legal & touching;
+        for (;;) {
+            int q = bb_first(rem);
+            if (q < 0) break;
+            BB pt = bb_single(q, g);
+            rem = andnot(rem, pt);
+            BB ptn = bb_nbrs(pt, g);
+            BB merged = bb_any(ptn & own) ? bb_flood(pt, own | pt, g) : pt;
+            BB seeds = ptn & A.opp_atari;
+            BB cap = bb_any(seeds) ? bb_flood(seeds, opp, g) : bb_zero();
+            int ncap = bb_count(cap);
+            BB libs = andnot(bb_nbrs(merged, g) & (empty | cap), pt);
+            int la = bb_count(libs);
+            plane_or(planes, kPlaneCaptureSize + (ncap < 7 ? ncap : 7), pt, g);
+            plane_or(planes, kPlaneLibertiesAfter + ((la - 1) < 7 ? ((la - 1) & 7) : 7), pt, g);
+            if (la == 1) {
+                int sz = bb_count(merged);
+                plane_or(planes, kPlaneSelfAtari + ((sz - 1) < 7 ? (sz - 1) : 7), pt, g);
+            }
+        }
+    }
+    return A;
+}
+
+// ------------------------------------------------------------------ ladder reader (go.py:329-463)
+
+struct LadderStack {
+    BB hunter[kLadderDepth];
+    BB prey[kLadderDepth];
+    BB pending[kLadderDepth];
+    int16_t ko[kLadderDepth];
+};
+
+enum { kLadderValue0 = 0, kLadderValue1 = 1, kLadderPush = 2 };
+
+// One call of is_ladder_capture (is_capture) or is_ladder_escape on a SINGLE prey group.
+// Plays `mv`, then either decides at once or leaves the set of replies to try in `pending`.
+//   capture node (go.py:345-391): hunter plays; replies = prey's liberties + the last liberty of
+//       every hunter group in atari that touches the prey; value = no reply escapes.
+//   escape node  (go.py:413-460): prey plays; >=3 liberties -> 1, 1 liberty -> 0, else
+//       replies = the two liberties; value = no reply is a ladder capture.
+// `remaining` is the reference's remaining_attempts; legality is tested before it (H11).
+RAG_FN int ladder_expand(const Geo& g, bool is_capture, BB& H, BB& P, int& ko, int mv, int prey_q,
+                         int remaining, BB& pending) {
+    bool ok = is_capture ? bb_play(g, H, P, ko, mv, nullptr) : bb_play(g, P, H, ko, mv, nullptr);
+    if (!ok) return kLadderValue0;
+    if (remaining <= 0) return is_capture ? kLadderValue1 : kLadderValue0;
+    BB empty = andnot(bb_board(g), H | P);
+    BB grp = bb_flood(bb_single(prey_q, g), P, g);
+    BB gn = bb_nbrs(grp, g);
+    BB libs = gn & empty;
+    if (is_capture) {
+        pending = libs;
+        BB rem = gn & H;
+        for (;;) {
+            int h = bb_first(rem);
+            if (h < 0) break;
+            BB hg = bb_flood(bb_single(h, g), H, g);
+            BB hl = bb_nbrs(hg, g) & empty;
+            if (bb_count(hl) == 1) pending = pending | hl;
+            rem = andnot(rem, hg);
+        }
+        return kLadderPush;
+    }
+    int L = bb_count(libs);
+    if (L >= 3) return kLadderValue1;
+    if (L == 1) return kLadderValue0;
+    pending = libs;
+    return kLadderPush;
+}
+
+// Depth-first search with an explicit stack; a node's value is "no child has value 1".
+RAG_FN_NOINLINE bool ladder_search(const Geo& g, BB H, BB P, int ko, int first_move, int prey_q,
+                                   bool root_is_capture, LadderStack& st) {
+    BB pending = bb_zero();
+    int res = ladder_expand(g, root_is_capture, H, P, ko, first_move, prey_q, kLadderDepth, pending);
+    if (res != kLadderPush) return res == kLadderValue1;
+    int d = 0;
+    st.hunter[0] = H; st.prey[0] = P; st.pending[0] = pending; st.ko[0] = (int16_t)ko;
+    for (;;) {
+        int v;
+        int m = bb_first(st.pending[d]);
+        if (m < 0) v = 1;                                    // every reply failed
+        else {
+            st.pending[d] = andnot(st.pending[d], bb_single(m, g));
+            bool node_is_capture = root_is_capture ^ ((d & 1) != 0);
+            H = st.hunter[d]; P = st.prey[d]; ko = st.ko[d];
+            res = ladder_expand(g, !node_is_capture, H, P, ko, m, prey_q, kLadderDepth - d - 1, pending);
+            if (res == kLadderPush) {
+                d++;
+                st.hunter[d] = H; st.prey[d] = P; st.pending[d] = pending; st.ko[d] = (int16_t)ko;
+                continue;
+            }
+            if (res == kLadderValue0) continue;              // this reply does not refute; try the next
+            v = 0;
+        }
+        for (;;) {                                           // frame d returns v
+            if (d == 0) return v == 1;
+            d--;
+            if (v == 0) break;                               // parent keeps looking
+            v = 0;                                           // a child of value 1 refutes the parent
+        }
+    }
+}
+
+// Top level of is_ladder_capture(action) / is_ladder_escape(action) with prey=None
+// (go.py:355-361, 422-428): any adjacent opponent group with exactly two liberties /
+// own group with exactly one.  `lib_sel` = stones of the groups that qualify.
+RAG_FN_NOINLINE bool ladder_root(const Geo& g, BB own, BB opp, int ko, int action_q, bool is_escape,
+                                 BB lib_sel, LadderStack& st) {
+    BB done = bb_zero();
+    for (int d = 0; d < 4; d++) {
+        int nq = q_neighbor(action_q, d, g.S);
+        if (nq < 0 || !bb_test(lib_sel, nq) || bb_test(done, nq)) continue;
+        done = done | bb_flood(bb_single(nq, g), lib_sel, g);
+        // capture: side to move hunts `opp`; escape: side to move is the prey
+        bool r = is_escape ? ladder_search(g, opp, own, ko, action_q, nq, false, st)
+                           : ladder_search(g, own, opp, ko, action_q, nq, true, st);
+        if (r) return true;
+    }
+    return false;
+}
+
+}  // namespace rag

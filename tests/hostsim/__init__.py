@@ -1,0 +1,39 @@
+"""Host stand-in for one warp running rocalphago_b200/csrc/go_bb.cuh -- TEST INFRASTRUCTURE ONLY."""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "libhostsim.so")
+_SRC = [os.path.join(_HERE, "hostsim.cpp"),
+        os.path.join(_HERE, "..", "..", "rocalphago_b200", "csrc", "go_bb.cuh")]
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_SO) or any(os.path.getmtime(s) > os.path.getmtime(_SO) for s in _SRC):
+            subprocess.check_call(["g++", "-O2", "-fPIC", "-shared", "-x", "c++", "-o", _SO, _SRC[0]])
+        L = ctypes.CDLL(_SO)
+        i32p = np.ctypeslib.ndpointer(np.int32, flags="C")
+        L.hostsim_features.restype = ctypes.c_int
+        L.hostsim_features.argtypes = [ctypes.c_int, ctypes.c_int, np.ctypeslib.ndpointer(np.int8, flags="C"),
+                                       np.ctypeslib.ndpointer(np.int16, flags="C"), i32p, i32p,
+                                       np.ctypeslib.ndpointer(np.uint8, flags="C"), ctypes.c_void_p]
+        _lib = L
+    return _lib
+
+
+def features49(board, age, ko, player):
+    """uint8 (n, 49, S, S): the 48 default planes + legal, computed by the lane-emulated device code."""
+    board = np.ascontiguousarray(board, np.int8)
+    n, S = board.shape[0], board.shape[-1]
+    out = np.empty((n, 49, S, S), np.uint8)
+    stats = np.zeros(2, np.int64)
+    lib().hostsim_features(n, S, board.reshape(n, -1), np.ascontiguousarray(age, np.int16).reshape(n, -1),
+                           np.ascontiguousarray(ko, np.int32), np.ascontiguousarray(player, np.int32),
+                           out.reshape(-1), stats.ctypes.data_as(ctypes.c_void_p))
+    return out, stats
