@@ -1,0 +1,138 @@
+/*
+ * rocalphago_b200.h -- C ABI of librocalphago_b200.so (sm_100a).
+ *
+ * The drop-in boundary for RocAlphaGo's batched position-evaluation path:
+ *     AlphaGo/preprocessing/preprocessing.py   Preprocess.state_to_tensor     (:287-294)
+ *     AlphaGo/models/nn_util.py                NeuralNetBase.forward          (:34-58)
+ *     AlphaGo/models/policy.py                 CNNPolicy.batch_eval_state     (:27-52)
+ *     AlphaGo/models/value.py                  value network forward          (:12-28)
+ * The reference is pure Python and has no FFI of its own; these are the entry
+ * points a ctypes/cffi stub in those four files binds (INTEGRATION.md shows the
+ * stub).  rocalphago_b200/_cabi.py is that stub for this repository's own
+ * Python host layer.
+ *
+ * Conventions
+ *   - every function returns 0 on success and a negative RAG_E* code on failure;
+ *     rag_last_error() gives the message of the calling thread's last failure
+ *   - pointers named d_* are DEVICE pointers owned by the caller; h_* are host
+ *     pointers; nothing here allocates or frees caller memory
+ *   - `stream` is a cudaStream_t passed as void* (0 = the legacy default stream);
+ *     calls enqueue work and return without synchronising unless stated
+ *   - board size S <= 19; flat point index p = x*S + y (AlphaGo/util.py:11-13)
+ */
+#ifndef ROCALPHAGO_B200_H
+#define ROCALPHAGO_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RAG_OK            0
+#define RAG_EINVAL       (-1)   /* bad argument */
+#define RAG_ECUDA        (-2)   /* a CUDA runtime/driver call failed */
+#define RAG_ENOMEM       (-3)   /* workspace too small / allocation failed */
+#define RAG_EUNSUPPORTED (-4)   /* shape or device not supported */
+
+/* message for the last error returned on this thread ("" if none) */
+const char* rag_last_error(void);
+/* ABI version, bumped on any signature change */
+int rag_abi_version(void);
+
+/* ------------------------------------------------------------------ packed game states
+ *
+ * A position on the device is RAG_STATE_WORDS uint32: six planes of 32 row words
+ * (row x in word x, point (x, y) in bit y): black, white, three bit-planes of
+ * min(stone_ages, 7), and a meta plane (word 0 = ko point p or -1, word 1 =
+ * current_player +1/-1, word 2 = board size).  This is the device twin of the
+ * fields of GameState the 48 planes depend on (go.py:18-22,55).
+ */
+#define RAG_STATE_WORDS 192
+#define RAG_STATE_BYTES (RAG_STATE_WORDS * 4)
+
+/* Host-side packing of GameState fields (go.py:18-22,55) into the device format.
+ * board int8 [n][S*S] in {+1 black, -1 white, 0}; age int16 [n][S*S] (stone_ages,
+ * -1 on empties); ko int32 [n] (x*S+y or -1); player int32 [n] (+1/-1).
+ * h_packed: n * RAG_STATE_WORDS uint32 (pinned memory recommended). */
+int rag_pack_states(int n, int size, const int8_t* h_board, const int16_t* h_age,
+                    const int32_t* h_ko, const int32_t* h_player, uint32_t* h_packed);
+/* The inverse (ages come back saturated at 7). */
+int rag_unpack_states(int n, int size, const uint32_t* h_packed, int8_t* h_board, int16_t* h_age,
+                      int32_t* h_ko, int32_t* h_player);
+
+/* ------------------------------------------------------------------ feature planes
+ *
+ * Preprocess.state_to_tensor (preprocessing.py:287-294) for a batch.  Planes are
+ * named by their index in the canonical list
+ *   0-2 board, 3 ones, 4-11 turns_since, 12-19 liberties, 20-27 capture_size,
+ *   28-35 self_atari_size, 36-43 liberties_after, 44 ladder_capture,
+ *   45 ladder_escape, 46 sensibleness, 47 zeros, 48 legal
+ * (preprocessing.py:209-263); h_plane_src lists, for each of the F output planes,
+ * which canonical plane it is, so any feature subset / order / repetition works.
+ */
+#define RAG_NUM_PLANES 49
+#define RAG_MAX_OUT_PLANES 128
+
+#define RAG_LAYOUT_NCHW_U8   0   /* uint8  [n][F][S*S]            (game_converter.py:76's storage dtype) */
+#define RAG_LAYOUT_NCHW_F32  1   /* float  [n][F][S*S]            (what NeuralNetBase.forward is fed)   */
+#define RAG_LAYOUT_CONV_IN   2   /* 16-bit [rag_conv_rows(n,S,pad)][conv_channels] zero-padded pixel rows:
+                                    the first conv layer's TMA source (layout described at
+                                    rag_conv_rows); element type chosen by `conv_dtype`                 */
+
+#define RAG_DTYPE_BF16 0
+#define RAG_DTYPE_FP16 1
+
+/* bytes of scratch rag_features / rag_features_analyze need for n positions */
+size_t rag_features_workspace_bytes(int n);
+
+/* Step 1: analyse n packed states into canonical bit-planes held in the workspace.
+ * with_ladders = 0 skips the ladder reader (planes 44/45 stay zero).  The
+ * workspace must stay untouched until the emits that read it have run. */
+int rag_features_analyze(const uint32_t* d_states, int n, int size, int with_ladders,
+                         void* d_workspace, size_t workspace_bytes, void* stream);
+/* Step 2: write the listed planes from the workspace in the requested layout.
+ * conv_dtype / conv_pad / conv_channels are read only for RAG_LAYOUT_CONV_IN
+ * (conv_pad = first layer's filter_width // 2; conv_channels = 64 or 128 >= F). */
+int rag_features_emit(const void* d_workspace, int n, int size, const int32_t* h_plane_src, int F,
+                      int layout, int conv_dtype, int conv_pad, int conv_channels, void* d_out,
+                      void* stream);
+/* Both steps (the ladder reader runs iff plane 44 or 45 is listed). */
+int rag_features(const uint32_t* d_states, int n, int size, const int32_t* h_plane_src, int F,
+                 int layout, int conv_dtype, int conv_pad, int conv_channels, void* d_out,
+                 void* d_workspace, size_t workspace_bytes, void* stream);
+
+/* Rows of the zero-padded pixel-row layout for n boards of size S with `pad` zero
+ * columns/rows per board: pixel (x, y) of board b is row
+ *     128 + b*(S+pad)*(S+pad) + x*(S+pad) + y
+ * and every other row is zero.  A buffer in this layout must be zero-filled once
+ * by its owner; kernels here only ever write the real-pixel rows. */
+long long rag_conv_rows(int n, int size, int pad);
+
+/* ------------------------------------------------------------------ state updates
+ *
+ * GameState.do_move (go.py:521-581) on packed states, in place, one move per
+ * state (p = x*S+y, or -1 = pass); d_status[i] = 0 played / -1 illegal (state
+ * untouched; the reference raises IllegalMove). */
+int rag_do_move(uint32_t* d_states, int n, int size, const int32_t* d_moves, int32_t* d_status,
+                void* stream);
+
+/* Random playouts on the device (the synthetic workload of BASELINE.json /
+ * SURVEY 8(d)).  Warp w owns output slots [w*quota, (w+1)*quota), quota =
+ * rag_playout_quota(max_ply, stride) = max_ply/stride + 1, and plays games from
+ * the empty board until they are full: every ply a uniformly random move from
+ * get_legal_moves(include_eyes=False) (go.py:465-480; pass when there is none;
+ * a game ends after two passes or max_ply), recording the position before ply t
+ * whenever t % stride == (w + game) % stride.  Deterministic in `seed`.
+ * d_move_log (optional, int32 [warps][log_stride]): every move warp w plays, in
+ * order (p, -1 = pass), each game preceded by -2 -- enough to replay the games
+ * elsewhere. */
+int rag_random_playouts(uint32_t* d_states_out, int n_positions, int size, uint64_t seed, int max_ply,
+                        int stride, int32_t* d_move_log, int log_stride, void* stream);
+int rag_playout_quota(int max_ply, int stride);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ROCALPHAGO_B200_H */

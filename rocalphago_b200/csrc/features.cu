@@ -1,0 +1,473 @@
+// features.cu -- batched Preprocess.state_to_tensor on packed game states (sm_100a).
+//
+// Replaces AlphaGo/preprocessing/preprocessing.py:14-294 and the parts of AlphaGo/go.py
+// it leans on (is_legal :267-285, is_eye :299-327, is_ladder_capture/escape :329-463,
+// do_move :521-581) for a batch held in HBM.  Three kernels per batch:
+//
+//   analyze_kernel  one warp per position (lane r = board row r): every plane that needs no
+//                   look-ahead, as 49 x 32 row words per position in the workspace, plus one
+//                   work item per ladder candidate (position, move, capture|escape) appended
+//                   to a queue in the workspace.
+//   ladder_kernel   persistent warps pull items off the queue and run the bounded-depth
+//                   ladder search (explicit stack in local memory), OR-ing hits into planes
+//                   44/45 of the workspace.  A queue instead of "one warp per position"
+//                   because ladder cost varies by 100x between positions.
+//   emit_*_kernel   bit-planes -> the layout the caller wants (uint8/float NCHW for the
+//                   Preprocess API, zero-padded 16-bit pixel rows for the first convolution).
+//                   Pure streaming; this is the HBM-bound kernel of the feature path.
+//
+// Also here: rag_do_move and rag_random_playouts (device do_move / playout generator).
+#include "go_bb.cuh"
+#include "rag_common.h"
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <string.h>
+
+namespace rag {
+
+char* last_error_buffer() {
+    static thread_local char buf[512] = {0};
+    return buf;
+}
+
+constexpr int kWarpsPerBlock = 4;
+constexpr int kPlaneWords = kNumPlanes * 32;           // 1568 words = 6272 B per position
+constexpr int kCounterBytes = 256;
+constexpr int kMaxPositionsPerLaunch = 1 << 21;        // queue item = pos<<11 | kind<<10 | q
+
+struct Workspace {
+    unsigned* counters;      // [0] items queued, [1] items taken
+    uint32_t* planes;        // [n][49][32]
+    uint32_t* queue;         // [n * 2 * S*S]
+    size_t queue_cap;
+};
+
+static size_t workspace_bytes(int n) {
+    return (size_t)kCounterBytes + (size_t)n * kPlaneWords * 4 + (size_t)n * 2 * kMaxBoard * kMaxBoard * 4;
+}
+
+static Workspace carve(void* base, int n) {
+    Workspace w;
+    char* p = (char*)base;
+    w.counters = (unsigned*)p;
+    w.planes = (uint32_t*)(p + kCounterBytes);
+    w.queue = (uint32_t*)(p + kCounterBytes + (size_t)n * kPlaneWords * 4);
+    w.queue_cap = (size_t)n * 2 * kMaxBoard * kMaxBoard;
+    return w;
+}
+
+// ---- packed state access --------------------------------------------------------------------
+
+struct LoadedState { BB black, white, age0, age1, age2; int ko_p, player; };
+
+__device__ __forceinline__ LoadedState load_state(const uint32_t* __restrict__ st, const Geo& g) {
+    LoadedState s;
+    s.black = bb_load(st + 0, g);  s.white = bb_load(st + 32, g);
+    s.age0 = bb_load(st + 64, g);  s.age1 = bb_load(st + 96, g);  s.age2 = bb_load(st + 128, g);
+    s.ko_p = (int)__ldg(st + 160); s.player = (int)__ldg(st + 161);
+    return s;
+}
+
+__device__ __forceinline__ int p_to_q(int p, int S) { return p < 0 ? -1 : (((p / S) << 5) | (p % S)); }
+__device__ __forceinline__ int q_to_p(int q, int S) { return q < 0 ? -1 : ((q >> 5) * S + (q & 31)); }
+
+// ---- kernel 1: planes without look-ahead + ladder work items ---------------------------------
+
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+analyze_kernel(const uint32_t* __restrict__ states, int n, int S, int with_ladders, Workspace ws)
+{
+    __shared__ uint32_t sm_planes[kWarpsPerBlock][kPlaneWords];
+    __shared__ EyeStack sm_eye[kWarpsPerBlock];
+    const int warp = threadIdx.x >> 5;
+    const int pos = blockIdx.x * kWarpsPerBlock + warp;
+    if (pos >= n) return;
+    const Geo g = make_geo(S);
+    uint32_t* planes = sm_planes[warp];
+    for (int k = 0; k < kNumPlanes; k++) planes[k * 32 + g.lane] = 0u;
+    __syncwarp();
+
+    const LoadedState s = load_state(states + (size_t)pos * RAG_STATE_WORDS, g);
+    const BB own = s.player > 0 ? s.black : s.white;
+    const BB opp = s.player > 0 ? s.white : s.black;
+    const Analysis A = bb_features(g, own, opp, s.age0, s.age1, s.age2, p_to_q(s.ko_p, S), planes, sm_eye[warp]);
+    __syncwarp();
+
+    uint32_t* out = ws.planes + (size_t)pos * kPlaneWords;
+    for (int k = 0; k < kNumPlanes; k++) out[k * 32 + g.lane] = planes[k * 32 + g.lane];
+
+    if (with_ladders) {
+        // is_ladder_capture needs an adjacent enemy group with exactly 2 liberties, is_ladder_escape
+        // an adjacent own group with exactly 1 (go.py:358-361, 425-428); only those moves are searched
+        BB cand[2] = { A.legal & bb_nbrs(A.opp_lib2, g), A.legal & bb_nbrs(A.own_atari, g) };
+        const int total = bb_count(cand[0]) + bb_count(cand[1]);
+        if (total > 0) {
+            unsigned base = 0;
+            if (g.lane == 0) base = atomicAdd(&ws.counters[0], (unsigned)total);
+            base = __shfl_sync(kFullMask, base, 0);
+            for (int kind = 0; kind < 2; kind++) {
+                BB rem = cand[kind];
+                for (;;) {
+                    int q = bb_first(rem);
+                    if (q < 0) break;
+                    rem = andnot(rem, bb_single(q, g));
+                    if (g.lane == 0 && base < ws.queue_cap)
+                        ws.queue[base] = ((uint32_t)pos << 11) | ((uint32_t)kind << 10) | (uint32_t)q;
+                    base++;
+                }
+            }
+        }
+    }
+}
+
+// ---- kernel 2: ladder reader -----------------------------------------------------------------
+
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+ladder_kernel(const uint32_t* __restrict__ states, int S, Workspace ws)
+{
+    const Geo g = make_geo(S);
+    LadderStack st;
+    const unsigned total = min((unsigned)ws.queue_cap, ws.counters[0]);
+    for (;;) {
+        unsigned idx = 0;
+        if (g.lane == 0) idx = atomicAdd(&ws.counters[1], 1u);
+        idx = __shfl_sync(kFullMask, idx, 0);
+        if (idx >= total) break;
+        const uint32_t item = ws.queue[idx];
+        const int pos = (int)(item >> 11), kind = (int)((item >> 10) & 1u), q = (int)(item & 1023u);
+        const LoadedState s = load_state(states + (size_t)pos * RAG_STATE_WORDS, g);
+        const BB own = s.player > 0 ? s.black : s.white;
+        const BB opp = s.player > 0 ? s.white : s.black;
+        const bool hit = ladder_root(g, own, opp, p_to_q(s.ko_p, S), q, kind == 1, st);
+        if (hit && g.lane == 0)
+            atomicOr(ws.planes + (size_t)pos * kPlaneWords + (kPlaneLadderCapture + kind) * 32 + (q >> 5),
+                     1u << (q & 31));
+    }
+}
+
+// ---- kernel 3: emit ---------------------------------------------------------------------------
+
+struct PlaneMap { int F; uint8_t src[RAG_MAX_OUT_PLANES]; };
+
+// NCHW: out[pos][f][x*S+y]; each thread writes V consecutive elements (16 bytes).
+template <typename T, int V>
+__global__ void __launch_bounds__(256)
+emit_nchw_kernel(const uint32_t* __restrict__ planes, long long total, int S, PlaneMap map, T* __restrict__ out)
+{
+    const int S2 = S * S, per_pos = map.F * S2;
+    for (long long e0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * V; e0 < total;
+         e0 += (long long)gridDim.x * blockDim.x * V) {
+        long long pos = e0 / per_pos;
+        int rem = (int)(e0 - pos * per_pos);
+        int f = rem / S2, p = rem - f * S2;
+        int x = p / S, y = p - x * S;
+        const uint32_t* pl = planes + pos * kPlaneWords;
+        uint32_t row = __ldg(pl + map.src[f] * 32 + x);
+        __align__(16) T vals[V];
+        #pragma unroll
+        for (int j = 0; j < V; j++) {
+            vals[j] = (T)((row >> y) & 1u);
+            if (++y == S) {
+                y = 0;
+                if (++x == S) {
+                    x = 0;
+                    if (++f == map.F) { f = 0; pos++; pl += kPlaneWords; }
+                }
+                if (e0 + j + 1 < total) row = __ldg(pl + map.src[f] * 32 + x);
+            }
+        }
+        if (e0 + V <= total) {
+            *reinterpret_cast<uint4*>(out + e0) = *reinterpret_cast<const uint4*>(vals);
+        } else {
+            for (int j = 0; e0 + j < total; j++) out[e0 + j] = vals[j];
+        }
+    }
+}
+
+// Conv input: 16-bit rows of C channels, row = lead + pos*Sp*Sp + x*Sp + y; only real pixels are
+// written (pad rows are zero from allocation and stay zero).  One thread = one 16-byte chunk
+// (8 channels) of one pixel; 8 (C=64) or 16 (C=128) consecutive threads share a pixel.
+__global__ void __launch_bounds__(256)
+emit_conv_kernel(const uint32_t* __restrict__ planes, int n, int S, int pad, int C, PlaneMap map,
+                 uint16_t one, uint16_t* __restrict__ out)
+{
+    const int S2 = S * S, Sp = S + pad, chunks = C / 8;
+    const long long total = (long long)n * S2 * chunks;
+    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+         t += (long long)gridDim.x * blockDim.x) {
+        int ch = (int)(t % chunks);
+        long long pix = t / chunks;
+        int pos = (int)(pix / S2), p = (int)(pix - (long long)pos * S2);
+        int x = p / S, y = p - x * S;
+        const uint32_t* pl = planes + (size_t)pos * kPlaneWords;
+        __align__(16) uint16_t v[8];
+        #pragma unroll
+        for (int j = 0; j < 8; j++) {
+            int f = ch * 8 + j;
+            uint32_t bit = 0;
+            if (f < map.F) bit = (__ldg(pl + map.src[f] * 32 + x) >> y) & 1u;
+            v[j] = bit ? one : (uint16_t)0;
+        }
+        long long row = kConvLeadRows + (long long)pos * Sp * Sp + x * Sp + y;
+        *reinterpret_cast<uint4*>(out + row * C + ch * 8) = *reinterpret_cast<const uint4*>(v);
+    }
+}
+
+// ---- do_move / playouts -----------------------------------------------------------------------
+
+__device__ __forceinline__ void store_state(uint32_t* st, const FullState& s, int S, const Geo& g) {
+    bb_store(st + 0, s.black, g);  bb_store(st + 32, s.white, g);
+    bb_store(st + 64, s.age0, g);  bb_store(st + 96, s.age1, g);  bb_store(st + 128, s.age2, g);
+    uint32_t m = 0;
+    if (g.lane == 0) m = (uint32_t)q_to_p(s.ko_q, S);
+    if (g.lane == 1) m = (uint32_t)s.player;
+    if (g.lane == 2) m = (uint32_t)S;
+    st[160 + g.lane] = m;
+}
+
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+do_move_kernel(uint32_t* states, int n, int S, const int32_t* __restrict__ moves, int32_t* status)
+{
+    const int pos = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
+    if (pos >= n) return;
+    const Geo g = make_geo(S);
+    uint32_t* st = states + (size_t)pos * RAG_STATE_WORDS;
+    const LoadedState l = load_state(st, g);
+    FullState s{l.black, l.white, l.age0, l.age1, l.age2, p_to_q(l.ko_p, S), l.player};
+    const int mv = moves[pos];
+    bool ok = mv < S * S;
+    if (ok) ok = bb_do_move(g, s, mv < 0 ? -1 : p_to_q(mv, S));
+    if (ok) store_state(st, s, S, g);
+    if (g.lane == 0 && status) status[pos] = ok ? 0 : -1;
+}
+
+__device__ __forceinline__ uint64_t splitmix64(uint64_t& x) {
+    uint64_t z = (x += 0x9E3779B97F4A7C15ull);
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+
+// One warp owns `quota` consecutive output slots and plays games until they are full.
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+playout_kernel(uint32_t* out, int n_positions, int S, uint64_t seed, int max_ply, int stride, int quota,
+               int32_t* move_log, int log_stride)
+{
+    __shared__ EyeStack sm_eye[kWarpsPerBlock];
+    const int warp = threadIdx.x >> 5;
+    const int w = blockIdx.x * kWarpsPerBlock + warp;
+    const int slot0 = w * quota;
+    if (slot0 >= n_positions) return;
+    const int slot_end = min(n_positions, slot0 + quota);
+    const Geo g = make_geo(S);
+    int slot = slot0, logged = 0;
+    for (int game = 0; slot < slot_end; game++) {
+        uint64_t rng = seed ^ (0xD1B54A32D192ED03ull * (uint64_t)(w + 1)) ^ (0x8CB92BA72F3D8DD7ull * (uint64_t)(game + 1));
+        FullState s{bb_zero(), bb_zero(), bb_zero(), bb_zero(), bb_zero(), -1, +1};
+        if (move_log && g.lane == 0 && logged < log_stride) move_log[(size_t)w * log_stride + logged] = -2;
+        logged++;
+        int passes = 0;
+        for (int t = 0; t <= max_ply && slot < slot_end; t++) {
+            if (t % stride == (w + game) % stride) {
+                store_state(out + (size_t)slot * RAG_STATE_WORDS, s, S, g);
+                slot++;
+            }
+            BB own = s.player > 0 ? s.black : s.white, opp = s.player > 0 ? s.white : s.black;
+            BB legal, sensible;
+            bb_moves(g, own, opp, s.ko_q, sm_eye[warp], legal, sensible);
+            const int cnt = bb_count(sensible);
+            int q = -1;
+            if (cnt > 0) q = bb_select(sensible, (int)(splitmix64(rng) % (uint64_t)cnt));
+            bb_do_move(g, s, q);
+            if (move_log && g.lane == 0 && logged < log_stride)
+                move_log[(size_t)w * log_stride + logged] = q_to_p(q, S);
+            logged++;
+            passes = q < 0 ? passes + 1 : 0;
+            if (passes >= 2) break;
+        }
+    }
+}
+
+static int check_size(int size) {
+    if (size < 2 || size > kMaxBoard) return fail(RAG_EUNSUPPORTED, "board size %d not in [2, 19]", size);
+    return RAG_OK;
+}
+
+static int build_map(const int32_t* h_plane_src, int F, PlaneMap* map) {
+    if (!h_plane_src || F <= 0 || F > RAG_MAX_OUT_PLANES)
+        return fail(RAG_EINVAL, "plane list must have 1..%d entries (got %d)", RAG_MAX_OUT_PLANES, F);
+    map->F = F;
+    for (int i = 0; i < F; i++) {
+        if (h_plane_src[i] < 0 || h_plane_src[i] >= kNumPlanes)
+            return fail(RAG_EINVAL, "plane_src[%d] = %d is not a canonical plane (0..%d)", i, h_plane_src[i], kNumPlanes - 1);
+        map->src[i] = (uint8_t)h_plane_src[i];
+    }
+    return RAG_OK;
+}
+
+}  // namespace rag
+
+using namespace rag;
+
+extern "C" {
+
+const char* rag_last_error(void) { return last_error_buffer(); }
+int rag_abi_version(void) { return 1; }
+
+int rag_pack_states(int n, int size, const int8_t* h_board, const int16_t* h_age, const int32_t* h_ko,
+                    const int32_t* h_player, uint32_t* h_packed)
+{
+    if (n < 0 || !h_board || !h_age || !h_ko || !h_player || !h_packed) return fail(RAG_EINVAL, "null argument");
+    if (int rc = check_size(size)) return rc;
+    const int np = size * size;
+    for (int b = 0; b < n; b++) {
+        uint32_t* st = h_packed + (size_t)b * RAG_STATE_WORDS;
+        memset(st, 0, RAG_STATE_BYTES);
+        const int8_t* bd = h_board + (size_t)b * np;
+        const int16_t* ag = h_age + (size_t)b * np;
+        for (int x = 0; x < size; x++)
+            for (int y = 0; y < size; y++) {
+                int v = bd[x * size + y];
+                if (v == 0) continue;
+                if (v != 1 && v != -1) return fail(RAG_EINVAL, "board[%d][%d][%d] = %d", b, x, y, v);
+                st[(v > 0 ? 0 : 32) + x] |= 1u << y;
+                int a = ag[x * size + y];
+                a = a < 0 ? 0 : (a > 7 ? 7 : a);
+                if (a & 1) st[64 + x] |= 1u << y;
+                if (a & 2) st[96 + x] |= 1u << y;
+                if (a & 4) st[128 + x] |= 1u << y;
+            }
+        if (h_ko[b] >= np) return fail(RAG_EINVAL, "ko[%d] = %d out of range", b, h_ko[b]);
+        if (h_player[b] != 1 && h_player[b] != -1) return fail(RAG_EINVAL, "player[%d] = %d", b, h_player[b]);
+        st[160] = (uint32_t)(h_ko[b] < 0 ? -1 : h_ko[b]);
+        st[161] = (uint32_t)h_player[b];
+        st[162] = (uint32_t)size;
+    }
+    return RAG_OK;
+}
+
+int rag_unpack_states(int n, int size, const uint32_t* h_packed, int8_t* h_board, int16_t* h_age,
+                      int32_t* h_ko, int32_t* h_player)
+{
+    if (n < 0 || !h_packed || !h_board || !h_age || !h_ko || !h_player) return fail(RAG_EINVAL, "null argument");
+    if (int rc = check_size(size)) return rc;
+    const int np = size * size;
+    for (int b = 0; b < n; b++) {
+        const uint32_t* st = h_packed + (size_t)b * RAG_STATE_WORDS;
+        for (int x = 0; x < size; x++)
+            for (int y = 0; y < size; y++) {
+                int bl = (st[x] >> y) & 1u, wh = (st[32 + x] >> y) & 1u;
+                h_board[(size_t)b * np + x * size + y] = (int8_t)(bl ? 1 : (wh ? -1 : 0));
+                int a = ((st[64 + x] >> y) & 1u) | (((st[96 + x] >> y) & 1u) << 1) | (((st[128 + x] >> y) & 1u) << 2);
+                h_age[(size_t)b * np + x * size + y] = (int16_t)((bl || wh) ? a : -1);
+            }
+        h_ko[b] = (int32_t)st[160];
+        h_player[b] = (int32_t)st[161];
+    }
+    return RAG_OK;
+}
+
+size_t rag_features_workspace_bytes(int n) { return n < 0 ? 0 : workspace_bytes(n); }
+
+int rag_features_analyze(const uint32_t* d_states, int n, int size, int with_ladders, void* d_workspace,
+                         size_t workspace_bytes_given, void* stream)
+{
+    if (n < 0 || (n > 0 && (!d_states || !d_workspace))) return fail(RAG_EINVAL, "null argument");
+    if (int rc = check_size(size)) return rc;
+    if (n > kMaxPositionsPerLaunch) return fail(RAG_EUNSUPPORTED, "n = %d exceeds %d positions per call", n, kMaxPositionsPerLaunch);
+    if (workspace_bytes_given < workspace_bytes(n))
+        return fail(RAG_ENOMEM, "workspace has %zu bytes, %zu needed for n = %d", workspace_bytes_given, workspace_bytes(n), n);
+    if (n == 0) return RAG_OK;
+    cudaStream_t s = (cudaStream_t)stream;
+    Workspace ws = carve(d_workspace, n);
+    RAG_CUDA_CHECK(cudaMemsetAsync(ws.counters, 0, kCounterBytes, s));
+    analyze_kernel<<<(n + kWarpsPerBlock - 1) / kWarpsPerBlock, kWarpsPerBlock * 32, 0, s>>>(d_states, n, size, with_ladders, ws);
+    RAG_CUDA_CHECK(cudaGetLastError());
+    if (with_ladders) {
+        int dev = 0, sms = 148;
+        RAG_CUDA_CHECK(cudaGetDevice(&dev));
+        RAG_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        // enough warps to keep every SM busy; each loops until the queue is drained
+        long long want = ((long long)n * 16 + kWarpsPerBlock - 1) / kWarpsPerBlock;
+        int blocks = (int)(want < (long long)sms * 8 ? (want < 1 ? 1 : want) : (long long)sms * 8);
+        ladder_kernel<<<blocks, kWarpsPerBlock * 32, 0, s>>>(d_states, size, ws);
+        RAG_CUDA_CHECK(cudaGetLastError());
+    }
+    return RAG_OK;
+}
+
+int rag_features_emit(const void* d_workspace, int n, int size, const int32_t* h_plane_src, int F, int layout,
+                      int conv_dtype, int conv_pad, int conv_channels, void* d_out, void* stream)
+{
+    if (n < 0 || (n > 0 && (!d_workspace || !d_out))) return fail(RAG_EINVAL, "null argument");
+    if (int rc = check_size(size)) return rc;
+    PlaneMap map;
+    if (int rc = build_map(h_plane_src, F, &map)) return rc;
+    if (n == 0) return RAG_OK;
+    cudaStream_t s = (cudaStream_t)stream;
+    const uint32_t* planes = (const uint32_t*)((const char*)d_workspace + kCounterBytes);
+    const long long total = (long long)n * F * size * size;
+    if (layout == RAG_LAYOUT_NCHW_U8) {
+        long long threads = (total + 15) / 16;
+        int blocks = (int)((threads + 255) / 256);
+        emit_nchw_kernel<uint8_t, 16><<<blocks, 256, 0, s>>>(planes, total, size, map, (uint8_t*)d_out);
+    } else if (layout == RAG_LAYOUT_NCHW_F32) {
+        long long threads = (total + 3) / 4;
+        int blocks = (int)((threads + 255) / 256);
+        emit_nchw_kernel<float, 4><<<blocks, 256, 0, s>>>(planes, total, size, map, (float*)d_out);
+    } else if (layout == RAG_LAYOUT_CONV_IN) {
+        if (conv_channels != 64 && conv_channels != 128) return fail(RAG_EINVAL, "conv_channels must be 64 or 128");
+        if (F > conv_channels) return fail(RAG_EINVAL, "%d planes do not fit %d channels", F, conv_channels);
+        if (conv_pad < 0 || conv_pad > 3) return fail(RAG_EINVAL, "conv_pad %d", conv_pad);
+        uint16_t one = conv_dtype == RAG_DTYPE_FP16 ? (uint16_t)0x3C00 : (uint16_t)0x3F80;
+        long long threads = (long long)n * size * size * (conv_channels / 8);
+        int blocks = (int)((threads + 255) / 256);
+        emit_conv_kernel<<<blocks, 256, 0, s>>>(planes, n, size, conv_pad, conv_channels, map, one, (uint16_t*)d_out);
+    } else {
+        return fail(RAG_EINVAL, "unknown layout %d", layout);
+    }
+    RAG_CUDA_CHECK(cudaGetLastError());
+    return RAG_OK;
+}
+
+int rag_features(const uint32_t* d_states, int n, int size, const int32_t* h_plane_src, int F, int layout,
+                 int conv_dtype, int conv_pad, int conv_channels, void* d_out, void* d_workspace,
+                 size_t workspace_bytes_given, void* stream)
+{
+    int with_ladders = 0;
+    for (int i = 0; h_plane_src && i < F; i++)
+        if (h_plane_src[i] == kPlaneLadderCapture || h_plane_src[i] == kPlaneLadderEscape) with_ladders = 1;
+    if (int rc = rag_features_analyze(d_states, n, size, with_ladders, d_workspace, workspace_bytes_given, stream)) return rc;
+    return rag_features_emit(d_workspace, n, size, h_plane_src, F, layout, conv_dtype, conv_pad, conv_channels, d_out, stream);
+}
+
+long long rag_conv_rows(int n, int size, int pad) { return conv_rows(n, size, pad); }
+
+int rag_do_move(uint32_t* d_states, int n, int size, const int32_t* d_moves, int32_t* d_status, void* stream)
+{
+    if (n < 0 || (n > 0 && (!d_states || !d_moves))) return fail(RAG_EINVAL, "null argument");
+    if (int rc = check_size(size)) return rc;
+    if (n == 0) return RAG_OK;
+    do_move_kernel<<<(n + kWarpsPerBlock - 1) / kWarpsPerBlock, kWarpsPerBlock * 32, 0, (cudaStream_t)stream>>>(
+        d_states, n, size, d_moves, d_status);
+    RAG_CUDA_CHECK(cudaGetLastError());
+    return RAG_OK;
+}
+
+int rag_random_playouts(uint32_t* d_states_out, int n_positions, int size, uint64_t seed, int max_ply, int stride,
+                        int32_t* d_move_log, int log_stride, void* stream)
+{
+    if (n_positions < 0 || (n_positions > 0 && !d_states_out)) return fail(RAG_EINVAL, "null argument");
+    if (int rc = check_size(size)) return rc;
+    if (max_ply < 0 || stride < 1) return fail(RAG_EINVAL, "max_ply %d / stride %d", max_ply, stride);
+    if (n_positions == 0) return RAG_OK;
+    const int quota = max_ply / stride + 1;
+    const int warps = (n_positions + quota - 1) / quota;
+    playout_kernel<<<(warps + kWarpsPerBlock - 1) / kWarpsPerBlock, kWarpsPerBlock * 32, 0, (cudaStream_t)stream>>>(
+        d_states_out, n_positions, size, seed, max_ply, stride, quota, d_move_log, d_move_log ? log_stride : 0);
+    RAG_CUDA_CHECK(cudaGetLastError());
+    return RAG_OK;
+}
+
+int rag_playout_quota(int max_ply, int stride) { return stride < 1 ? 0 : max_ply / stride + 1; }
+
+}  // extern "C"

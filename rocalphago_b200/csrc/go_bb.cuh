@@ -81,6 +81,22 @@ RAG_FN int bb_first(BB a) {
     uint32_t w = __shfl_sync(kFullMask, a.w, x);
     return (x << 5) | (__ffs(w) - 1);
 }
+// r-th (0-based) point of the set in x-major order; r must be < bb_count(a)
+RAG_FN int bb_select(BB a, int r) {
+    unsigned c = (unsigned)__popc(a.w), incl = c;
+    const unsigned lane = threadIdx.x & 31u;
+    #pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        unsigned t = __shfl_up_sync(kFullMask, incl, o);
+        if (lane >= (unsigned)o) incl += t;
+    }
+    unsigned excl = incl - c;
+    bool mine = (unsigned)r >= excl && (unsigned)r < incl;
+    int x = __ffs(__ballot_sync(kFullMask, mine)) - 1;
+    uint32_t w = __shfl_sync(kFullMask, a.w, x);
+    unsigned k = (unsigned)r - __shfl_sync(kFullMask, excl, x);
+    return (x << 5) | (int)__fns(w, 0, (int)k + 1);
+}
 // 4-neighbourhood of a set (without the set itself); go.py:103-116
 RAG_FN BB bb_nbrs(BB a, const Geo& g) {
     uint32_t up = __shfl_up_sync(kFullMask, a.w, 1);        // row x-1
@@ -129,6 +145,14 @@ RAG_FN BB bb_single(int q, const Geo&) { BB r = bb_zero(); r.w[q >> 5] = 1u << (
 RAG_FN bool bb_test(BB a, int q) { return (a.w[q >> 5] >> (q & 31)) & 1u; }
 RAG_FN int bb_first(BB a) {
     for (int i = 0; i < 32; i++) if (a.w[i]) return (i << 5) | __builtin_ctz(a.w[i]);
+    return -1;
+}
+RAG_FN int bb_select(BB a, int r) {
+    for (int i = 0; i < 32; i++) {
+        int c = __builtin_popcount(a.w[i]);
+        if (r < c) { uint32_t w = a.w[i]; while (r--) w &= w - 1; return (i << 5) | __builtin_ctz(w); }
+        r -= c;
+    }
     return -1;
 }
 RAG_FN BB bb_nbrs(BB a, const Geo& g) {
@@ -281,6 +305,59 @@ struct Analysis {
     BB opp_lib2;                   // opponent stones of groups with exactly two liberties
 };
 
+// One flood per group: stones of groups with exactly 1 / exactly 2 liberties, and (when
+// `planes` is given) the one-hot min(liberty_counts, 8) planes of preprocessing.py:40-56.
+RAG_FN void bb_scan_groups(const Geo& g, BB own, BB opp, BB empty, uint32_t* planes, BB& lib1, BB& lib2) {
+    lib1 = bb_zero(); lib2 = bb_zero();
+    BB rem = own | opp;
+    for (;;) {
+        int s = bb_first(rem);
+        if (s < 0) break;
+        BB grp = bb_flood(bb_single(s, g), bb_test(own, s) ? own : opp, g);
+        int L = bb_count(bb_nbrs(grp, g) & empty);
+        if (planes) {
+            int k = (L < 8 ? L : 8) - 1;
+            if (k >= 0) plane_or(planes, kPlaneLiberties + k, grp, g);
+        }
+        if (L == 1) lib1 = lib1 | grp;
+        if (L == 2) lib2 = lib2 | grp;
+        rem = andnot(rem, grp);
+    }
+}
+
+// Legality of every point at once (go.py:219-285): an empty point is playable iff it has an
+// empty neighbour, or joins an own group that keeps another liberty, or takes the last
+// liberty of an enemy group; and it is not the ko point.
+RAG_FN BB bb_legal(const Geo& g, BB own, BB empty, BB own_atari, BB opp_atari, int ko_q) {
+    BB legal = empty & (bb_nbrs(empty, g) | bb_nbrs(andnot(own, own_atari), g) | bb_nbrs(opp_atari, g));
+    if (ko_q >= 0) legal = andnot(legal, bb_single(ko_q, g));
+    return legal;
+}
+
+// Own true eyes among `among` (go.py:299-327).
+RAG_FN BB bb_own_eyes(const Geo& g, BB own, BB opp, BB empty, BB among, EyeStack& est) {
+    BB eyeish = empty & bb_from_north(own, g, true) & bb_from_south(own, g, true) &
+                bb_from_west(own, g, true) & bb_from_east(own, g, true);
+    BB eyes = bb_zero();
+    BB rem = eyeish & among;
+    for (;;) {
+        int q = bb_first(rem);
+        if (q < 0) break;
+        BB pt = bb_single(q, g);
+        if (bb_is_eye(g, opp, empty, eyeish, q, est)) eyes = eyes | pt;
+        rem = andnot(rem, pt);
+    }
+    return eyes;
+}
+
+// Legal and sensible moves only (what a playout step needs; go.py:465-480).
+RAG_FN_NOINLINE void bb_moves(const Geo& g, BB own, BB opp, int ko_q, EyeStack& est, BB& legal, BB& sensible) {
+    BB empty = andnot(bb_board(g), own | opp), lib1, lib2;
+    bb_scan_groups(g, own, opp, empty, nullptr, lib1, lib2);
+    legal = bb_legal(g, own, empty, own & lib1, opp & lib1, ko_q);
+    sensible = andnot(legal, bb_own_eyes(g, own, opp, empty, legal, est));
+}
+
 // Fills the canonical planes that need no look-ahead (everything but 44/45) and returns the
 // masks the ladder reader starts from.  `planes` = kNumPlanes x 32 words, zeroed by the caller.
 // own/opp are relative to the side to move (preprocessing.py:19-20); age0..2 = bits of
@@ -308,48 +385,19 @@ RAG_FN_NOINLINE Analysis bb_features(const Geo& g, BB own, BB opp, BB age0, BB a
         plane_or(planes, kPlaneTurnsSince + k, m, g);
     }
 
-    // liberties (preprocessing.py:40-56): one flood per group
-    BB lib1 = bb_zero(), lib2 = bb_zero();
-    {
-        BB rem = stones;
-        for (;;) {
-            int s = bb_first(rem);
-            if (s < 0) break;
-            BB grp = bb_flood(bb_single(s, g), bb_test(own, s) ? own : opp, g);
-            int L = bb_count(bb_nbrs(grp, g) & empty);
-            int k = (L < 8 ? L : 8) - 1;
-            if (k >= 0) plane_or(planes, kPlaneLiberties + k, grp, g);
-            if (L == 1) lib1 = lib1 | grp;
-            if (L == 2) lib2 = lib2 | grp;
-            rem = andnot(rem, grp);
-        }
-    }
+    // liberties (preprocessing.py:40-56)
+    BB lib1, lib2;
+    bb_scan_groups(g, own, opp, empty, planes, lib1, lib2);
     A.own_atari = own & lib1;
     A.opp_atari = opp & lib1;
     A.opp_lib2 = opp & lib2;
 
-    // legality (go.py:219-285): an empty point is playable iff it has an empty neighbour, or
-    // joins an own group that keeps another liberty, or takes the last liberty of an enemy group
-    BB legal = empty & (bb_nbrs(empty, g) | bb_nbrs(andnot(own, A.own_atari), g) | bb_nbrs(A.opp_atari, g));
-    if (ko_q >= 0) legal = andnot(legal, bb_single(ko_q, g));
+    BB legal = bb_legal(g, own, empty, A.own_atari, A.opp_atari, ko_q);
     A.legal = legal;
     plane_or(planes, kPlaneLegal, legal, g);
 
     // sensibleness (preprocessing.py:190-196): legal and not an own true eye
-    BB eyeish = empty & bb_from_north(own, g, true) & bb_from_south(own, g, true) &
-                bb_from_west(own, g, true) & bb_from_east(own, g, true);
-    BB eyes = bb_zero();
-    {
-        BB rem = eyeish & legal;
-        for (;;) {
-            int q = bb_first(rem);
-            if (q < 0) break;
-            BB pt = bb_single(q, g);
-            if (bb_is_eye(g, opp, empty, eyeish, q, est)) eyes = eyes | pt;
-            rem = andnot(rem, pt);
-        }
-    }
-    A.sensible = andnot(legal, eyes);
+    A.sensible = andnot(legal, bb_own_eyes(g, own, opp, empty, legal, est));
     plane_or(planes, kPlaneSensibleness, A.sensible, g);
 
     // candidate-move planes (preprocessing.py:59-169).
@@ -396,6 +444,34 @@ RAG_FN_NOINLINE Analysis bb_features(const Geo& g, BB own, BB opp, BB age0, BB a
         }
     }
     return A;
+}
+
+// ------------------------------------------------------------------ full do_move incl. stone ages
+
+// Colours are absolute here (black/white); `player` = +1 black to move, -1 white.
+struct FullState { BB black, white, age0, age1, age2; int ko_q; int player; };
+
+// GameState.do_move(action) for the side to move (go.py:521-581); q < 0 = pass.
+// Ages are the 3-bit saturating twin of stone_ages: +1 for every stone on any legal move
+// incl. pass (go.py:533), 0 for the new stone (go.py:539), cleared on capture (go.py:175).
+// Returns false and leaves the state alone on an illegal move (IllegalMove, go.py:573-575).
+RAG_FN bool bb_do_move(const Geo& g, FullState& s, int q) {
+    BB M = s.player > 0 ? s.black : s.white, O = s.player > 0 ? s.white : s.black;
+    int ko = s.ko_q;
+    BB stones_before = M | O;
+    if (q >= 0) { if (!bb_play(g, M, O, ko, q, nullptr)) return false; }
+    else ko = -1;
+    BB sat = s.age0 & s.age1 & s.age2;
+    BB n0 = andnot(stones_before, s.age0) | sat;
+    BB c0 = s.age0;
+    BB n1 = (s.age1 ^ c0) | sat;
+    BB n2 = (s.age2 ^ (s.age1 & c0)) | sat;
+    BB keep = M | O;                                   // survivors + the new stone
+    if (q >= 0) keep = andnot(keep, bb_single(q, g));  // new stone: age 0
+    s.age0 = n0 & stones_before & keep; s.age1 = n1 & stones_before & keep; s.age2 = n2 & stones_before & keep;
+    if (s.player > 0) { s.black = M; s.white = O; } else { s.white = M; s.black = O; }
+    s.ko_q = ko; s.player = -s.player;
+    return true;
 }
 
 // ------------------------------------------------------------------ ladder reader (go.py:329-463)
@@ -480,15 +556,20 @@ RAG_FN_NOINLINE bool ladder_search(const Geo& g, BB H, BB P, int ko, int first_m
 }
 
 // Top level of is_ladder_capture(action) / is_ladder_escape(action) with prey=None
-// (go.py:355-361, 422-428): any adjacent opponent group with exactly two liberties /
-// own group with exactly one.  `lib_sel` = stones of the groups that qualify.
+// (go.py:355-361, 422-428): true if the search succeeds for ANY adjacent opponent group with
+// exactly two liberties (capture) / own group with exactly one (escape).
 RAG_FN_NOINLINE bool ladder_root(const Geo& g, BB own, BB opp, int ko, int action_q, bool is_escape,
-                                 BB lib_sel, LadderStack& st) {
+                                 LadderStack& st) {
+    const BB side = is_escape ? own : opp;
+    const BB empty = andnot(bb_board(g), own | opp);
+    const int want = is_escape ? 1 : 2;
     BB done = bb_zero();
     for (int d = 0; d < 4; d++) {
         int nq = q_neighbor(action_q, d, g.S);
-        if (nq < 0 || !bb_test(lib_sel, nq) || bb_test(done, nq)) continue;
-        done = done | bb_flood(bb_single(nq, g), lib_sel, g);
+        if (nq < 0 || !bb_test(side, nq) || bb_test(done, nq)) continue;
+        BB grp = bb_flood(bb_single(nq, g), side, g);
+        done = done | grp;
+        if (bb_count(bb_nbrs(grp, g) & empty) != want) continue;
         // capture: side to move hunts `opp`; escape: side to move is the prey
         bool r = is_escape ? ladder_search(g, opp, own, ko, action_q, nq, false, st)
                            : ladder_search(g, own, opp, ko, action_q, nq, true, st);

@@ -1,0 +1,135 @@
+"""Preprocess: GameState -> one-hot feature planes, computed on the GPU.
+
+Drop-in for AlphaGo/preprocessing/preprocessing.py (names, feature order, shapes and error
+text follow preprocessing.py:209-294).  `state_to_tensor(state)` keeps the reference
+signature; `states_to_tensor` / `to_device` are the batched forms the reference lacks.
+"""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _cabi
+from .state import BatchedGameState, _ptr, _stream, _require_cuda
+
+# name -> (number of planes, first canonical plane)   preprocessing.py:209-258
+FEATURES = {
+    "board": {"size": 3, "plane": 0},
+    "ones": {"size": 1, "plane": 3},
+    "turns_since": {"size": 8, "plane": 4},
+    "liberties": {"size": 8, "plane": 12},
+    "capture_size": {"size": 8, "plane": 20},
+    "self_atari_size": {"size": 8, "plane": 28},
+    "liberties_after": {"size": 8, "plane": 36},
+    "ladder_capture": {"size": 1, "plane": 44},
+    "ladder_escape": {"size": 1, "plane": 45},
+    "sensibleness": {"size": 1, "plane": 46},
+    "zeros": {"size": 1, "plane": 47},
+    "legal": {"size": 1, "plane": 48},
+}
+
+# preprocessing.py:260-263
+DEFAULT_FEATURES = [
+    "board", "ones", "turns_since", "liberties", "capture_size",
+    "self_atari_size", "liberties_after", "ladder_capture", "ladder_escape",
+    "sensibleness", "zeros"]
+
+LAYOUT_NCHW_U8, LAYOUT_NCHW_F32, LAYOUT_CONV_IN = 0, 1, 2
+DTYPE_BF16, DTYPE_FP16 = 0, 1
+_MOVE_PLANES = np.asarray([46, 48], np.int32)      # sensibleness, legal
+
+
+class _Workspace(object):
+    """Grows-only scratch for the analyse step, one per (device)."""
+
+    def __init__(self):
+        self.buf = None
+
+    def get(self, n, device):
+        need = int(_cabi.lib().rag_features_workspace_bytes(n))
+        if self.buf is None or self.buf.numel() < need or self.buf.device != device:
+            self.buf = torch.empty(need, dtype=torch.uint8, device=device)
+        return self.buf
+
+
+class Preprocess(object):
+    """a class to convert from AlphaGo GameState objects to tensors of one-hot
+    features for NN inputs (preprocessing.py:266-294)"""
+
+    def __init__(self, feature_list=DEFAULT_FEATURES):
+        self.output_dim = 0
+        self.feature_list = feature_list
+        self.processors = [None] * len(feature_list)
+        src = []
+        for i in range(len(feature_list)):
+            feat = feature_list[i].lower()
+            if feat in FEATURES:
+                self.processors[i] = feat
+                self.output_dim += FEATURES[feat]["size"]
+                src += list(range(FEATURES[feat]["plane"], FEATURES[feat]["plane"] + FEATURES[feat]["size"]))
+            else:
+                raise ValueError("uknown feature: %s" % feat)        # sic, preprocessing.py:285
+        self.plane_src = np.asarray(src, np.int32)
+        self._ws = _Workspace()
+
+    # ------------------------------------------------------------------ device-level
+    def analyze(self, batch, with_ladders=None):
+        """Runs the analysis + ladder kernels; returns the workspace tensor the emits read."""
+        _require_cuda()
+        if with_ladders is None:
+            with_ladders = bool(np.any((self.plane_src == 44) | (self.plane_src == 45)))
+        ws = self._ws.get(len(batch), batch.device)
+        with torch.cuda.device(batch.device):
+            _cabi.check(_cabi.lib().rag_features_analyze(_ptr(batch.packed), len(batch), batch.size,
+                                                         int(with_ladders), _ptr(ws), ws.numel(), _stream()))
+        return ws
+
+    def emit(self, ws, n, size, layout=LAYOUT_NCHW_U8, plane_src=None, conv_dtype=DTYPE_BF16, conv_pad=2,
+             conv_channels=64, out=None):
+        src = self.plane_src if plane_src is None else np.ascontiguousarray(plane_src, np.int32)
+        F = len(src)
+        dev = ws.device
+        L = _cabi.lib()
+        if out is None:
+            if layout == LAYOUT_NCHW_U8:
+                out = torch.empty((n, F, size, size), dtype=torch.uint8, device=dev)
+            elif layout == LAYOUT_NCHW_F32:
+                out = torch.empty((n, F, size, size), dtype=torch.float32, device=dev)
+            else:
+                rows = int(L.rag_conv_rows(n, size, conv_pad))
+                out = torch.zeros((rows, conv_channels), device=dev,
+                                  dtype=torch.bfloat16 if conv_dtype == DTYPE_BF16 else torch.float16)
+        with torch.cuda.device(dev):
+            _cabi.check(L.rag_features_emit(_ptr(ws), n, size, src.ctypes.data_as(ctypes.c_void_p), F, layout,
+                                            conv_dtype, conv_pad, conv_channels, _ptr(out), _stream()))
+        return out
+
+    def to_device(self, batch, layout=LAYOUT_NCHW_U8, **kw):
+        """Feature planes of a BatchedGameState as a CUDA tensor in `layout`."""
+        ws = self.analyze(batch)
+        return self.emit(ws, len(batch), batch.size, layout=layout, **kw)
+
+    def legal_move_lists(self, ws, n, size):
+        """get_legal_moves() of every position in reference order (go.py:465-480): legal
+        non-eye points x-major, then legal own eyes x-major.  Returns lists of (x, y)."""
+        two = self.emit(ws, n, size, LAYOUT_NCHW_U8, plane_src=_MOVE_PLANES).cpu().numpy().reshape(n, 2, -1)
+        out = []
+        for i in range(n):
+            sens = np.flatnonzero(two[i, 0])
+            eyes = np.flatnonzero(two[i, 1] & (1 - two[i, 0]))
+            idx = np.concatenate([sens, eyes])
+            out.append([(int(p) // size, int(p) % size) for p in idx])
+        return out
+
+    # ------------------------------------------------------------------ reference-shaped API
+    def states_to_tensor(self, states):
+        """Batched state_to_tensor: (N, F, S, S) uint8 numpy array for a list of GameStates."""
+        if len(states) == 0:
+            return np.zeros((0, self.output_dim, 0, 0), np.uint8)
+        batch = states if isinstance(states, BatchedGameState) else BatchedGameState.from_states(states)
+        return self.to_device(batch, LAYOUT_NCHW_U8).cpu().numpy()
+
+    def state_to_tensor(self, state):
+        """Convert a GameState to a Theano-compatible tensor: (1, F, S, S) float64 of 0/1
+        (preprocessing.py:287-294)."""
+        return self.states_to_tensor([state]).astype(np.float64)

@@ -46,7 +46,7 @@ extern "C" int hostsim_features(int n, int S, const int8_t* board, const int16_t
                 int q = bb_first(rem);
                 if (q < 0) break;
                 rem = andnot(rem, bb_single(q, g));
-                bool r = ladder_root(g, own, opp, ko_q, q, kind == 1, kind ? A.own_atari : A.opp_lib2, *lst);
+                bool r = ladder_root(g, own, opp, ko_q, q, kind == 1, *lst);
                 if (r) planes[(kind ? kPlaneLadderEscape : kPlaneLadderCapture) * 32 + (q >> 5)] |= 1u << (q & 31);
             }
         }

@@ -1,0 +1,161 @@
+"""Parity of the CUDA feature path (through the C ABI) with the reference: bit-exact planes
+against the golden fixtures recorded from the reference, and against the C oracle on fresh
+random playouts at sizes the fixtures cannot hold.  Run on the B200 box: pytest -m gpu."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import go_oracle
+from rocalphago_b200 import BatchedGameState, Preprocess, PositionView
+from rocalphago_b200 import preprocessing as P
+from tests import golden_util as gu
+
+pytestmark = pytest.mark.gpu
+
+ALL = ["board", "ones", "turns_since", "liberties", "capture_size", "self_atari_size",
+       "liberties_after", "ladder_capture", "ladder_escape", "sensibleness", "zeros", "legal"]
+
+
+def _explain(got, want):
+    bad = np.argwhere(got != want)
+    planes = sorted(set(bad[:, 1].tolist()))
+    return "mismatches %d in planes %s, first (pos, plane, x, y): %s" % (len(bad), planes, bad[:6].tolist())
+
+
+def _gpu_planes(board, age, ko, player, feature_list=ALL, layout=P.LAYOUT_NCHW_U8):
+    batch = BatchedGameState.from_arrays(board, age, ko, player)
+    return Preprocess(feature_list).to_device(batch, layout).cpu().numpy()
+
+
+@pytest.mark.parametrize("name", gu.FEATURE_FILES)
+def test_planes_bit_exact_vs_reference_golden(name):
+    g = gu.load_features(name)
+    got = _gpu_planes(g["board"], g["age"], g["ko"], g["player"])
+    assert got.dtype == np.uint8 and got.shape == g["planes"].shape
+    assert np.array_equal(got, g["planes"]), _explain(got, g["planes"])
+
+
+@pytest.mark.parametrize("size,n,seed", [(19, 12000, 101), (13, 2000, 102), (9, 2000, 103), (7, 1000, 104),
+                                         (6, 500, 105), (5, 500, 106), (2, 20, 107)])
+def test_planes_bit_exact_vs_oracle_on_playouts(size, n, seed):
+    b, a, ko, pl = go_oracle.random_playouts(n, size=size, seed=seed, max_ply=size * size + 40, stride=5)
+    want = go_oracle.features(b, a, ko, pl, ALL)
+    got = _gpu_planes(b, a, ko, pl)
+    assert np.array_equal(got, want), _explain(got, want)
+
+
+def test_feature_subsets_orders_repeats_and_float_layout():
+    g = gu.load_features("features_playouts_9.npz")
+    for fl in (["board", "sensibleness", "capture_size"], ["legal"], ["zeros", "ones", "board", "board"],
+               ["LADDER_ESCAPE", "Liberties"], ["ladder_capture"]):
+        got = _gpu_planes(g["board"], g["age"], g["ko"], g["player"], fl)
+        assert np.array_equal(got, gu.select_planes(g["planes"], fl)), fl
+    got = _gpu_planes(g["board"], g["age"], g["ko"], g["player"], P.DEFAULT_FEATURES, P.LAYOUT_NCHW_F32)
+    assert got.dtype == np.float32
+    assert np.array_equal(got, gu.select_planes(g["planes"], P.DEFAULT_FEATURES).astype(np.float32))
+
+
+@pytest.mark.parametrize("dtype", [P.DTYPE_BF16, P.DTYPE_FP16])
+@pytest.mark.parametrize("size,pad", [(19, 2), (19, 1), (9, 2)])
+def test_conv_input_layout(size, pad, dtype):
+    """Zero-padded pixel rows: real pixels carry the planes as 1.0/0.0, every other row is zero."""
+    g = gu.load_features("features_playouts_%d.npz" % size)
+    n = 37
+    batch = BatchedGameState.from_arrays(g["board"][:n], g["age"][:n], g["ko"][:n], g["player"][:n])
+    pp = Preprocess(P.DEFAULT_FEATURES)
+    out = pp.to_device(batch, P.LAYOUT_CONV_IN, conv_dtype=dtype, conv_pad=pad, conv_channels=64)
+    rows = out.float().cpu().numpy()
+    Sp = size + pad
+    want = np.zeros_like(rows)
+    planes = gu.select_planes(g["planes"][:n], P.DEFAULT_FEATURES)            # (n,48,S,S)
+    for b in range(n):
+        blk = np.zeros((Sp, Sp, 64), np.float32)
+        blk[:size, :size, :48] = planes[b].transpose(1, 2, 0)
+        want[128 + b * Sp * Sp:128 + (b + 1) * Sp * Sp] = blk.reshape(Sp * Sp, 64)
+    assert rows.shape[0] % 128 == 0 and rows.shape[0] >= 128 + n * Sp * Sp + 128
+    assert np.array_equal(rows, want)
+
+
+def test_state_to_tensor_keeps_reference_signature():
+    g = gu.load_features("features_fixture_boards.npz")
+    pp = Preprocess()
+    for i in range(len(g["ko"])):
+        st = PositionView(g["board"][i], g["age"][i], int(g["ko"][i]), int(g["player"][i]))
+        t = pp.state_to_tensor(st)
+        assert t.shape == (1, 48, 7, 7) and t.dtype == np.float64
+        assert np.array_equal(t[0], gu.select_planes(g["planes"][i:i + 1], P.DEFAULT_FEATURES)[0])
+    assert Preprocess(["board"]).states_to_tensor([]).shape[0] == 0
+    a = PositionView(np.zeros((9, 9)), -np.ones((9, 9)), None, 1)
+    b = PositionView(np.zeros((7, 7)), -np.ones((7, 7)), None, 1)
+    with pytest.raises(ValueError, match="same size"):
+        pp.states_to_tensor([a, b])
+
+
+def test_legal_move_lists_follow_reference_order():
+    g = gu.load_features("features_sgf.npz")
+    batch = BatchedGameState.from_arrays(g["board"], g["age"], g["ko"], g["player"])
+    pp = Preprocess()
+    ws = pp.analyze(batch)
+    lists = pp.legal_move_lists(ws, len(batch), 19)
+    for i, lst in enumerate(lists):
+        want = g["legal_moves"][i, :g["n_legal"][i]]
+        assert [x * 19 + y for (x, y) in lst] == want.tolist()
+
+
+def test_do_move_matches_oracle():
+    for size, seed in ((19, 201), (9, 202), (5, 203)):
+        n = 3000
+        b, a, ko, pl, mv = go_oracle.random_playouts(n, size=size, seed=seed, max_ply=size * size + 40,
+                                                     stride=3, with_moves=True)
+        rng = np.random.RandomState(seed)
+        # a third of the moves are replaced by arbitrary points (occupied, suicide, ko ...) or passes
+        rnd = rng.randint(-1, size * size, size=n).astype(np.int32)
+        moves = np.where(rng.rand(n) < 0.33, rnd, mv).astype(np.int32)
+        koidx = np.flatnonzero(ko >= 0)
+        moves[koidx[::2]] = ko[koidx[::2]]                  # retake the ko: must be refused
+        wb, wa, wko, wpl, wst = go_oracle.do_move_batch(b, a, ko, pl, moves)
+        batch = BatchedGameState.from_arrays(b, a, ko, pl)
+        st = batch.do_move(torch.from_numpy(moves)).cpu().numpy()
+        gb, ga, gko, gpl = batch.to_arrays()
+        assert np.array_equal(st, wst)
+        assert (st == -1).sum() > 10 and (st == 0).sum() > n // 2
+        assert np.array_equal(gb, wb) and np.array_equal(gko, wko) and np.array_equal(gpl, wpl)
+        assert np.array_equal(ga, np.minimum(wa, 7))
+
+
+def test_device_playouts_replay_on_oracle():
+    """Positions the device playout generator records equal the oracle's replay of the very
+    moves it logged (board, saturated ages, ko, side to move)."""
+    n, max_ply, stride = 600, 400, 8
+    batch, log = BatchedGameState.random_playouts(n, seed=31, max_ply=max_ply, stride=stride, with_log=True)
+    gb, ga, gko, gpl = batch.to_arrays()
+    log = log.cpu().numpy()
+    quota = max_ply // stride + 1
+    checked = 0
+    for w in range(log.shape[0]):
+        seq = log[w]
+        slot = w * quota
+        games = np.flatnonzero(seq == -2)
+        for gi, start in enumerate(games):
+            end = games[gi + 1] if gi + 1 < len(games) else len(seq)
+            moves = seq[start + 1:end]
+            moves = moves[moves > -2]
+            played, rb, ra, rko, rpl = go_oracle.replay(19, moves, None, every=True)
+            assert played == len(moves)
+            # iteration t of a game records the position before ply t (when t matches the
+            # sampling rule and the warp still has a free slot), then plays and logs move t
+            for t in range(len(moves)):
+                if t % stride != (w + gi) % stride or slot >= min(n, (w + 1) * quota):
+                    continue
+                if t == 0:
+                    assert not gb[slot].any() and gpl[slot] == 1 and gko[slot] == -1
+                else:
+                    assert np.array_equal(gb[slot], rb[t - 1]), (w, gi, t)
+                    assert np.array_equal(ga[slot], np.minimum(ra[t - 1], 7))
+                    assert gko[slot] == rko[t - 1] and gpl[slot] == rpl[t - 1]
+                slot += 1
+                checked += 1
+        assert slot == min(n, (w + 1) * quota)
+    assert checked == n
+    stones = (gb != 0).sum(axis=(1, 2))
+    assert stones.max() > 200 and stones.min() < 10          # all game phases are covered
