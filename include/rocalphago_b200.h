@@ -69,10 +69,11 @@ int rag_unpack_states(int n, int size, const uint32_t* h_packed, int8_t* h_board
  *   0-2 board, 3 ones, 4-11 turns_since, 12-19 liberties, 20-27 capture_size,
  *   28-35 self_atari_size, 36-43 liberties_after, 44 ladder_capture,
  *   45 ladder_escape, 46 sensibleness, 47 zeros, 48 legal
- * (preprocessing.py:209-263); h_plane_src lists, for each of the F output planes,
+ * (preprocessing.py:209-263) plus 49 color (all ones iff BLACK is to move: the value
+ * network's 49th input plane, which the reference leaves undefined -- value.py:16); h_plane_src lists, for each of the F output planes,
  * which canonical plane it is, so any feature subset / order / repetition works.
  */
-#define RAG_NUM_PLANES 49
+#define RAG_NUM_PLANES 50
 #define RAG_MAX_OUT_PLANES 128
 
 #define RAG_LAYOUT_NCHW_U8   0   /* uint8  [n][F][S*S]            (game_converter.py:76's storage dtype) */
@@ -106,8 +107,8 @@ int rag_features(const uint32_t* d_states, int n, int size, const int32_t* h_pla
 /* Rows of the zero-padded pixel-row layout for n boards of size S with `pad` zero
  * columns/rows per board: pixel (x, y) of board b is row
  *     128 + b*(S+pad)*(S+pad) + x*(S+pad) + y
- * and every other row is zero.  A buffer in this layout must be zero-filled once
- * by its owner; kernels here only ever write the real-pixel rows. */
+ * and every other row is zero (the emit writes the zeros too, so the buffer needs
+ * no preparation by its owner). */
 long long rag_conv_rows(int n, int size, int pad);
 
 /* ------------------------------------------------------------------ state updates
@@ -131,6 +132,62 @@ int rag_do_move(uint32_t* d_states, int n, int size, const int32_t* d_moves, int
 int rag_random_playouts(uint32_t* d_states_out, int n_positions, int size, uint64_t seed, int max_ply,
                         int stride, int32_t* d_move_log, int log_stride, void* stream);
 int rag_playout_quota(int max_ply, int stride);
+
+/* ------------------------------------------------------------------ network forward
+ *
+ * CNNPolicy.create_network (policy.py:66-138) / value_trainer (value.py:12-28) as one object:
+ * `layers` k x k 'same' convolutions with ReLU, a 1x1 convolution to one plane, then either
+ * Flatten + Bias + softmax (policy) or Flatten + Dense(dense_units) + Dense(1, tanh) (value).
+ * Convolutions run as tcgen05 implicit GEMMs on 16-bit operands (`dtype`) with fp32
+ * accumulation; the 1x1 layer and the heads are fp32. */
+#define RAG_MAX_LAYERS 32
+#define RAG_HEAD_POLICY 0
+#define RAG_HEAD_VALUE  1
+
+typedef struct rag_net_desc {
+    int board;                       /* params["board"]                     policy.py:82  */
+    int in_planes;                   /* params["input_dim"]                 policy.py:98  */
+    int layers;                      /* params["layers"] (k x k layers; the 1x1 is implied) */
+    int filters[RAG_MAX_LAYERS];     /* filters_per_layer_K                 policy.py:112-114 */
+    int widths[RAG_MAX_LAYERS];      /* filter_width_K (odd, <= 7)          policy.py:108-110 */
+    int head;                        /* RAG_HEAD_POLICY / RAG_HEAD_VALUE    */
+    int dense_units;                 /* value head: 256                     value.py:27   */
+    int dtype;                       /* RAG_DTYPE_BF16 / RAG_DTYPE_FP16 operands */
+    int kernel_flip;                 /* 1: Theano semantics (true convolution, the reference's
+                                        pinned backend); 0: cross-correlation (TensorFlow) */
+} rag_net_desc;
+
+typedef struct rag_net rag_net;
+
+int rag_net_create(const rag_net_desc* desc, rag_net** out);
+int rag_net_destroy(rag_net* net);
+
+/* Keras model.get_weights() order and layouts: per conv layer W (out, in, kh, kw) and b (out,);
+ * the 1x1 conv's W (1, in, 1, 1) and b (1,); then policy: Bias W (S*S,)  (nn_util.py:128-133);
+ * value: Dense W (S*S, units), b (units,), Dense W (units, 1), b (1,)  (value.py:27-28).
+ * Host float arrays; copies them to the device (synchronous). */
+int rag_net_num_weight_arrays(const rag_net* net);
+int rag_net_load_weights(rag_net* net, const float* const* h_arrays, int n_arrays);
+
+size_t rag_net_workspace_bytes(const rag_net* net, int n);
+/* layout of the input the *_rows entry expects: rag_conv_rows(n, board, pad) rows of `channels` */
+long long rag_net_input_rows(const rag_net* net, int n);
+int rag_net_input_channels(const rag_net* net);
+int rag_net_input_pad(const rag_net* net);
+
+/* NeuralNetBase.forward (nn_util.py:57-58): d_nchw float [n][in_planes][S][S] ->
+ * d_out float [n][S*S] probabilities (policy) or [n] values in [-1, 1] (value). */
+int rag_net_forward(rag_net* net, const float* d_nchw, int n, float* d_out, void* d_workspace,
+                    size_t workspace_bytes, void* stream);
+/* The same from pixel rows (RAG_LAYOUT_CONV_IN with this net's dtype / pad / channels). */
+int rag_net_forward_rows(rag_net* net, const void* d_in_rows, int n, float* d_out, void* d_workspace,
+                         size_t workspace_bytes, void* stream);
+
+/* CNNPolicy.batch_eval_state's device part (policy.py:42-45) in one call: packed states ->
+ * feature planes (h_plane_src, F = in_planes) -> forward.  No host round trip in between. */
+size_t rag_eval_workspace_bytes(const rag_net* net, int n);
+int rag_eval_batch(rag_net* net, const uint32_t* d_states, int n, const int32_t* h_plane_src, int F,
+                   float* d_out, void* d_workspace, size_t workspace_bytes, void* stream);
 
 #ifdef __cplusplus
 }

@@ -19,7 +19,7 @@ _LIB_PATH = os.path.join(_HERE, "_build", "libgo_oracle.so")
 FEATURE_IDS = {
     "board": 0, "ones": 1, "turns_since": 2, "liberties": 3, "capture_size": 4,
     "self_atari_size": 5, "liberties_after": 6, "ladder_capture": 7, "ladder_escape": 8,
-    "sensibleness": 9, "zeros": 10, "legal": 11,
+    "sensibleness": 9, "zeros": 10, "legal": 11, "color": 12,
 }
 DEFAULT_FEATURES = [
     "board", "ones", "turns_since", "liberties", "capture_size", "self_atari_size",

@@ -53,18 +53,21 @@ def lib():
         "rag_playout_quota": (i32, [i32, i32]),
         "rag_net_create": (i32, [vp, vp]),
         "rag_net_destroy": (i32, [vp]),
+        "rag_net_num_weight_arrays": (i32, [vp]),
         "rag_net_load_weights": (i32, [vp, vp, i32]),
         "rag_net_workspace_bytes": (sz, [vp, i32]),
         "rag_net_input_rows": (i64, [vp, i32]),
+        "rag_net_input_channels": (i32, [vp]),
+        "rag_net_input_pad": (i32, [vp]),
         "rag_net_forward": (i32, [vp, vp, i32, vp, vp, sz, vp]),
-        "rag_net_forward_nchw": (i32, [vp, vp, i32, vp, vp, sz, vp]),
-        "rag_eval_batch": (i32, [vp, vp, i32, vp, vp, sz, vp]),
+        "rag_net_forward_rows": (i32, [vp, vp, i32, vp, vp, sz, vp]),
+        "rag_eval_workspace_bytes": (sz, [vp, i32]),
+        "rag_eval_batch": (i32, [vp, vp, i32, vp, i32, vp, vp, sz, vp]),
     }
     for name, (res, args) in sigs.items():
-        if hasattr(L, name):
-            fn = getattr(L, name)
-            fn.restype = res
-            fn.argtypes = args
+        fn = getattr(L, name)          # AttributeError here = the library is older than this binding
+        fn.restype = res
+        fn.argtypes = args
     _lib = L
     return L
 

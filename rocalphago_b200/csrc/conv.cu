@@ -1,0 +1,718 @@
+// conv.cu -- the CNNPolicy / value-network forward as tcgen05 implicit-GEMM convolutions (sm_100a).
+//
+// Replaces the Keras/Theano graph built by AlphaGo/models/policy.py:94-138 (CNNPolicy.create_network)
+// and AlphaGo/models/value.py:14-28 and run by AlphaGo/models/nn_util.py:48-58 (K.function).
+//
+// Data layout ("pixel rows"): an activation tensor is a 2-D matrix [row][channel] of 16-bit
+// values; pixel (x, y) of board b is row  128 + b*Sp*Sp + x*Sp + y  with Sp = S + pad, pad =
+// filter_width/2 of the layer that READS it, and every other row is zero.  A (dx, dy) filter
+// tap is then the same matrix shifted by dx*Sp + dy rows, so a k x k 'same' convolution is
+//       out[r, :] = act( bias + sum_taps  in[r + shift_t, :] . W_t^T )
+// -- k*k plain GEMMs that share one accumulator.  No im2col buffer exists anywhere: the TMA
+// engine fetches the shifted [128 rows x 64 channels] operand tiles straight from the
+// activation matrix, and the zero rows stand in for 'same' padding.
+//
+// Kernel (one persistent CTA per SM, 6 warps):
+//   warp 0      TMA producer: per (tap, 64-channel chunk) one A tile (shifted activations) and
+//               one B tile (that tap's weights) into a ring of 128B-swizzled smem stages
+//   warp 1      tcgen05.mma issuer (one elected lane): M=128 x N=filters x K=16 UMMAs, fp32
+//               accumulators in TMEM, double-buffered so the epilogue of tile i overlaps the
+//               MMAs of tile i+1
+//   warps 2-5   epilogue: tcgen05.ld the accumulator, + bias, ReLU, then either 16-bit pixel rows
+//               for the next layer, or (last layer) the fused 1x1 convolution: a dot product
+//               with the head's 192 weights giving one fp32 logit per point (policy.py:125-130).
+// Heads: Bias + softmax (nn_util.py:118-133, policy.py:134-136) or Dense(256) + Dense(1, tanh)
+// (value.py:27-28) as small fp32 kernels over the logits.
+#include "rag_common.h"
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+#include <vector>
+
+namespace rag {
+
+constexpr int kTileM = 128;           // rows (pixels) per accumulator tile
+constexpr int kChunkK = 64;           // channels per smem stage (= one 128-byte swizzled row)
+constexpr int kMaxTaps = 49;
+constexpr int kMaxBoardPoints = 361;
+constexpr int kTmemCols = 512;
+constexpr int kConvThreads = 192;
+constexpr int kATileBytes = kTileM * kChunkK * 2;     // 16 KiB
+
+struct ConvParams {
+    int tiles, taps, kchunks, N, stages, dtype;
+    int S, Sp_in, Sp_out, n;
+    int mode;                 // 0: write 16-bit pixel rows; 1: fused 1x1 head -> fp32 logits
+    int relu;
+    long long body_rows;      // n * Sp_in * Sp_in
+    const float* bias;        // [N]
+    const float* head_w;      // [N]   (mode 1)
+    float head_b;
+    void* out;
+    int shift[kMaxTaps];
+};
+
+// ---- PTX wrappers ----------------------------------------------------------------------------
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t"
+        "}" ::"r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_mma_f16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+        "}" ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+          "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+          "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// K-major operand tile, 128-byte rows, SWIZZLE_128B, 8-row groups 1024 B apart (cute::UMMA::SmemDescriptor)
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
+    uint64_t lo = (uint64_t)((smem_addr >> 4) & 0x3FFFu) | ((uint64_t)1 << 16);          // start, LBO (unused) = 1
+    uint64_t hi = (uint64_t)(1024 >> 4) | ((uint64_t)1 << 14) | ((uint64_t)2 << 29);     // SBO, version 1, SW128
+    return lo | (hi << 32);
+}
+
+// kind::f16 instruction descriptor (cute::UMMA::InstrDescriptor): fp32 accumulate, K-major A and B
+__device__ __forceinline__ uint32_t umma_idesc(int dtype, int N) {
+    uint32_t fmt = dtype == RAG_DTYPE_BF16 ? 1u : 0u;
+    return (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(kTileM >> 4) << 24);
+}
+
+// ---- the convolution kernel --------------------------------------------------------------------
+
+__global__ void __launch_bounds__(kConvThreads, 1)
+conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                 const ConvParams p)
+{
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw = smem_u32(smem_raw);
+    const uint32_t base = (raw + 1023u) & ~1023u;                 // SWIZZLE_128B tiles need 1024-byte alignment
+    uint8_t* smem = smem_raw + (base - raw);
+    const uint32_t stage_bytes = kATileBytes + (uint32_t)p.N * 128u;
+    uint8_t* after = smem + (size_t)p.stages * stage_bytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(after);          // full[stages], empty[stages], tfull[2], tempty[2]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * p.stages + 4);
+    float* s_bias = reinterpret_cast<float*>(tmem_slot + 4);
+    float* s_head = s_bias + p.N;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t bar0 = smem_u32(bars);
+    auto full_bar = [&](int s) { return bar0 + 8u * (uint32_t)s; };
+    auto empty_bar = [&](int s) { return bar0 + 8u * (uint32_t)(p.stages + s); };
+    auto tfull_bar = [&](int a) { return bar0 + 8u * (uint32_t)(2 * p.stages + a); };
+    auto tempty_bar = [&](int a) { return bar0 + 8u * (uint32_t)(2 * p.stages + 2 + a); };
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < p.stages; s++) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+        for (int a = 0; a < 2; a++) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 4); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(kTmemCols));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    for (int i = threadIdx.x; i < p.N; i += blockDim.x) {
+        s_bias[i] = p.bias[i];
+        s_head[i] = p.mode == 1 ? p.head_w[i] : 0.f;
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const int kblocks = p.taps * p.kchunks;
+
+    if (warp == 0) {
+        // ===== TMA producer =====
+        if (lane == 0) {
+            uint32_t it = 0;
+            for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) {
+                const int r0 = kConvLeadRows + tile * kTileM;
+                for (int t = 0; t < p.taps; t++) {
+                    for (int c = 0; c < p.kchunks; c++, it++) {
+                        const int s = (int)(it % (uint32_t)p.stages);
+                        const uint32_t ph = (it / (uint32_t)p.stages) & 1u;
+                        mbar_wait(empty_bar(s), ph ^ 1u);
+                        const uint32_t sa = base + (uint32_t)s * stage_bytes;
+                        mbar_expect_tx(full_bar(s), stage_bytes);
+                        tma_load_2d(sa, &tmA, c * kChunkK, r0 + p.shift[t], full_bar(s));
+                        tma_load_2d(sa + kATileBytes, &tmB, c * kChunkK, t * p.N, full_bar(s));
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer =====
+        if (lane == 0) {
+            const uint32_t idesc = umma_idesc(p.dtype, p.N);
+            uint32_t it = 0, lt = 0;
+            for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, lt++) {
+                const uint32_t a = lt & 1u, aph = (lt >> 1) & 1u;
+                mbar_wait(tempty_bar((int)a), aph ^ 1u);
+                tc_fence_after();
+                const uint32_t tmem_d = tmem_base + a * (uint32_t)p.N;
+                for (int kb = 0; kb < kblocks; kb++, it++) {
+                    const int s = (int)(it % (uint32_t)p.stages);
+                    const uint32_t ph = (it / (uint32_t)p.stages) & 1u;
+                    mbar_wait(full_bar(s), ph);
+                    tc_fence_after();
+                    const uint32_t sa = base + (uint32_t)s * stage_bytes;
+                    const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + kATileBytes);
+                    #pragma unroll
+                    for (int k = 0; k < kChunkK / 16; k++)        // +32 bytes along K inside the swizzled row
+                        tc_mma_f16(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((kb | k) != 0));
+                    tc_commit(empty_bar(s));                       // frees the stage once these MMAs have read it
+                }
+                tc_commit(tfull_bar((int)a));                      // accumulator complete
+            }
+        }
+    } else {
+        // ===== epilogue =====
+        const int quarter = warp & 3;                              // TMEM lanes this warp may read
+        uint32_t lt = 0;
+        for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, lt++) {
+            const uint32_t a = lt & 1u, aph = (lt >> 1) & 1u;
+            // which pixel is my row?
+            const long long rel = (long long)tile * kTileM + quarter * 32 + lane;
+            const int spp = p.Sp_in * p.Sp_in;
+            const int pos = (int)(rel / spp), rem = (int)(rel - (long long)pos * spp);
+            const int x = rem / p.Sp_in, y = rem - x * p.Sp_in;
+            const bool in_body = rel < p.body_rows;
+            const bool real = in_body && x < p.S && y < p.S;
+            mbar_wait(tfull_bar((int)a), aph);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + a * (uint32_t)p.N;
+            if (p.mode == 0) {
+                // every row of the output body is written: real pixels with data, padding with zeros
+                const bool writes = in_body && x < p.Sp_out && y < p.Sp_out;
+                uint16_t* orow = reinterpret_cast<uint16_t*>(p.out) +
+                    ((long long)kConvLeadRows + (long long)pos * p.Sp_out * p.Sp_out + x * p.Sp_out + y) * p.N;
+                for (int c0 = 0; c0 < p.N; c0 += 32) {
+                    uint32_t v[32];
+                    tc_ld32(taddr + (uint32_t)c0, v);
+                    tc_wait_ld();
+                    uint32_t packed[16];
+                    #pragma unroll
+                    for (int j = 0; j < 16; j++) {
+                        float f0 = __uint_as_float(v[2 * j]) + s_bias[c0 + 2 * j];
+                        float f1 = __uint_as_float(v[2 * j + 1]) + s_bias[c0 + 2 * j + 1];
+                        if (p.relu) { f0 = fmaxf(f0, 0.f); f1 = fmaxf(f1, 0.f); }
+                        if (!real) { f0 = 0.f; f1 = 0.f; }
+                        if (p.dtype == RAG_DTYPE_BF16) {
+                            __nv_bfloat162 h = __floats2bfloat162_rn(f0, f1);
+                            packed[j] = *reinterpret_cast<uint32_t*>(&h);
+                        } else {
+                            __half2 h = __floats2half2_rn(f0, f1);
+                            packed[j] = *reinterpret_cast<uint32_t*>(&h);
+                        }
+                    }
+                    if (writes) {
+                        uint4* dst = reinterpret_cast<uint4*>(orow + c0);
+                        #pragma unroll
+                        for (int j = 0; j < 4; j++)
+                            dst[j] = make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
+                    }
+                }
+            } else {
+                float acc = 0.f;
+                for (int c0 = 0; c0 < p.N; c0 += 32) {
+                    uint32_t v[32];
+                    tc_ld32(taddr + (uint32_t)c0, v);
+                    tc_wait_ld();
+                    #pragma unroll
+                    for (int j = 0; j < 32; j++) {
+                        float f = __uint_as_float(v[j]) + s_bias[c0 + j];
+                        if (p.relu) f = fmaxf(f, 0.f);
+                        acc = fmaf(f, s_head[c0 + j], acc);
+                    }
+                }
+                if (real) reinterpret_cast<float*>(p.out)[(long long)pos * p.S * p.S + x * p.S + y] = acc + p.head_b;
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty_bar((int)a));
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols));
+    }
+}
+
+// ---- small kernels around it ---------------------------------------------------------------------
+
+// (N, F, S, S) float -> pixel rows (what NeuralNetBase.forward is handed, nn_util.py:57-58)
+__global__ void __launch_bounds__(256)
+nchw_to_rows_kernel(const float* __restrict__ in, int n, int F, int S, int pad, int C, int dtype, uint16_t* __restrict__ out)
+{
+    const int Sp = S + pad, spp = Sp * Sp, chunks = C / 8, S2 = S * S;
+    const long long total = (long long)n * spp * chunks;
+    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+        const int ch = (int)(t % chunks);
+        const long long pix = t / chunks;
+        const int pos = (int)(pix / spp), rem = (int)(pix - (long long)pos * spp);
+        const int x = rem / Sp, y = rem - x * Sp;
+        __align__(16) uint16_t v[8];
+        #pragma unroll
+        for (int j = 0; j < 8; j++) {
+            const int f = ch * 8 + j;
+            float val = 0.f;
+            if (x < S && y < S && f < F) val = in[((long long)pos * F + f) * S2 + x * S + y];
+            if (dtype == RAG_DTYPE_BF16) { __nv_bfloat16 h = __float2bfloat16_rn(val); v[j] = *reinterpret_cast<uint16_t*>(&h); }
+            else { __half h = __float2half_rn(val); v[j] = *reinterpret_cast<uint16_t*>(&h); }
+        }
+        *reinterpret_cast<uint4*>(out + ((long long)kConvLeadRows + pix) * C + ch * 8) = *reinterpret_cast<const uint4*>(v);
+    }
+}
+
+// Flatten -> Bias -> softmax (policy.py:132-136): one warp per board
+__global__ void __launch_bounds__(128)
+softmax_head_kernel(const float* __restrict__ logits, const float* __restrict__ pos_bias, int n, int P, float* __restrict__ probs)
+{
+    const int b = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (b >= n) return;
+    const float* in = logits + (long long)b * P;
+    float v[12];
+    float mx = -INFINITY;
+    #pragma unroll
+    for (int j = 0; j < 12; j++) {
+        const int i = lane + 32 * j;
+        v[j] = i < P ? in[i] + pos_bias[i] : -INFINITY;
+        mx = fmaxf(mx, v[j]);
+    }
+    for (int o = 16; o; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    float sum = 0.f;
+    #pragma unroll
+    for (int j = 0; j < 12; j++) { v[j] = (lane + 32 * j) < P ? expf(v[j] - mx) : 0.f; sum += v[j]; }
+    for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    const float inv = 1.f / sum;
+    #pragma unroll
+    for (int j = 0; j < 12; j++) { const int i = lane + 32 * j; if (i < P) probs[(long long)b * P + i] = v[j] * inv; }
+}
+
+// Flatten -> Dense(D, linear) -> Dense(1, tanh) (value.py:26-28): one block of D threads per board
+__global__ void __launch_bounds__(256)
+value_head_kernel(const float* __restrict__ logits, const float* __restrict__ w1, const float* __restrict__ b1,
+                  const float* __restrict__ w2, const float* __restrict__ b2, int n, int P, int D, float* __restrict__ out)
+{
+    __shared__ float s_in[kMaxBoardPoints];
+    __shared__ float s_red[8];
+    const int b = blockIdx.x, j = threadIdx.x;
+    for (int i = j; i < P; i += blockDim.x) s_in[i] = logits[(long long)b * P + i];
+    __syncthreads();
+    float part = 0.f;
+    for (int jj = j; jj < D; jj += blockDim.x) {
+        float h = b1[jj];
+        for (int i = 0; i < P; i++) h = fmaf(s_in[i], w1[(long long)i * D + jj], h);     // Dense W is (in, out)
+        part = fmaf(h, w2[jj], part);
+    }
+    for (int o = 16; o; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+    if ((j & 31) == 0) s_red[j >> 5] = part;
+    __syncthreads();
+    if (j == 0) {
+        float t = b2[0];
+        for (int w = 0; w < (int)(blockDim.x >> 5); w++) t += s_red[w];
+        out[b] = tanhf(t);
+    }
+}
+
+// ---- host side --------------------------------------------------------------------------------------
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_tiled() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* sym = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = (EncodeTiledFn)sym;
+    }
+    return fn;
+}
+
+// 2-D row-major 16-bit matrix [rows][cols], box = [box_rows][64 columns], 128-byte swizzle
+static int make_map(CUtensorMap* map, const void* ptr, long long rows, int cols, int box_rows, int dtype) {
+    EncodeTiledFn enc = encode_tiled();
+    if (!enc) return fail(RAG_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
+    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)cols * 2};
+    cuuint32_t box[2] = {(cuuint32_t)kChunkK, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(map, dtype == RAG_DTYPE_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2,
+                     const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(RAG_ECUDA, "cuTensorMapEncodeTiled failed with CUresult %d (rows %lld cols %d box %d)", (int)r, rows, cols, box_rows);
+    return RAG_OK;
+}
+
+static int round_up(int v, int m) { return (v + m - 1) / m * m; }
+
+struct Layer {
+    int width, cin, cout, cin_pad, n_pad, taps;
+    uint16_t* d_w = nullptr;      // [taps][n_pad][cin_pad]
+    float* d_bias = nullptr;      // [n_pad]
+};
+
+}  // namespace rag
+
+using namespace rag;
+
+struct rag_net {
+    rag_net_desc desc;
+    int device = 0, sms = 148;
+    std::vector<Layer> layers;
+    int max_c = 0;                 // widest padded channel count of any hidden activation
+    float* d_head_w = nullptr;     // [n_pad of last layer]  1x1 conv weights
+    float head_b = 0.f;
+    float* d_pos_bias = nullptr;   // policy: Bias layer [S*S]
+    float* d_dense1_w = nullptr;   // value: [S*S][D]
+    float* d_dense1_b = nullptr;
+    float* d_dense2_w = nullptr;   // [D]
+    float* d_dense2_b = nullptr;   // [1]
+    bool loaded = false;
+};
+
+namespace rag {
+
+static size_t conv_smem_bytes(int N, int stages) {
+    return 1024 + (size_t)stages * (kATileBytes + (size_t)N * 128) + (2 * stages + 4) * 8 + 16 + 2 * (size_t)N * 4;
+}
+
+static int pick_stages(int N) {
+    for (int st = 6; st >= 2; st--)
+        if (conv_smem_bytes(N, st) <= 225 * 1024) return st;
+    return 0;
+}
+
+struct NetBuffers {
+    uint16_t* act[2];
+    float* logits;
+    uint16_t* in_rows;       // only for the NCHW entry
+    size_t act_bytes, in_bytes, total;
+};
+
+static long long max_hidden_rows(const rag_net* net, int n) {
+    long long m = 0;
+    for (size_t l = 1; l < net->layers.size(); l++) {
+        long long r = conv_rows(n, net->desc.board, net->layers[l].width / 2);
+        if (r > m) m = r;
+    }
+    return m;
+}
+
+static NetBuffers carve_net(const rag_net* net, int n, void* ws, bool with_input) {
+    NetBuffers b;
+    auto al = [](size_t v) { return (v + 1023) / 1024 * 1024; };
+    b.act_bytes = al((size_t)max_hidden_rows(net, n) * net->max_c * 2);
+    b.in_bytes = with_input ? al((size_t)conv_rows(n, net->desc.board, net->layers[0].width / 2) * net->layers[0].cin_pad * 2) : 0;
+    size_t logits_bytes = al((size_t)n * net->desc.board * net->desc.board * 4);
+    char* p = (char*)ws;
+    b.act[0] = (uint16_t*)p; p += b.act_bytes;
+    b.act[1] = (uint16_t*)p; p += b.act_bytes;
+    b.logits = (float*)p; p += logits_bytes;
+    b.in_rows = (uint16_t*)p; p += b.in_bytes;
+    b.total = 2 * b.act_bytes + logits_bytes + b.in_bytes;
+    return b;
+}
+
+// zero the rows before and after the body of a pixel-row buffer (the only rows a conv reads
+// that no kernel writes)
+static int zero_margins(uint16_t* buf, int n, int S, int pad, int C, cudaStream_t s) {
+    long long sp = S + pad, body = (long long)n * sp * sp, rows = conv_rows(n, S, pad);
+    RAG_CUDA_CHECK(cudaMemsetAsync(buf, 0, (size_t)kConvLeadRows * C * 2, s));
+    RAG_CUDA_CHECK(cudaMemsetAsync(buf + (kConvLeadRows + body) * C, 0, (size_t)(rows - kConvLeadRows - body) * C * 2, s));
+    return RAG_OK;
+}
+
+static int run_layers(rag_net* net, const uint16_t* d_in, int n, float* d_out, const NetBuffers& b, cudaStream_t s) {
+    const int S = net->desc.board, L = (int)net->layers.size();
+    const uint16_t* cur = d_in;
+    for (int l = 0; l < L; l++) {
+        const Layer& ly = net->layers[l];
+        const bool last = l == L - 1;
+        const int pad_in = ly.width / 2, Sp_in = S + pad_in;
+        const int pad_out = last ? 0 : net->layers[l + 1].width / 2, Sp_out = S + pad_out;
+        uint16_t* dst = last ? nullptr : b.act[l & 1];
+        if (!last) {
+            if (int rc = zero_margins(dst, n, S, pad_out, ly.n_pad, s)) return rc;
+            // the epilogue writes output rows (x, y) for x, y < S + pad_in only; a wider padding on
+            // the next layer (a 3x3 layer feeding a 5x5 one) leaves rows it reads unwritten
+            if (pad_out > pad_in)
+                RAG_CUDA_CHECK(cudaMemsetAsync(dst, 0, (size_t)conv_rows(n, S, pad_out) * ly.n_pad * 2, s));
+        }
+
+        ConvParams p;
+        memset(&p, 0, sizeof p);
+        p.body_rows = (long long)n * Sp_in * Sp_in;
+        p.tiles = (int)((p.body_rows + kTileM - 1) / kTileM);
+        p.taps = ly.taps; p.kchunks = ly.cin_pad / kChunkK; p.N = ly.n_pad;
+        p.stages = pick_stages(ly.n_pad); p.dtype = net->desc.dtype;
+        p.S = S; p.Sp_in = Sp_in; p.Sp_out = Sp_out; p.n = n;
+        p.mode = last ? 1 : 0; p.relu = 1;
+        p.bias = ly.d_bias; p.head_w = net->d_head_w; p.head_b = net->head_b;
+        p.out = last ? (void*)b.logits : (void*)dst;
+        for (int i = 0; i < ly.width; i++)
+            for (int j = 0; j < ly.width; j++) p.shift[i * ly.width + j] = (i - pad_in) * Sp_in + (j - pad_in);
+
+        CUtensorMap tmA, tmB;
+        if (int rc = make_map(&tmA, cur, conv_rows(n, S, pad_in), ly.cin_pad, kTileM, net->desc.dtype)) return rc;
+        if (int rc = make_map(&tmB, ly.d_w, (long long)ly.taps * ly.n_pad, ly.cin_pad, ly.n_pad, net->desc.dtype)) return rc;
+        const size_t smem = conv_smem_bytes(ly.n_pad, p.stages);
+        RAG_CUDA_CHECK(cudaFuncSetAttribute(conv_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        const int grid = p.tiles < net->sms ? p.tiles : net->sms;
+        conv_umma_kernel<<<grid, kConvThreads, smem, s>>>(tmA, tmB, p);
+        RAG_CUDA_CHECK(cudaGetLastError());
+        cur = dst;
+    }
+    const int P = S * S;
+    if (net->desc.head == RAG_HEAD_POLICY) {
+        softmax_head_kernel<<<(n + 3) / 4, 128, 0, s>>>(b.logits, net->d_pos_bias, n, P, d_out);
+    } else {
+        value_head_kernel<<<n, 256, 0, s>>>(b.logits, net->d_dense1_w, net->d_dense1_b, net->d_dense2_w, net->d_dense2_b,
+                                            n, P, net->desc.dense_units, d_out);
+    }
+    RAG_CUDA_CHECK(cudaGetLastError());
+    return RAG_OK;
+}
+
+static uint16_t to16(float f, int dtype) {
+    if (dtype == RAG_DTYPE_BF16) { __nv_bfloat16 h = __float2bfloat16_rn(f); uint16_t u; memcpy(&u, &h, 2); return u; }
+    __half h = __float2half_rn(f); uint16_t u; memcpy(&u, &h, 2); return u;
+}
+
+template <typename T>
+static int upload(T** dptr, const std::vector<T>& host) {
+    if (*dptr) { cudaFree(*dptr); *dptr = nullptr; }
+    RAG_CUDA_CHECK(cudaMalloc((void**)dptr, host.size() * sizeof(T)));
+    RAG_CUDA_CHECK(cudaMemcpy(*dptr, host.data(), host.size() * sizeof(T), cudaMemcpyHostToDevice));
+    return RAG_OK;
+}
+
+}  // namespace rag
+
+extern "C" {
+
+int rag_net_create(const rag_net_desc* desc, rag_net** out)
+{
+    if (!desc || !out) return fail(RAG_EINVAL, "null argument");
+    if (desc->board < 2 || desc->board > 19) return fail(RAG_EUNSUPPORTED, "board %d not in [2, 19]", desc->board);
+    if (desc->layers < 1 || desc->layers > RAG_MAX_LAYERS) return fail(RAG_EINVAL, "layers %d not in [1, %d]", desc->layers, RAG_MAX_LAYERS);
+    if (desc->in_planes < 1 || desc->in_planes > 128) return fail(RAG_EUNSUPPORTED, "in_planes %d not in [1, 128]", desc->in_planes);
+    if (desc->head != RAG_HEAD_POLICY && desc->head != RAG_HEAD_VALUE) return fail(RAG_EINVAL, "head %d", desc->head);
+    if (desc->dtype != RAG_DTYPE_BF16 && desc->dtype != RAG_DTYPE_FP16) return fail(RAG_EINVAL, "dtype %d", desc->dtype);
+    if (desc->head == RAG_HEAD_VALUE && (desc->dense_units < 1 || desc->dense_units > 4096)) return fail(RAG_EINVAL, "dense_units %d", desc->dense_units);
+    rag_net* net = new rag_net();
+    net->desc = *desc;
+    int cin = desc->in_planes;
+    for (int l = 0; l < desc->layers; l++) {
+        Layer ly;
+        ly.width = desc->widths[l]; ly.cin = cin; ly.cout = desc->filters[l];
+        if (ly.width < 1 || ly.width > 7 || ly.width % 2 == 0) { delete net; return fail(RAG_EUNSUPPORTED, "filter_width_%d = %d (odd, <= 7 supported)", l + 1, ly.width); }
+        if (ly.cout < 1 || ly.cout > 256) { delete net; return fail(RAG_EUNSUPPORTED, "filters_per_layer_%d = %d (<= 256 supported)", l + 1, ly.cout); }
+        ly.cin_pad = round_up(cin, kChunkK); ly.n_pad = round_up(ly.cout, kChunkK); ly.taps = ly.width * ly.width;
+        if (pick_stages(ly.n_pad) < 2) { delete net; return fail(RAG_EUNSUPPORTED, "layer %d does not fit shared memory", l + 1); }
+        if (ly.n_pad > net->max_c) net->max_c = ly.n_pad;
+        net->layers.push_back(ly);
+        cin = ly.cout;
+    }
+    if (cudaGetDevice(&net->device) != cudaSuccess ||
+        cudaDeviceGetAttribute(&net->sms, cudaDevAttrMultiProcessorCount, net->device) != cudaSuccess) {
+        delete net; return fail(RAG_ECUDA, "no CUDA device");
+    }
+    int major = 0;
+    cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, net->device);
+    if (major != 10) { delete net; return fail(RAG_EUNSUPPORTED, "needs an sm_100a device (compute capability %d.x found)", major); }
+    *out = net;
+    return RAG_OK;
+}
+
+int rag_net_destroy(rag_net* net)
+{
+    if (!net) return RAG_OK;
+    for (auto& ly : net->layers) { cudaFree(ly.d_w); cudaFree(ly.d_bias); }
+    cudaFree(net->d_head_w); cudaFree(net->d_pos_bias);
+    cudaFree(net->d_dense1_w); cudaFree(net->d_dense1_b); cudaFree(net->d_dense2_w); cudaFree(net->d_dense2_b);
+    delete net;
+    return RAG_OK;
+}
+
+int rag_net_num_weight_arrays(const rag_net* net)
+{
+    if (!net) return 0;
+    return 2 * (int)net->layers.size() + 2 + (net->desc.head == RAG_HEAD_POLICY ? 1 : 4);
+}
+
+int rag_net_load_weights(rag_net* net, const float* const* h_arrays, int n_arrays)
+{
+    if (!net || !h_arrays) return fail(RAG_EINVAL, "null argument");
+    if (n_arrays != rag_net_num_weight_arrays(net)) return fail(RAG_EINVAL, "expected %d weight arrays, got %d", rag_net_num_weight_arrays(net), n_arrays);
+    for (int i = 0; i < n_arrays; i++) if (!h_arrays[i]) return fail(RAG_EINVAL, "weight array %d is null", i);
+    RAG_CUDA_CHECK(cudaSetDevice(net->device));
+    const int dtype = net->desc.dtype, L = (int)net->layers.size(), P = net->desc.board * net->desc.board;
+    int ai = 0;
+    for (int l = 0; l < L; l++) {
+        Layer& ly = net->layers[l];
+        const float* W = h_arrays[ai++];      // (cout, cin, kh, kw)  Keras 'th' kernel layout
+        const float* bsrc = h_arrays[ai++];   // (cout,)
+        const int k = ly.width;
+        std::vector<uint16_t> w((size_t)ly.taps * ly.n_pad * ly.cin_pad, 0);
+        for (int i = 0; i < k; i++)
+            for (int j = 0; j < k; j++) {
+                // tap (i, j) reads in[x + i - pad, y + j - pad].  Theano's conv2d is a true
+                // convolution, i.e. a correlation with the kernel rotated by 180 degrees.
+                const int si = net->desc.kernel_flip ? k - 1 - i : i, sj = net->desc.kernel_flip ? k - 1 - j : j;
+                for (int co = 0; co < ly.cout; co++)
+                    for (int ci = 0; ci < ly.cin; ci++)
+                        w[((size_t)(i * k + j) * ly.n_pad + co) * ly.cin_pad + ci] =
+                            to16(W[(((size_t)co * ly.cin + ci) * k + si) * k + sj], dtype);
+            }
+        std::vector<float> bias(ly.n_pad, 0.f);
+        for (int co = 0; co < ly.cout; co++) bias[co] = bsrc[co];
+        if (int rc = upload(&ly.d_w, w)) return rc;
+        if (int rc = upload(&ly.d_bias, bias)) return rc;
+    }
+    {   // the 1x1 convolution to one plane (policy.py:125-130, value.py:23-25): W (1, cin, 1, 1), b (1,)
+        const Layer& ly = net->layers[L - 1];
+        const float* W = h_arrays[ai++];
+        const float* bsrc = h_arrays[ai++];
+        std::vector<float> hw(ly.n_pad, 0.f);
+        for (int c = 0; c < ly.cout; c++) hw[c] = W[c];
+        if (int rc = upload(&net->d_head_w, hw)) return rc;
+        net->head_b = bsrc[0];
+    }
+    if (net->desc.head == RAG_HEAD_POLICY) {
+        std::vector<float> pb(h_arrays[ai], h_arrays[ai] + P); ai++;
+        if (int rc = upload(&net->d_pos_bias, pb)) return rc;
+    } else {
+        const int D = net->desc.dense_units;
+        std::vector<float> w1(h_arrays[ai], h_arrays[ai] + (size_t)P * D); ai++;
+        std::vector<float> b1(h_arrays[ai], h_arrays[ai] + D); ai++;
+        std::vector<float> w2(h_arrays[ai], h_arrays[ai] + D); ai++;
+        std::vector<float> b2(h_arrays[ai], h_arrays[ai] + 1); ai++;
+        if (int rc = upload(&net->d_dense1_w, w1)) return rc;
+        if (int rc = upload(&net->d_dense1_b, b1)) return rc;
+        if (int rc = upload(&net->d_dense2_w, w2)) return rc;
+        if (int rc = upload(&net->d_dense2_b, b2)) return rc;
+    }
+    net->loaded = true;
+    return RAG_OK;
+}
+
+size_t rag_net_workspace_bytes(const rag_net* net, int n)
+{
+    if (!net || n <= 0) return 0;
+    return carve_net(net, n, nullptr, true).total;
+}
+
+long long rag_net_input_rows(const rag_net* net, int n) { return net ? conv_rows(n, net->desc.board, net->layers[0].width / 2) : 0; }
+int rag_net_input_channels(const rag_net* net) { return net ? net->layers[0].cin_pad : 0; }
+int rag_net_input_pad(const rag_net* net) { return net ? net->layers[0].width / 2 : 0; }
+
+static int net_ready(const rag_net* net, int n, const void* in, const void* out, const void* ws, size_t bytes) {
+    if (!net) return fail(RAG_EINVAL, "null net");
+    if (!net->loaded) return fail(RAG_EINVAL, "rag_net_load_weights has not been called");
+    if (n < 0 || (n > 0 && (!in || !out || !ws))) return fail(RAG_EINVAL, "null argument");
+    if (n > 0 && bytes < rag_net_workspace_bytes(net, n)) return fail(RAG_ENOMEM, "workspace has %zu bytes, %zu needed for n = %d", bytes, rag_net_workspace_bytes(net, n), n);
+    return RAG_OK;
+}
+
+int rag_net_forward_rows(rag_net* net, const void* d_in_rows, int n, float* d_out, void* d_workspace, size_t workspace_bytes, void* stream)
+{
+    if (int rc = net_ready(net, n, d_in_rows, d_out, d_workspace, workspace_bytes)) return rc;
+    if (n == 0) return RAG_OK;
+    NetBuffers b = carve_net(net, n, d_workspace, true);
+    return run_layers(net, (const uint16_t*)d_in_rows, n, d_out, b, (cudaStream_t)stream);
+}
+
+int rag_net_forward(rag_net* net, const float* d_nchw, int n, float* d_out, void* d_workspace, size_t workspace_bytes, void* stream)
+{
+    if (int rc = net_ready(net, n, d_nchw, d_out, d_workspace, workspace_bytes)) return rc;
+    if (n == 0) return RAG_OK;
+    cudaStream_t s = (cudaStream_t)stream;
+    NetBuffers b = carve_net(net, n, d_workspace, true);
+    const Layer& l0 = net->layers[0];
+    const int S = net->desc.board, pad = l0.width / 2;
+    if (int rc = zero_margins(b.in_rows, n, S, pad, l0.cin_pad, s)) return rc;
+    long long threads = (long long)n * (S + pad) * (S + pad) * (l0.cin_pad / 8);
+    nchw_to_rows_kernel<<<(int)((threads + 255) / 256), 256, 0, s>>>(d_nchw, n, net->desc.in_planes, S, pad, l0.cin_pad, net->desc.dtype, b.in_rows);
+    RAG_CUDA_CHECK(cudaGetLastError());
+    return run_layers(net, b.in_rows, n, d_out, b, s);
+}
+
+
+size_t rag_eval_workspace_bytes(const rag_net* net, int n)
+{
+    if (!net || n <= 0) return 0;
+    size_t f = (rag_features_workspace_bytes(n) + 1023) / 1024 * 1024;
+    return f + rag_net_workspace_bytes(net, n);
+}
+
+int rag_eval_batch(rag_net* net, const uint32_t* d_states, int n, const int32_t* h_plane_src, int F, float* d_out,
+                   void* d_workspace, size_t workspace_bytes, void* stream)
+{
+    if (!net) return fail(RAG_EINVAL, "null net");
+    if (F != net->desc.in_planes) return fail(RAG_EINVAL, "network takes %d planes, %d listed", net->desc.in_planes, F);
+    if (n > 0 && workspace_bytes < rag_eval_workspace_bytes(net, n))
+        return fail(RAG_ENOMEM, "workspace has %zu bytes, %zu needed for n = %d", workspace_bytes, rag_eval_workspace_bytes(net, n), n);
+    if (int rc = net_ready(net, n, d_states, d_out, d_workspace, (size_t)-1)) return rc;
+    if (n == 0) return RAG_OK;
+    const size_t fbytes = (rag_features_workspace_bytes(n) + 1023) / 1024 * 1024;
+    char* ws = (char*)d_workspace;
+    NetBuffers b = carve_net(net, n, ws + fbytes, true);
+    const Layer& l0 = net->layers[0];
+    if (int rc = rag_features(d_states, n, net->desc.board, h_plane_src, F, RAG_LAYOUT_CONV_IN, net->desc.dtype,
+                              l0.width / 2, l0.cin_pad, b.in_rows, ws, fbytes, stream)) return rc;
+    return run_layers(net, b.in_rows, n, d_out, b, (cudaStream_t)stream);
+}
+
+}  // extern "C"

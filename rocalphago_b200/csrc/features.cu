@@ -90,6 +90,7 @@ analyze_kernel(const uint32_t* __restrict__ states, int n, int S, int with_ladde
     const BB own = s.player > 0 ? s.black : s.white;
     const BB opp = s.player > 0 ? s.white : s.black;
     const Analysis A = bb_features(g, own, opp, s.age0, s.age1, s.age2, p_to_q(s.ko_p, S), planes, sm_eye[warp]);
+    if (s.player > 0) plane_or(planes, kPlaneColor, bb_board(g), g);
     __syncwarp();
 
     uint32_t* out = ws.planes + (size_t)pos * kPlaneWords;
@@ -183,32 +184,32 @@ emit_nchw_kernel(const uint32_t* __restrict__ planes, long long total, int S, Pl
     }
 }
 
-// Conv input: 16-bit rows of C channels, row = lead + pos*Sp*Sp + x*Sp + y; only real pixels are
-// written (pad rows are zero from allocation and stay zero).  One thread = one 16-byte chunk
-// (8 channels) of one pixel; 8 (C=64) or 16 (C=128) consecutive threads share a pixel.
+// Conv input ("pixel rows", see conv.cu): 16-bit rows of C channels, row = lead + pos*Sp*Sp +
+// x*Sp + y with Sp = S + pad.  Every row of the body is written -- real pixels with the planes
+// as 1.0/0.0, padding pixels with zeros.  One thread = one 16-byte chunk (8 channels) of a row.
 __global__ void __launch_bounds__(256)
 emit_conv_kernel(const uint32_t* __restrict__ planes, int n, int S, int pad, int C, PlaneMap map,
                  uint16_t one, uint16_t* __restrict__ out)
 {
-    const int S2 = S * S, Sp = S + pad, chunks = C / 8;
-    const long long total = (long long)n * S2 * chunks;
+    const int Sp = S + pad, spp = Sp * Sp, chunks = C / 8;
+    const long long total = (long long)n * spp * chunks;
     for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total;
          t += (long long)gridDim.x * blockDim.x) {
         int ch = (int)(t % chunks);
         long long pix = t / chunks;
-        int pos = (int)(pix / S2), p = (int)(pix - (long long)pos * S2);
-        int x = p / S, y = p - x * S;
+        int pos = (int)(pix / spp), rem = (int)(pix - (long long)pos * spp);
+        int x = rem / Sp, y = rem - x * Sp;
         const uint32_t* pl = planes + (size_t)pos * kPlaneWords;
         __align__(16) uint16_t v[8];
+        const bool real = x < S && y < S;
         #pragma unroll
         for (int j = 0; j < 8; j++) {
             int f = ch * 8 + j;
             uint32_t bit = 0;
-            if (f < map.F) bit = (__ldg(pl + map.src[f] * 32 + x) >> y) & 1u;
+            if (real && f < map.F) bit = (__ldg(pl + map.src[f] * 32 + x) >> y) & 1u;
             v[j] = bit ? one : (uint16_t)0;
         }
-        long long row = kConvLeadRows + (long long)pos * Sp * Sp + x * Sp + y;
-        *reinterpret_cast<uint4*>(out + row * C + ch * 8) = *reinterpret_cast<const uint4*>(v);
+        *reinterpret_cast<uint4*>(out + ((long long)kConvLeadRows + pix) * C + ch * 8) = *reinterpret_cast<const uint4*>(v);
     }
 }
 
@@ -419,7 +420,13 @@ int rag_features_emit(const void* d_workspace, int n, int size, const int32_t* h
         if (F > conv_channels) return fail(RAG_EINVAL, "%d planes do not fit %d channels", F, conv_channels);
         if (conv_pad < 0 || conv_pad > 3) return fail(RAG_EINVAL, "conv_pad %d", conv_pad);
         uint16_t one = conv_dtype == RAG_DTYPE_FP16 ? (uint16_t)0x3C00 : (uint16_t)0x3F80;
-        long long threads = (long long)n * size * size * (conv_channels / 8);
+        const long long sp = size + conv_pad, body = (long long)n * sp * sp, rows = conv_rows(n, size, conv_pad);
+        uint16_t* o = (uint16_t*)d_out;
+        // the margins are the only rows a convolution reads that the kernel does not write
+        RAG_CUDA_CHECK(cudaMemsetAsync(o, 0, (size_t)kConvLeadRows * conv_channels * 2, s));
+        RAG_CUDA_CHECK(cudaMemsetAsync(o + (kConvLeadRows + body) * conv_channels, 0,
+                                       (size_t)(rows - kConvLeadRows - body) * conv_channels * 2, s));
+        long long threads = body * (conv_channels / 8);
         int blocks = (int)((threads + 255) / 256);
         emit_conv_kernel<<<blocks, 256, 0, s>>>(planes, n, size, conv_pad, conv_channels, map, one, (uint16_t*)d_out);
     } else {

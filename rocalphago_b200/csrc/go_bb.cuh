@@ -42,7 +42,9 @@ enum Plane {
     kPlaneBoard = 0, kPlaneOnes = 3, kPlaneTurnsSince = 4, kPlaneLiberties = 12,
     kPlaneCaptureSize = 20, kPlaneSelfAtari = 28, kPlaneLibertiesAfter = 36,
     kPlaneLadderCapture = 44, kPlaneLadderEscape = 45, kPlaneSensibleness = 46,
-    kPlaneZeros = 47, kPlaneLegal = 48, kNumPlanes = 49
+    kPlaneZeros = 47, kPlaneLegal = 48,
+    kPlaneColor = 49,      // not a reference feature: all ones iff BLACK is to move (value net's 49th plane)
+    kNumPlanes = 50
 };
 
 // ------------------------------------------------------------------ BB: a board-sized bit set

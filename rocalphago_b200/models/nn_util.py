@@ -1,0 +1,304 @@
+"""NeuralNetBase and friends on the B200 path (drop-in for AlphaGo/models/nn_util.py).
+
+`NeuralNetBase(feature_list, **kwargs)` keeps the reference's surface -- `.preprocessor`,
+`.model`, `.forward(ndarray)`, `load_model` / `save_model`, the `@neuralnet` registry and a
+`Bias` name -- but `.model` is a `Network` (layer list + weights + a handle on the CUDA
+forward), not a Keras object: training is out of scope.
+"""
+import ctypes
+import json
+
+import numpy as np
+import torch
+
+from .. import _cabi
+from ..preprocessing import Preprocess, DTYPE_BF16, DTYPE_FP16
+from ..state import _ptr, _stream, _require_cuda
+
+HEAD_POLICY, HEAD_VALUE = 0, 1
+MAX_LAYERS = 32
+
+
+class _NetDesc(ctypes.Structure):
+    _fields_ = [("board", ctypes.c_int), ("in_planes", ctypes.c_int), ("layers", ctypes.c_int),
+                ("filters", ctypes.c_int * MAX_LAYERS), ("widths", ctypes.c_int * MAX_LAYERS),
+                ("head", ctypes.c_int), ("dense_units", ctypes.c_int), ("dtype", ctypes.c_int),
+                ("kernel_flip", ctypes.c_int)]
+
+
+class Bias(object):
+    """Name kept for `custom_objects={'Bias': Bias}` call sites (nn_util.py:118-133).  On this
+    path the per-location bias is the last array of a policy Network's weights."""
+
+
+class Network(object):
+    """What sits behind `.model`: the layer stack of policy.py:94-138 / value.py:14-28.
+
+    specs: list of (filters, filter_width) for the k x k ReLU layers; a 1x1 convolution to one
+    plane follows, then Flatten + Bias + softmax (head='policy') or Flatten + Dense(dense_units)
+    + Dense(1, tanh) (head='value').  Weights are kept as numpy arrays in Keras'
+    get_weights() order and 'th' layouts, so Keras-trained arrays drop in with set_weights().
+    """
+
+    def __init__(self, board, input_dim, specs, head="policy", dense_units=256, dtype="bf16",
+                 kernel_flip=True, seed=None):
+        self.board, self.input_dim = int(board), int(input_dim)
+        self.specs = [(int(f), int(w)) for f, w in specs]
+        self.head, self.dense_units = head, int(dense_units)
+        self.dtype, self.kernel_flip = dtype, bool(kernel_flip)
+        self.input_shape = (None, self.input_dim, self.board, self.board)      # read by trainers
+        self.output_shape = (None, self.board * self.board) if head == "policy" else (None, 1)
+        self._weights = self._init_uniform(seed)
+        self._handle = None
+        self._handle_device = None
+        self._dirty = True
+        self._ws = None
+        self.uses_learning_phase = False
+
+    # -- weights ---------------------------------------------------------------------------
+    def _shapes(self):
+        shapes, cin = [], self.input_dim
+        for nb, k in self.specs:
+            shapes += [(nb, cin, k, k), (nb,)]
+            cin = nb
+        shapes += [(1, cin, 1, 1), (1,)]
+        P = self.board * self.board
+        if self.head == "policy":
+            shapes += [(P,)]
+        else:
+            shapes += [(P, self.dense_units), (self.dense_units,), (self.dense_units, 1), (1,)]
+        return shapes
+
+    def _init_uniform(self, seed):
+        """init='uniform' (Keras 1.2.0: U(-0.05, 0.05)); biases and Bias start at zero."""
+        rng = np.random.RandomState(seed)
+        return [rng.uniform(-0.05, 0.05, size=s).astype(np.float32) if len(s) > 1 else np.zeros(s, np.float32)
+                for s in self._shapes()]
+
+    def get_weights(self):
+        return [w.copy() for w in self._weights]
+
+    def set_weights(self, weights):
+        shapes = self._shapes()
+        if len(weights) != len(shapes):
+            raise ValueError("expected %d weight arrays, got %d" % (len(shapes), len(weights)))
+        new = []
+        for w, s in zip(weights, shapes):
+            w = np.ascontiguousarray(w, dtype=np.float32)
+            if tuple(w.shape) != tuple(s):
+                raise ValueError("weight shape %s does not match %s" % (w.shape, s))
+            new.append(w)
+        self._weights = new
+        self._dirty = True
+
+    def save_weights(self, path, overwrite=True):
+        """.npz twin of Keras' HDF5 weight file (no HDF5 library on this image)."""
+        with open(path, "wb") as f:
+            np.savez(f, **{"w%03d" % i: w for i, w in enumerate(self._weights)})
+
+    def load_weights(self, path):
+        z = np.load(path)
+        self.set_weights([z["w%03d" % i] for i in range(len(z.files))])
+
+    # -- (de)serialisation in Keras-1 Sequential JSON -------------------------------------------
+    def to_json(self):
+        layers = []
+        for i, (nb, k) in enumerate(self.specs):
+            cfg = {"name": "convolution2d_%d" % (i + 1), "nb_filter": nb, "nb_row": k, "nb_col": k,
+                   "init": "uniform", "activation": "relu", "border_mode": "same", "dim_ordering": "th",
+                   "subsample": [1, 1], "bias": True}
+            if i == 0:
+                cfg["batch_input_shape"] = [None, self.input_dim, self.board, self.board]
+            layers.append({"class_name": "Convolution2D", "config": cfg})
+        layers.append({"class_name": "Convolution2D", "config": {
+            "name": "convolution2d_%d" % (len(self.specs) + 1), "nb_filter": 1, "nb_row": 1, "nb_col": 1,
+            "init": "uniform", "activation": "linear", "border_mode": "same", "dim_ordering": "th",
+            "subsample": [1, 1], "bias": True}})
+        layers.append({"class_name": "Flatten", "config": {"name": "flatten_1"}})
+        if self.head == "policy":
+            layers.append({"class_name": "Bias", "config": {"name": "bias_1"}})
+            layers.append({"class_name": "Activation", "config": {"activation": "softmax", "name": "activation_1"}})
+        else:
+            layers.append({"class_name": "Dense", "config": {"name": "dense_1", "output_dim": self.dense_units,
+                                                             "init": "uniform", "activation": "linear"}})
+            layers.append({"class_name": "Dense", "config": {"name": "dense_2", "output_dim": 1,
+                                                             "init": "uniform", "activation": "tanh"}})
+        return json.dumps({"class_name": "Sequential", "keras_version": "1.2.0", "config": layers,
+                           "rocalphago_b200": {"dtype": self.dtype, "kernel_flip": self.kernel_flip}})
+
+    @staticmethod
+    def from_json(text):
+        """Reads the Sequential JSON Keras 1.x writes for these architectures
+        (e.g. the reference's tests/test_data/minimodel.json)."""
+        km = json.loads(text)
+        if km.get("class_name") != "Sequential":
+            raise ValueError("only Sequential models are supported on this path (got %s)" % km.get("class_name"))
+        convs, head, dense, board, input_dim = [], None, [], None, None
+        for layer in km["config"]:
+            name, cfg = layer["class_name"], layer["config"]
+            if name == "Convolution2D":
+                if cfg.get("border_mode", "same") != "same" or tuple(cfg.get("subsample", (1, 1))) != (1, 1):
+                    raise ValueError("only stride-1 'same' convolutions are supported")
+                if cfg["nb_row"] != cfg["nb_col"]:
+                    raise ValueError("only square filters are supported")
+                if "batch_input_shape" in cfg:
+                    _, input_dim, board, _ = cfg["batch_input_shape"]
+                convs.append((cfg["nb_filter"], cfg["nb_row"], cfg.get("activation", "linear")))
+            elif name == "Dense":
+                dense.append((cfg["output_dim"], cfg.get("activation", "linear")))
+            elif name == "Activation" and cfg.get("activation") == "softmax":
+                head = "policy"
+            elif name in ("Flatten", "Bias"):
+                pass
+            else:
+                raise ValueError("layer %s is not supported on this path" % name)
+        if not convs or convs[-1][:2] != (1, 1) or convs[-1][2] != "linear":
+            raise ValueError("expected the stack to end in a linear 1x1 convolution to one plane")
+        if any(a != "relu" for _, _, a in convs[:-1]):
+            raise ValueError("hidden convolutions must use relu")
+        if head is None:
+            if len(dense) != 2 or dense[1] != (1, "tanh") or dense[0][1] != "linear":
+                raise ValueError("expected Dense(n, linear) + Dense(1, tanh) as the value head")
+            head = "value"
+        extra = km.get("rocalphago_b200", {})
+        return Network(board, input_dim, [(f, w) for f, w, _ in convs[:-1]], head=head,
+                       dense_units=dense[0][0] if dense else 256, dtype=extra.get("dtype", "bf16"),
+                       kernel_flip=extra.get("kernel_flip", True))
+
+    # -- the CUDA forward ---------------------------------------------------------------------
+    def _ensure_handle(self, device):
+        L = _cabi.lib()
+        if self._handle is not None and self._handle_device != device:
+            L.rag_net_destroy(self._handle)
+            self._handle = None
+        if self._handle is None:
+            if len(self.specs) > MAX_LAYERS:
+                raise ValueError("at most %d layers are supported" % MAX_LAYERS)
+            d = _NetDesc()
+            d.board, d.in_planes, d.layers = self.board, self.input_dim, len(self.specs)
+            for i, (nb, k) in enumerate(self.specs):
+                d.filters[i], d.widths[i] = nb, k
+            d.head = HEAD_POLICY if self.head == "policy" else HEAD_VALUE
+            d.dense_units = self.dense_units
+            d.dtype = DTYPE_BF16 if self.dtype == "bf16" else DTYPE_FP16
+            d.kernel_flip = int(self.kernel_flip)
+            h = ctypes.c_void_p()
+            with torch.cuda.device(device):
+                _cabi.check(L.rag_net_create(ctypes.byref(d), ctypes.byref(h)))
+            self._handle, self._handle_device, self._dirty = h, device, True
+        if self._dirty:
+            arr = (ctypes.c_void_p * len(self._weights))(*[w.ctypes.data_as(ctypes.c_void_p).value for w in self._weights])
+            with torch.cuda.device(device):
+                _cabi.check(L.rag_net_load_weights(self._handle, arr, len(self._weights)))
+            self._dirty = False
+        return self._handle
+
+    def _workspace(self, nbytes, device):
+        if self._ws is None or self._ws.numel() < nbytes or self._ws.device != device:
+            self._ws = torch.empty(int(nbytes), dtype=torch.uint8, device=device)
+        return self._ws
+
+    def _out(self, n, device):
+        return torch.empty((n, self.board * self.board) if self.head == "policy" else (n,),
+                           dtype=torch.float32, device=device)
+
+    def forward_device(self, x):
+        """x: CUDA float32 (N, F, S, S) -> CUDA float32 (N, S*S) or (N,)."""
+        _require_cuda()
+        n = int(x.shape[0])
+        if tuple(x.shape[1:]) != (self.input_dim, self.board, self.board):
+            raise ValueError("input shape %s does not match %s" % (tuple(x.shape), self.input_shape))
+        x = x.contiguous()
+        h = self._ensure_handle(x.device)
+        out = self._out(n, x.device)
+        if n == 0:
+            return out
+        L = _cabi.lib()
+        ws = self._workspace(L.rag_net_workspace_bytes(h, n), x.device)
+        with torch.cuda.device(x.device):
+            _cabi.check(L.rag_net_forward(h, _ptr(x), n, _ptr(out), _ptr(ws), ws.numel(), _stream()))
+        return out
+
+    def eval_batch_device(self, batch, plane_src):
+        """Packed states -> features -> forward without leaving the device (rag_eval_batch)."""
+        _require_cuda()
+        n = len(batch)
+        h = self._ensure_handle(batch.device)
+        out = self._out(n, batch.device)
+        if n == 0:
+            return out
+        L = _cabi.lib()
+        ws = self._workspace(L.rag_eval_workspace_bytes(h, n), batch.device)
+        src = np.ascontiguousarray(plane_src, np.int32)
+        with torch.cuda.device(batch.device):
+            _cabi.check(L.rag_eval_batch(h, _ptr(batch.packed), n, src.ctypes.data_as(ctypes.c_void_p), len(src),
+                                         _ptr(out), _ptr(ws), ws.numel(), _stream()))
+        return out
+
+    def features_workspace(self):
+        """The analysis workspace of the last eval_batch_device call (planes 46/48 give the move lists)."""
+        return self._ws
+
+    def __del__(self):
+        try:
+            if self._handle is not None:
+                _cabi.lib().rag_net_destroy(self._handle)
+        except Exception:  # noqa: BLE001
+            pass
+
+
+class NeuralNetBase(object):
+    """Base class for neural network classes handling feature processing, construction
+    of a 'forward' function, etc. (nn_util.py:8-108)"""
+
+    subclasses = {}
+
+    def __init__(self, feature_list, **kwargs):
+        self.preprocessor = Preprocess(feature_list)
+        kwargs["input_dim"] = self.preprocessor.output_dim
+        if kwargs.get("init_network", True):
+            self.model = self.__class__.create_network(**kwargs)
+            self.forward = self._model_forward()
+
+    def _model_forward(self):
+        """forward(ndarray (N,F,S,S)) -> ndarray float32, as nn_util.py:34-58's K.function closure."""
+        def forward(inpt):
+            _require_cuda()
+            x = torch.as_tensor(np.ascontiguousarray(inpt, dtype=np.float32)).cuda(non_blocking=True)
+            return self.model.forward_device(x).cpu().numpy().reshape((x.shape[0],) + self.model.output_shape[1:])
+        return forward
+
+    @staticmethod
+    def load_model(json_file):
+        with open(json_file, "r") as f:
+            object_specs = json.load(f)
+        class_name = object_specs.get("class", "CNNPolicy")
+        try:
+            network_class = NeuralNetBase.subclasses[class_name]
+        except KeyError:
+            raise ValueError("Unknown neural network type in json file: {}\n"
+                             "(was it registered with the @neuralnet decorator?)".format(class_name))
+        new_net = network_class(object_specs["feature_list"], init_network=False)
+        new_net.model = Network.from_json(object_specs["keras_model"])
+        if "weights_file" in object_specs:
+            new_net.model.load_weights(object_specs["weights_file"])
+        new_net.forward = new_net._model_forward()
+        return new_net
+
+    def save_model(self, json_file, weights_file=None):
+        object_specs = {
+            "class": self.__class__.__name__,
+            "keras_model": self.model.to_json(),
+            "feature_list": self.preprocessor.feature_list,
+        }
+        if weights_file is not None:
+            self.model.save_weights(weights_file)
+            object_specs["weights_file"] = weights_file
+        with open(json_file, "w") as f:
+            json.dump(object_specs, f)
+
+
+def neuralnet(cls):
+    """Class decorator for registering subclasses of NeuralNetBase (nn_util.py:111-115)"""
+    NeuralNetBase.subclasses[cls.__name__] = cls
+    return cls

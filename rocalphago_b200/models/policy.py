@@ -1,0 +1,95 @@
+"""CNNPolicy on the B200 path (drop-in for AlphaGo/models/policy.py:9-138)."""
+import numpy as np
+
+from ..state import BatchedGameState
+from .nn_util import NeuralNetBase, Network, neuralnet
+
+
+def flatten_idx(position, size):
+    (x, y) = position
+    return x * size + y            # AlphaGo/util.py:11-13
+
+
+@neuralnet
+class CNNPolicy(NeuralNetBase):
+    """uses a convolutional neural network to evaluate the state of the game
+    and compute a probability distribution over the next action"""
+
+    def _select_moves_and_normalize(self, nn_output, moves, size):
+        """normalize a distribution over the given list of moves and return a list of
+        (move, prob) tuples (policy.py:15-25; a list, as Python 2's zip gave)"""
+        if len(moves) == 0:
+            return []
+        move_indices = [flatten_idx(m, size) for m in moves]
+        distribution = nn_output[move_indices]
+        distribution = distribution / distribution.sum()
+        return list(zip(moves, distribution))
+
+    def batch_eval_state(self, states, moves_lists=None):
+        """Given a list of states (or a BatchedGameState), evaluates them all at once.
+        Returns a parallel list of move distributions as in eval_state (policy.py:27-52).
+
+        States are packed once, then features, convolutions and softmax run on the device with
+        no host round trip (rag_eval_batch); the default move lists -- get_legal_moves() order,
+        non-eyes then own eyes (go.py:465-480) -- come from the same analysis."""
+        n_states = len(states)
+        if n_states == 0:
+            return []
+        if isinstance(states, BatchedGameState):
+            batch, state_size = states, states.size
+        else:
+            state_size = states[0].size
+            if not all([st.size == state_size for st in states]):
+                raise ValueError("all states must have the same size")
+            batch = BatchedGameState.from_states(states)
+        probs = self.model.eval_batch_device(batch, self.preprocessor.plane_src)
+        if not moves_lists:
+            moves_lists = self.preprocessor.legal_move_lists(self.model.features_workspace(), n_states, state_size)
+        network_output = probs.cpu().numpy()
+        results = [None] * n_states
+        for i in range(n_states):
+            results[i] = self._select_moves_and_normalize(network_output[i], moves_lists[i], state_size)
+        return results
+
+    def eval_state(self, state, moves=None):
+        """Given a GameState object, returns a list of (action, probability) pairs
+        according to the network outputs (policy.py:54-64)"""
+        return self.batch_eval_state([state], [moves] if moves else None)[0]
+
+    @staticmethod
+    def create_network(**kwargs):
+        """construct a convolutional neural network (policy.py:66-138).
+
+        Keyword Arguments (same names as the reference):
+        - input_dim, board (19), filters_per_layer (128), filters_per_layer_K, layers (12),
+          filter_width_K (3; first layer 5)
+        and, for this implementation: dtype ('bf16' | 'fp16' operands of the convolutions),
+        kernel_flip (True = Theano convolution semantics), seed (None = fresh random weights).
+        """
+        defaults = {
+            "board": 19,
+            "filters_per_layer": 128,
+            "layers": 12,
+            "filter_width_1": 5
+        }
+        params = defaults
+        params.update(kwargs)
+        specs = []
+        for i in range(1, params["layers"] + 1):
+            width = params.get("filter_width_%d" % i, 3)
+            nb = params.get("filters_per_layer_%d" % i, params["filters_per_layer"])
+            specs.append((nb, width))
+        return Network(params["board"], params["input_dim"], specs, head="policy",
+                       dtype=params.get("dtype", "bf16"), kernel_flip=params.get("kernel_flip", True),
+                       seed=params.get("seed"))
+
+
+def _smoke(batch, board, age, ko, player):
+    """Used by __graft_entry__.smoke(): a 3-layer policy on the smoke batch vs the CPU oracle."""
+    from oracle import cnn_oracle, go_oracle
+    net = CNNPolicy(go_oracle.DEFAULT_FEATURES, layers=3, filters_per_layer=32, seed=5)
+    probs = net.model.eval_batch_device(batch, net.preprocessor.plane_src).cpu().numpy()
+    planes = go_oracle.features(board, age, ko, player, go_oracle.DEFAULT_FEATURES)
+    want = cnn_oracle.forward(net.model.get_weights(), planes, net.model.specs)
+    err = float(np.abs(probs - want).max())
+    assert err < 2e-3, "policy probabilities differ from the oracle by %g" % err

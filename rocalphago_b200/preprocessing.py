@@ -26,6 +26,9 @@ FEATURES = {
     "sensibleness": {"size": 1, "plane": 46},
     "zeros": {"size": 1, "plane": 47},
     "legal": {"size": 1, "plane": 48},
+    # not in the reference: value.py:16 takes 49 planes but preprocessing.py defines no 49th.
+    # Here it is the player-colour plane of the AlphaGo paper: all ones iff BLACK is to move.
+    "color": {"size": 1, "plane": 49},
 }
 
 # preprocessing.py:260-263

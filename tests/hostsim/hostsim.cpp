@@ -50,8 +50,8 @@ extern "C" int hostsim_features(int n, int S, const int8_t* board, const int16_t
                 if (r) planes[(kind ? kPlaneLadderEscape : kPlaneLadderCapture) * 32 + (q >> 5)] |= 1u << (q & 31);
             }
         }
-        uint8_t* o = out + (size_t)b * kNumPlanes * np;
-        for (int k = 0; k < kNumPlanes; k++)
+        uint8_t* o = out + (size_t)b * 49 * np;
+        for (int k = 0; k < 49; k++)
             for (int x = 0; x < S; x++)
                 for (int y = 0; y < S; y++) o[k * np + x * S + y] = (planes[k * 32 + x] >> y) & 1u;
     }

@@ -59,5 +59,7 @@ def test_preprocess_registry_matches_reference_names():
     assert pp.output_dim == 48 and pp.feature_list == DEFAULT_FEATURES
     assert Preprocess(["Board", "LEGAL"]).output_dim == 4
     assert set(FEATURES) == set(go_oracle.FEATURE_IDS)
+    assert set(FEATURES) - {"color"} == {"board", "ones", "turns_since", "liberties", "capture_size", "self_atari_size",
+                                          "liberties_after", "ladder_capture", "ladder_escape", "sensibleness", "zeros", "legal"}
     with pytest.raises(ValueError, match="uknown feature"):
         Preprocess(["board", "nonsense"])
