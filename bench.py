@@ -1,0 +1,324 @@
+#!/usr/bin/env python
+"""bench.py -- positions/sec of the batched position-evaluation hot path on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--batch B] [--dtype fp16|bf16]
+    python bench.py --impl reference ...        # the CPU path, for the driver's ratio
+
+One step = one pass of the hot path over one batch of synthetic random-playout positions
+(BASELINE.json: 48-plane features incl. ladders + 13-layer x 192-filter policy forward, 19x19):
+packed states -> analyze/ladder/emit kernels -> 12 tcgen05 convolutions (+ fused 1x1) -> softmax.
+
+  value     positions/s with the packed states already resident in HBM (device-timed, CUDA events)
+  e2e       the same through the C-ABI with HOST buffers: pinned packed states -> H2D ->
+            rag_eval_batch -> D2H of the probabilities, every step
+  roofline  the dominant kernel (the 3x3 192->192 convolution, 11 of the 12 launches per step):
+            algorithmic FLOPs per launch / its CUDA-event time, vs the measured dense bf16 peak
+  cpu_baseline  the CPU port of the reference path (C oracle for the features on all host cores
+            + torch fp32 forward), on a bounded sample
+
+Multi-GPU (torchrun, one rank per GPU): every rank evaluates its own batch, no collective on the
+data path ("scaling": "weak"); the timed region is bracketed by barriers and the slowest rank's
+time is used.
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "positions/sec: 48-plane features + policy CNN fwd, 19x19"
+FLOP_3X3 = 2 * 361 * 192 * 192 * 9            # per position, one 3x3 192->192 layer
+FLOP_POLICY = 2_801_452_416                    # per position, whole 13x192 policy
+FEATURE_BYTES = 17_568                         # per position, packed state in + 48x361 u8 out
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        p = json.load(open(path))
+        return dict(hbm=p["hbm_gbs"], tf_burst=p["bf16_tflops"], tf_sustained=p["bf16_tflops_sustained"], src="measured")
+    return dict(hbm=6650.0, tf_burst=1590.0, tf_sustained=1400.0, src="fallback")
+
+
+class ClockSampler(object):
+    """nvidia-smi clocks and throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu, self.rows, self.proc = gpu_index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:  # noqa: BLE001
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:  # noqa: BLE001
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2]))
+                for nm, v in zip(names, r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+            except Exception:  # noqa: BLE001
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ----------------------------------------------------------------------------------------- CPU arm
+
+def _cpu_features_worker(args):
+    from oracle import go_oracle
+    b, a, ko, pl = args
+    return go_oracle.features(b, a, ko, pl, go_oracle.DEFAULT_FEATURES)
+
+
+def cpu_path(n_positions, cores, seed=99, pool=None):
+    """The reference's serial features -> forward (policy.py:42-45) in its CPU port: C oracle
+    feature planes on `cores` processes, then the torch fp32 forward on `cores` threads.
+    Returns (seconds_features, seconds_forward)."""
+    import multiprocessing as mp
+    from oracle import cnn_oracle, go_oracle
+    b, a, ko, pl = go_oracle.random_playouts(n_positions, size=19, seed=seed)
+    specs = cnn_oracle.layer_specs(input_dim=48, layers=12, filters_per_layer=192)
+    weights = cnn_oracle.uniform_weights(specs, 48, 19, seed=1)
+    chunks = [(b[i::cores], a[i::cores], ko[i::cores], pl[i::cores]) for i in range(cores) if len(b[i::cores])]
+    own_pool = pool is None
+    if own_pool:
+        pool = mp.get_context("fork").Pool(cores)
+        pool.map(_cpu_features_worker, [(c[0][:1], c[1][:1], c[2][:1], c[3][:1]) for c in chunks])  # spin up
+    t0 = time.time()
+    parts = pool.map(_cpu_features_worker, chunks)
+    t1 = time.time()
+    planes = np.concatenate(parts, axis=0)
+    cnn_oracle.forward(weights, planes[:2], specs, threads=cores)
+    t2 = time.time()
+    cnn_oracle.forward(weights, planes, specs, threads=cores)
+    t3 = time.time()
+    if own_pool:
+        pool.close()
+    return t1 - t0, t3 - t2
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    sample = args.ref_sample
+    import multiprocessing as mp
+    pool = mp.get_context("fork").Pool(cores)
+    for _ in range(args.warmup):
+        cpu_path(min(sample, 64), cores, pool=pool)
+    t0 = time.time()
+    tf = tn = 0.0
+    for k in range(args.steps):
+        a, b = cpu_path(sample, cores, seed=1000 + k, pool=pool)
+        tf += a; tn += b
+    total = time.time() - t0
+    pool.close()
+    value = sample * args.steps / (tf + tn)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "positions/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * (tf + tn) / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "13x192 policy + 48 planes, 19x19; CPU port of the reference path "
+                               "(C feature oracle on all cores, then torch fp32 forward), %d positions/step" % sample},
+        "cpu_baseline": {"value": value, "unit": "positions/s", "cores": cores, "kind": "port",
+                         "sample": "%d steps x %d random-playout positions; features %.2fs + forward %.2fs; wall %.1fs"
+                                   % (args.steps, sample, tf, tn, total)},
+        "e2e": {"value": value, "unit": "positions/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+
+
+# ----------------------------------------------------------------------------------------- GPU arm
+
+def run_gpu(args):
+    import torch
+    import torch.distributed as dist
+    from rocalphago_b200 import BatchedGameState, _cabi
+    from rocalphago_b200.models import CNNPolicy
+    from rocalphago_b200.preprocessing import DEFAULT_FEATURES
+    from rocalphago_b200.state import _ptr, _stream
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device; there is no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    n = args.batch
+    L = _cabi.lib()
+    net = CNNPolicy(DEFAULT_FEATURES, layers=12, filters_per_layer=192, dtype=args.dtype, seed=1234)
+    model = net.model
+    plane_src = net.preprocessor.plane_src
+    h = model._ensure_handle(dev)
+    _cabi.check(L.rag_net_set_profiling(h, 1))
+
+    # synthetic inputs: `pool` distinct batches of random-playout positions generated on the device
+    pool = max(2, args.pool)
+    batches = [BatchedGameState.random_playouts(n, seed=20261106 + 7919 * (rank * pool + i), device=dev) for i in range(pool)]
+    host_in = [b.packed.cpu().pin_memory() for b in batches]
+    dev_in = torch.empty_like(batches[0].packed)
+    host_out = torch.empty((n, 361), dtype=torch.float32).pin_memory()
+    out = torch.empty((n, 361), dtype=torch.float32, device=dev)
+    ws_bytes = int(L.rag_eval_workspace_bytes(h, n))
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)          # > 126 MB L2
+    src_ptr = plane_src.ctypes.data_as(ctypes.c_void_p)
+
+    def step(packed):
+        _cabi.check(L.rag_eval_batch(h, _ptr(packed), n, src_ptr, len(plane_src), _ptr(out), _ptr(ws), ws_bytes, _stream()))
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(max(3, args.warmup)):
+        step(batches[i % pool].packed)
+    barrier()
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+
+    # ---- device-resident: K steps, each timed with its own CUDA event pair, L2 flushed between
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    layer_ms = np.zeros(12)
+    barrier()
+    wall0 = time.time()
+    for k in range(args.steps):
+        flush.zero_()
+        ev[k][0].record()
+        step(batches[k % pool].packed)
+        ev[k][1].record()
+        lm = (ctypes.c_float * 12)()
+        _cabi.check(L.rag_net_layer_times(h, lm, 12))
+        layer_ms += np.asarray(list(lm))
+    barrier()
+    wall = time.time() - wall0
+    dev_ms = sum(a.elapsed_time(b) for a, b in ev)
+    layer_ms /= args.steps
+
+    # ---- end to end through the C ABI with host buffers (pinned): H2D + eval + D2H every step
+    stream = torch.cuda.current_stream()
+    for i in range(2):
+        dev_in.copy_(host_in[i % pool], non_blocking=True); step(dev_in); host_out.copy_(out, non_blocking=True)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.time()
+    e0.record()
+    for k in range(args.steps):
+        dev_in.copy_(host_in[k % pool], non_blocking=True)
+        step(dev_in)
+        host_out.copy_(out, non_blocking=True)
+        stream.synchronize()                                  # the caller owns the result after every step
+    e1.record()
+    barrier()
+    e2e_wall = time.time() - t0
+    e2e_ms = max(e0.elapsed_time(e1), 0.0)
+    clocks = sampler.stop() if rank == 0 else None
+
+    t = torch.tensor([dev_ms, e2e_ms, e2e_wall * 1e3], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms, e2e_ms, e2e_wall_ms = [float(v) for v in t.cpu()]
+
+    if rank == 0:
+        peaks = load_peaks()
+        total_pos = n * args.steps * world
+        value = total_pos / (dev_ms / 1e3)
+        e2e_val = total_pos / (max(e2e_ms, e2e_wall_ms) / 1e3)
+        k3 = float(np.mean(layer_ms[1:]))                      # the eleven 3x3 192->192 launches
+        achieved = FLOP_3X3 * n / (k3 / 1e3) / 1e12
+        line = {
+            "metric": METRIC, "value": value, "unit": "positions/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(3, args.warmup), "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
+            "config": {"workload": "48 planes (incl. ladders) + 13x192 policy forward, 19x19, batch %d/GPU, "
+                                   "device-generated random-playout positions, random-init weights" % n,
+                       "batch_per_gpu": n, "l2": "256 MiB buffer written between timed steps",
+                       "parallelism": "dp%d (independent batches, no collective on the data path)" % world},
+            "e2e": {"value": e2e_val, "unit": "positions/s", "h2d_bytes_per_step": int(n * 768),
+                    "d2h_bytes_per_step": int(n * 361 * 4), "ms_per_step": max(e2e_ms, e2e_wall_ms) / args.steps},
+            "gpu_launches": 16 * args.steps,
+            "clocks": clocks,
+            "roofline": {"bound": "tensor", "kernel": "conv_umma_kernel, 3x3 192->192 layer (11 of 12 conv launches per step)",
+                         "achieved": achieved, "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
+                         "frac": achieved / peaks["tf_sustained"], "peak_source": peaks["src"] + " (sustained)",
+                         "ms_per_launch": k3, "traffic": None},
+            "stage_ms": {"conv_layer1": float(layer_ms[0]), "conv_3x3_mean": k3, "conv_all": float(layer_ms.sum()),
+                         "step": dev_ms / args.steps},
+            "whole_net_tflops": FLOP_POLICY * n / (float(layer_ms.sum()) / 1e3) / 1e12,
+            "wall_s": wall,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            cores = os.cpu_count() or 1
+            sample = args.cpu_sample
+            tf, tn = cpu_path(sample, cores)
+            line["cpu_baseline"] = {"value": sample / (tf + tn), "unit": "positions/s", "cores": cores, "kind": "port",
+                                    "sample": "%d random-playout positions once: C feature oracle on %d processes %.2fs "
+                                              "(%.0f pos/s) + torch fp32 13x192 forward on %d threads %.2fs (%.0f pos/s)"
+                                              % (sample, cores, tf, sample / tf, cores, tn, sample / tn)}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--batch", type=int, default=4096, help="positions per GPU per step")
+    ap.add_argument("--pool", type=int, default=4, help="distinct input batches cycled through")
+    ap.add_argument("--dtype", default="fp16", choices=["fp16", "bf16"])
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--cpu-sample", type=int, default=512)
+    ap.add_argument("--ref-sample", type=int, default=256)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -175,6 +175,17 @@ long long rag_net_input_rows(const rag_net* net, int n);
 int rag_net_input_channels(const rag_net* net);
 int rag_net_input_pad(const rag_net* net);
 
+/* Measurement aid: with profiling on, every forward records a CUDA event on its stream before
+ * each convolution launch and after the last; rag_net_layer_times then gives the device time
+ * of each of the `layers` convolution kernels of the most recent forward (waits for it).
+ * Between two layers the interval also covers the margin memsets of the next buffer. */
+int rag_net_set_profiling(rag_net* net, int enable);
+int rag_net_layer_times(rag_net* net, float* h_ms, int n_layers);
+
+/* Byte offset, inside the workspace of a finished forward for n boards, of the fp32 output of
+ * the 1x1 convolution ([n][S*S], before Bias/softmax or the dense head): for inspection/tests. */
+size_t rag_net_logits_offset(const rag_net* net, int n);
+
 /* NeuralNetBase.forward (nn_util.py:57-58): d_nchw float [n][in_planes][S][S] ->
  * d_out float [n][S*S] probabilities (policy) or [n] values in [-1, 1] (value). */
 int rag_net_forward(rag_net* net, const float* d_nchw, int n, float* d_out, void* d_workspace,

@@ -56,6 +56,9 @@ def lib():
         "rag_net_num_weight_arrays": (i32, [vp]),
         "rag_net_load_weights": (i32, [vp, vp, i32]),
         "rag_net_workspace_bytes": (sz, [vp, i32]),
+        "rag_net_logits_offset": (sz, [vp, i32]),
+        "rag_net_set_profiling": (i32, [vp, i32]),
+        "rag_net_layer_times": (i32, [vp, vp, i32]),
         "rag_net_input_rows": (i64, [vp, i32]),
         "rag_net_input_channels": (i32, [vp]),
         "rag_net_input_pad": (i32, [vp]),

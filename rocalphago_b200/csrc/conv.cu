@@ -420,6 +420,8 @@ struct rag_net {
     float* d_dense2_w = nullptr;   // [D]
     float* d_dense2_b = nullptr;   // [1]
     bool loaded = false;
+    bool profiling = false;        // record a CUDA event around every convolution launch
+    std::vector<cudaEvent_t> events;   // layers + 1
 };
 
 namespace rag {
@@ -510,8 +512,10 @@ static int run_layers(rag_net* net, const uint16_t* d_in, int n, float* d_out, c
         const size_t smem = conv_smem_bytes(ly.n_pad, p.stages);
         RAG_CUDA_CHECK(cudaFuncSetAttribute(conv_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         const int grid = p.tiles < net->sms ? p.tiles : net->sms;
+        if (net->profiling) RAG_CUDA_CHECK(cudaEventRecord(net->events[l], s));
         conv_umma_kernel<<<grid, kConvThreads, smem, s>>>(tmA, tmB, p);
         RAG_CUDA_CHECK(cudaGetLastError());
+        if (net->profiling && last) RAG_CUDA_CHECK(cudaEventRecord(net->events[L], s));
         cur = dst;
     }
     const int P = S * S;
@@ -580,6 +584,7 @@ int rag_net_destroy(rag_net* net)
 {
     if (!net) return RAG_OK;
     for (auto& ly : net->layers) { cudaFree(ly.d_w); cudaFree(ly.d_bias); }
+    for (auto& e : net->events) cudaEventDestroy(e);
     cudaFree(net->d_head_w); cudaFree(net->d_pos_bias);
     cudaFree(net->d_dense1_w); cudaFree(net->d_dense1_b); cudaFree(net->d_dense2_w); cudaFree(net->d_dense2_b);
     delete net;
@@ -652,6 +657,35 @@ size_t rag_net_workspace_bytes(const rag_net* net, int n)
 {
     if (!net || n <= 0) return 0;
     return carve_net(net, n, nullptr, true).total;
+}
+
+int rag_net_set_profiling(rag_net* net, int enable)
+{
+    if (!net) return fail(RAG_EINVAL, "null net");
+    if (enable && net->events.empty()) {
+        net->events.resize(net->layers.size() + 1);
+        for (auto& e : net->events) RAG_CUDA_CHECK(cudaEventCreate(&e));
+    }
+    net->profiling = enable != 0;
+    return RAG_OK;
+}
+
+int rag_net_layer_times(rag_net* net, float* h_ms, int n_layers)
+{
+    if (!net || !h_ms) return fail(RAG_EINVAL, "null argument");
+    if (!net->profiling || n_layers != (int)net->layers.size()) return fail(RAG_EINVAL, "profiling is off or n_layers != %zu", net->layers.size());
+    for (int l = 0; l < n_layers; l++) {
+        RAG_CUDA_CHECK(cudaEventSynchronize(net->events[l + 1]));
+        RAG_CUDA_CHECK(cudaEventElapsedTime(&h_ms[l], net->events[l], net->events[l + 1]));
+    }
+    return RAG_OK;
+}
+
+size_t rag_net_logits_offset(const rag_net* net, int n)
+{
+    if (!net || n <= 0) return 0;
+    NetBuffers b = carve_net(net, n, nullptr, true);
+    return (size_t)((char*)b.logits - (char*)nullptr);
 }
 
 long long rag_net_input_rows(const rag_net* net, int n) { return net ? conv_rows(n, net->desc.board, net->layers[0].width / 2) : 0; }

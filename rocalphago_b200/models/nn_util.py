@@ -235,6 +235,12 @@ class Network(object):
                                          _ptr(out), _ptr(ws), ws.numel(), _stream()))
         return out
 
+    def last_logits(self, n):
+        """fp32 output of the 1x1 convolution of the last forward_device(n boards) call."""
+        off = int(_cabi.lib().rag_net_logits_offset(self._handle, n))
+        P = self.board * self.board
+        return self._ws[off:off + 4 * n * P].view(torch.float32).reshape(n, P).clone()
+
     def features_workspace(self):
         """The analysis workspace of the last eval_batch_device call (planes 46/48 give the move lists)."""
         return self._ws

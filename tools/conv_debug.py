@@ -26,7 +26,7 @@ def check(name, feats, n, board=19, dtype="bf16", head="policy", **arch):
     tcpu = time.time() - t0
     torch.cuda.synchronize()
     try:
-        got = net.forward(planes.astype(np.float32))
+        got = net.forward(planes.astype(np.float32)).reshape(want.shape)
     except Exception as e:  # noqa: BLE001
         print("%-28s FAILED: %s" % (name, e))
         return
