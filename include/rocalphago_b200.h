@@ -104,6 +104,32 @@ int rag_features(const uint32_t* d_states, int n, int size, const int32_t* h_pla
                  int layout, int conv_dtype, int conv_pad, int conv_channels, void* d_out,
                  void* d_workspace, size_t workspace_bytes, void* stream);
 
+/* rag_features for callers that must not allocate.  (No counterpart in the reference: its
+ * Python allocates a fresh numpy array per call.)
+ *
+ * Some hosts cannot give this library a workspace: an engine that hands out all of its device
+ * memory at start-up and forbids cudaMalloc afterwards, a plug-in running inside another
+ * framework's memory pool, or a latency-critical loop (a GTP engine answering under a clock)
+ * that cannot afford the device-wide synchronisation an allocation may imply.  For them the
+ * scratch of the analysis and ladder kernels lives in the library itself: a fixed array in device
+ * memory, about 2.3 MB on every GPU that loads the library, kept until the process exits.
+ *
+ *   - at most rag_features_static_max_positions() (= 256) positions per call; more is refused
+ *     with RAG_ENOMEM and a message -- split the batch or use rag_features
+ *   - the caller still passes the states and the output buffer; nothing is allocated or freed,
+ *     here or in any routine this calls
+ *   - the first call on each device looks the array's device address up (one runtime query,
+ *     with that device current); make that first call during start-up, before any stream
+ *     capture is begun
+ *   - all calls share the one array per GPU: two calls whose work overlaps on the GPU (different
+ *     streams, different threads) race on it -- keep them on one stream or serialise them
+ *     yourself.  Contents left by an earlier call never leak into a later result.
+ * Arguments and results are exactly those of rag_features. */
+int rag_features_static(const uint32_t* d_states, int n, int size, const int32_t* h_plane_src, int F,
+                        int layout, int conv_dtype, int conv_pad, int conv_channels, void* d_out,
+                        void* stream);
+int rag_features_static_max_positions(void);
+
 /* Rows of the zero-padded pixel-row layout for n boards of size S with `pad` zero
  * columns/rows per board: pixel (x, y) of board b is row
  *     128 + b*(S+pad)*(S+pad) + x*(S+pad) + y

@@ -47,6 +47,8 @@ def lib():
         "rag_features_analyze": (i32, [vp, i32, i32, i32, vp, sz, vp]),
         "rag_features_emit": (i32, [vp, i32, i32, vp, i32, i32, i32, i32, i32, vp, vp]),
         "rag_features": (i32, [vp, i32, i32, vp, i32, i32, i32, i32, i32, vp, vp, sz, vp]),
+        "rag_features_static": (i32, [vp, i32, i32, vp, i32, i32, i32, i32, i32, vp, vp]),
+        "rag_features_static_max_positions": (i32, []),
         "rag_conv_rows": (i64, [i32, i32, i32]),
         "rag_do_move": (i32, [vp, i32, i32, vp, vp, vp]),
         "rag_random_playouts": (i32, [vp, i32, i32, u64, i32, i32, vp, i32, vp]),

@@ -22,6 +22,7 @@
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 #include <string.h>
+#include <mutex>
 
 namespace rag {
 
@@ -288,6 +289,35 @@ playout_kernel(uint32_t* out, int n_positions, int S, uint64_t seed, int max_ply
     }
 }
 
+// ---- scratch that nobody allocates (rag_features_static) -----------------------------------------
+//
+// Same layout as the caller-provided workspace (counters, bit-planes, ladder queue), sized for
+// kStaticMaxPositions positions, but living in the library's own device image: every GPU that loads
+// the library carries these ~2.3 MB until the process exits, and no allocation call is ever needed.
+constexpr int kStaticMaxPositions = 256;
+constexpr size_t kStaticScratchBytes =
+    (size_t)kCounterBytes + (size_t)kStaticMaxPositions * (kPlaneWords * 4 + 2 * kMaxBoard * kMaxBoard * 4);
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+// In host code `g_static_scratch` is only a handle for the runtime, not an address a kernel could
+// use; the device address has to be asked for, per device, with that device current.
+static int static_scratch_address(void** out) {
+    static std::mutex mu;
+    static void* per_device[64] = {nullptr};
+    int dev = -1;
+    RAG_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return fail(RAG_EUNSUPPORTED, "device ordinal %d not supported", dev);
+    std::lock_guard<std::mutex> lock(mu);
+    if (!per_device[dev]) {
+        void* p = nullptr;
+        RAG_CUDA_CHECK(cudaGetSymbolAddress(&p, g_static_scratch));
+        if (!p) return fail(RAG_ECUDA, "cudaGetSymbolAddress returned a null address on device %d", dev);
+        per_device[dev] = p;
+    }
+    *out = per_device[dev];
+    return RAG_OK;
+}
+
 static int check_size(int size) {
     if (size < 2 || size > kMaxBoard) return fail(RAG_EUNSUPPORTED, "board size %d not in [2, 19]", size);
     return RAG_OK;
@@ -445,6 +475,26 @@ int rag_features(const uint32_t* d_states, int n, int size, const int32_t* h_pla
         if (h_plane_src[i] == kPlaneLadderCapture || h_plane_src[i] == kPlaneLadderEscape) with_ladders = 1;
     if (int rc = rag_features_analyze(d_states, n, size, with_ladders, d_workspace, workspace_bytes_given, stream)) return rc;
     return rag_features_emit(d_workspace, n, size, h_plane_src, F, layout, conv_dtype, conv_pad, conv_channels, d_out, stream);
+}
+
+int rag_features_static_max_positions(void) { return kStaticMaxPositions; }
+
+int rag_features_static(const uint32_t* d_states, int n, int size, const int32_t* h_plane_src, int F, int layout,
+                        int conv_dtype, int conv_pad, int conv_channels, void* d_out, void* stream)
+{
+    if (n > kStaticMaxPositions)
+        return fail(RAG_ENOMEM, "rag_features_static handles at most %d positions per call (got %d); "
+                                "split the batch or use rag_features with your own workspace", kStaticMaxPositions, n);
+    static_assert(kStaticScratchBytes >= (size_t)kCounterBytes, "scratch too small");
+    if (workspace_bytes(kStaticMaxPositions) != kStaticScratchBytes)
+        return fail(RAG_EINVAL, "internal: static scratch size out of date");
+    void* scratch = nullptr;
+    if (int rc = static_scratch_address(&scratch)) return rc;
+    // The array still holds whatever the previous call left.  What has to start from zero is
+    // cleared on the stream by the analysis step itself (the queue counters); the bit-planes and
+    // queue slots of positions < n are fully rewritten before anything reads them.
+    return rag_features(d_states, n, size, h_plane_src, F, layout, conv_dtype, conv_pad, conv_channels, d_out,
+                        scratch, kStaticScratchBytes, stream);
 }
 
 long long rag_conv_rows(int n, int size, int pad) { return conv_rows(n, size, pad); }
