@@ -89,10 +89,15 @@ int rag_unpack_states(int n, int size, const uint32_t* h_packed, int8_t* h_board
 size_t rag_features_workspace_bytes(int n);
 
 /* Step 1: analyse n packed states into canonical bit-planes held in the workspace.
- * with_ladders = 0 skips the ladder reader (planes 44/45 stay zero).  The
- * workspace must stay untouched until the emits that read it have run. */
+ * with_ladders = 0 skips the ladder reader (planes 44/45 stay zero); 1 runs it; 2 only queues
+ * the ladder candidates, for a later rag_features_ladders on the same workspace (lets a caller
+ * put the short analysis and the long, latency-bound ladder search on different streams).
+ * The workspace must stay untouched until the emits that read it have run. */
 int rag_features_analyze(const uint32_t* d_states, int n, int size, int with_ladders,
                          void* d_workspace, size_t workspace_bytes, void* stream);
+/* Step 1b: the ladder reader over the candidates queued by rag_features_analyze(with_ladders = 2). */
+int rag_features_ladders(const uint32_t* d_states, int n, int size, void* d_workspace,
+                         size_t workspace_bytes, void* stream);
 /* Step 2: write the listed planes from the workspace in the requested layout.
  * conv_dtype / conv_pad / conv_channels are read only for RAG_LAYOUT_CONV_IN
  * (conv_pad = first layer's filter_width // 2; conv_channels = 64 or 128 >= F). */

@@ -38,8 +38,8 @@ constexpr int kMaxPositionsPerLaunch = 1 << 21;        // queue item = pos<<11 |
 
 struct Workspace {
     unsigned* counters;      // [0] items queued, [1] items taken
-    uint32_t* planes;        // [n][49][32]
-    uint32_t* queue;         // [n * 2 * S*S]
+    uint32_t* planes;        // [n][50][32]
+    uint32_t* queue;         // [n * 2 * S*S]  ladder work items
     size_t queue_cap;
 };
 
@@ -139,8 +139,14 @@ ladder_kernel(const uint32_t* __restrict__ states, int S, Workspace ws)
         const LoadedState s = load_state(states + (size_t)pos * RAG_STATE_WORDS, g);
         const BB own = s.player > 0 ? s.black : s.white;
         const BB opp = s.player > 0 ? s.white : s.black;
-        const bool hit = ladder_root(g, own, opp, p_to_q(s.ko_p, S), q, kind == 1, st);
-        if (hit && g.lane == 0)
+#ifdef RAG_LADDER_TIMING
+        const long long t_item = clock64();
+#endif
+        const int r = ladder_root(g, own, opp, p_to_q(s.ko_p, S), q, kind == 1, -1, st);
+#ifdef RAG_LADDER_TIMING
+        if (g.lane == 0) ws.queue[idx] = (uint32_t)((clock64() - t_item) >> 4);     // tools/ladder_profile.py
+#endif
+        if (r == kLadderValue1 && g.lane == 0)
             atomicOr(ws.planes + (size_t)pos * kPlaneWords + (kPlaneLadderCapture + kind) * 32 + (q >> 5),
                      1u << (q & 31));
     }
@@ -295,7 +301,7 @@ playout_kernel(uint32_t* out, int n_positions, int S, uint64_t seed, int max_ply
 // kStaticMaxPositions positions, but living in the library's own device image: every GPU that loads
 // the library carries these ~2.3 MB until the process exits, and no allocation call is ever needed.
 constexpr int kStaticMaxPositions = 256;
-constexpr size_t kStaticScratchBytes =
+constexpr size_t kStaticScratchBytes =                              // = workspace_bytes(kStaticMaxPositions)
     (size_t)kCounterBytes + (size_t)kStaticMaxPositions * (kPlaneWords * 4 + 2 * kMaxBoard * kMaxBoard * 4);
 static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
 
@@ -413,16 +419,38 @@ int rag_features_analyze(const uint32_t* d_states, int n, int size, int with_lad
     RAG_CUDA_CHECK(cudaMemsetAsync(ws.counters, 0, kCounterBytes, s));
     analyze_kernel<<<(n + kWarpsPerBlock - 1) / kWarpsPerBlock, kWarpsPerBlock * 32, 0, s>>>(d_states, n, size, with_ladders, ws);
     RAG_CUDA_CHECK(cudaGetLastError());
-    if (with_ladders) {
+    if (with_ladders == 1) {
         int dev = 0, sms = 148;
         RAG_CUDA_CHECK(cudaGetDevice(&dev));
         RAG_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-        // enough warps to keep every SM busy; each loops until the queue is drained
+        // Persistent warps, each looping until the queue is drained.  4 CTAs (16 warps, half the
+        // register file) per SM at most: the searches are latency-bound, so more warps buy little,
+        // and a convolution CTA of another stream (conv.cu) must still fit beside them.
         long long want = ((long long)n * 16 + kWarpsPerBlock - 1) / kWarpsPerBlock;
-        int blocks = (int)(want < (long long)sms * 8 ? (want < 1 ? 1 : want) : (long long)sms * 8);
+        int blocks = (int)(want < (long long)sms * 4 ? (want < 1 ? 1 : want) : (long long)sms * 4);
         ladder_kernel<<<blocks, kWarpsPerBlock * 32, 0, s>>>(d_states, size, ws);
         RAG_CUDA_CHECK(cudaGetLastError());
     }
+    return RAG_OK;
+}
+
+int rag_features_ladders(const uint32_t* d_states, int n, int size, void* d_workspace, size_t workspace_bytes_given,
+                         void* stream)
+{
+    if (n < 0 || (n > 0 && (!d_states || !d_workspace))) return fail(RAG_EINVAL, "null argument");
+    if (int rc = check_size(size)) return rc;
+    if (n > kMaxPositionsPerLaunch) return fail(RAG_EUNSUPPORTED, "n = %d exceeds %d positions per call", n, kMaxPositionsPerLaunch);
+    if (workspace_bytes_given < workspace_bytes(n))
+        return fail(RAG_ENOMEM, "workspace has %zu bytes, %zu needed for n = %d", workspace_bytes_given, workspace_bytes(n), n);
+    if (n == 0) return RAG_OK;
+    Workspace ws = carve(d_workspace, n);
+    int dev = 0, sms = 148;
+    RAG_CUDA_CHECK(cudaGetDevice(&dev));
+    RAG_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    long long want = ((long long)n * 16 + kWarpsPerBlock - 1) / kWarpsPerBlock;
+    int blocks = (int)(want < (long long)sms * 4 ? (want < 1 ? 1 : want) : (long long)sms * 4);
+    ladder_kernel<<<blocks, kWarpsPerBlock * 32, 0, (cudaStream_t)stream>>>(d_states, size, ws);
+    RAG_CUDA_CHECK(cudaGetLastError());
     return RAG_OK;
 }
 

@@ -487,6 +487,18 @@ struct LadderStack {
 
 enum { kLadderValue0 = 0, kLadderValue1 = 1, kLadderPush = 2 };
 
+#if !RAG_DEVICE_BUILD
+// host-only instrumentation for tests/hostsim experiments
+struct LadderStats { long long nodes; int max_depth; long long per_depth[96]; int cur_depth; };
+static LadderStats g_ladder_stats = {0, 0, {0}, 0};
+#define RAG_LADDER_COUNT_NODE() (g_ladder_stats.nodes++, g_ladder_stats.per_depth[g_ladder_stats.cur_depth]++)
+static void (*g_ladder_node_hook)(const uint32_t* h32, const uint32_t* p32, int ko, int is_capture, int mv) = nullptr;
+#define RAG_LADDER_DEPTH(d) do { if ((d) > g_ladder_stats.max_depth) g_ladder_stats.max_depth = (d); } while (0)
+#else
+#define RAG_LADDER_COUNT_NODE() ((void)0)
+#define RAG_LADDER_DEPTH(d) ((void)0)
+#endif
+
 // One call of is_ladder_capture (is_capture) or is_ladder_escape on a SINGLE prey group.
 // Plays `mv`, then either decides at once or leaves the set of replies to try in `pending`.
 //   capture node (go.py:345-391): hunter plays; replies = prey's liberties + the last liberty of
@@ -496,6 +508,10 @@ enum { kLadderValue0 = 0, kLadderValue1 = 1, kLadderPush = 2 };
 // `remaining` is the reference's remaining_attempts; legality is tested before it (H11).
 RAG_FN int ladder_expand(const Geo& g, bool is_capture, BB& H, BB& P, int& ko, int mv, int prey_q,
                          int remaining, BB& pending) {
+    RAG_LADDER_COUNT_NODE();
+#if !RAG_DEVICE_BUILD
+    if (g_ladder_node_hook) g_ladder_node_hook(H.w, P.w, ko, is_capture ? 1 : 0, mv);
+#endif
     bool ok = is_capture ? bb_play(g, H, P, ko, mv, nullptr) : bb_play(g, P, H, ko, mv, nullptr);
     if (!ok) return kLadderValue0;
     if (remaining <= 0) return is_capture ? kLadderValue1 : kLadderValue0;
@@ -523,12 +539,31 @@ RAG_FN int ladder_expand(const Geo& g, bool is_capture, BB& H, BB& P, int& ko, i
     return kLadderPush;
 }
 
+constexpr int kLadderAborted = 2;
+
 // Depth-first search with an explicit stack; a node's value is "no child has value 1".
-RAG_FN_NOINLINE bool ladder_search(const Geo& g, BB H, BB P, int ko, int first_move, int prey_q,
-                                   bool root_is_capture, LadderStack& st) {
-    BB pending = bb_zero();
-    int res = ladder_expand(g, root_is_capture, H, P, ko, first_move, prey_q, kLadderDepth, pending);
-    if (res != kLadderPush) return res == kLadderValue1;
+// `remaining0` is the reference's remaining_attempts at the first move (80 at the top level);
+// `budget` bounds the number of moves tried (< 0: unbounded) -- when it runs out the search
+// stops with kLadderAborted and `nodes` tells how far it got.  Returns 0, 1 or kLadderAborted.
+// `frame_is_capture` is the kind of the node whose replies are in `pending` (frame 0); its
+// replies are tried with remaining_attempts = remaining_children.
+struct NeverCancel {
+#if RAG_DEVICE_BUILD
+    __device__ __forceinline__
+#endif
+    bool operator()() const { return false; }
+};
+
+// `cancel()` is asked every 16 moves; when it says yes the search stops with kLadderAborted (used
+// by the all-warps evaluator to drop subtrees whose result no longer matters).
+template <class Cancel>
+#if RAG_DEVICE_BUILD
+__device__ __noinline__
+#else
+static
+#endif
+int ladder_dfs(const Geo& g, BB H, BB P, int ko, BB pending, int prey_q, bool frame_is_capture,
+                               int remaining_children, int budget, int nodes, LadderStack& st, Cancel cancel) {
     int d = 0;
     st.hunter[0] = H; st.prey[0] = P; st.pending[0] = pending; st.ko[0] = (int16_t)ko;
     for (;;) {
@@ -536,12 +571,19 @@ RAG_FN_NOINLINE bool ladder_search(const Geo& g, BB H, BB P, int ko, int first_m
         int m = bb_first(st.pending[d]);
         if (m < 0) v = 1;                                    // every reply failed
         else {
+            if (budget >= 0 && nodes >= budget) return kLadderAborted;
+            if ((nodes & 15) == 15 && cancel()) return kLadderAborted;
+            nodes++;
             st.pending[d] = andnot(st.pending[d], bb_single(m, g));
-            bool node_is_capture = root_is_capture ^ ((d & 1) != 0);
+            bool node_is_capture = frame_is_capture ^ ((d & 1) != 0);
             H = st.hunter[d]; P = st.prey[d]; ko = st.ko[d];
-            res = ladder_expand(g, !node_is_capture, H, P, ko, m, prey_q, kLadderDepth - d - 1, pending);
+#if !RAG_DEVICE_BUILD
+            g_ladder_stats.cur_depth = d + 1;
+#endif
+            int res = ladder_expand(g, !node_is_capture, H, P, ko, m, prey_q, remaining_children - d, pending);
             if (res == kLadderPush) {
                 d++;
+                RAG_LADDER_DEPTH(d);
                 st.hunter[d] = H; st.prey[d] = P; st.pending[d] = pending; st.ko[d] = (int16_t)ko;
                 continue;
             }
@@ -549,7 +591,7 @@ RAG_FN_NOINLINE bool ladder_search(const Geo& g, BB H, BB P, int ko, int first_m
             v = 0;
         }
         for (;;) {                                           // frame d returns v
-            if (d == 0) return v == 1;
+            if (d == 0) return v;
             d--;
             if (v == 0) break;                               // parent keeps looking
             v = 0;                                           // a child of value 1 refutes the parent
@@ -557,27 +599,47 @@ RAG_FN_NOINLINE bool ladder_search(const Geo& g, BB H, BB P, int ko, int first_m
     }
 }
 
-// Top level of is_ladder_capture(action) / is_ladder_escape(action) with prey=None
-// (go.py:355-361, 422-428): true if the search succeeds for ANY adjacent opponent group with
-// exactly two liberties (capture) / own group with exactly one (escape).
-RAG_FN_NOINLINE bool ladder_root(const Geo& g, BB own, BB opp, int ko, int action_q, bool is_escape,
-                                 LadderStack& st) {
+RAG_FN int ladder_search(const Geo& g, BB H, BB P, int ko, int first_move, int prey_q,
+                         bool root_is_capture, int remaining0, int budget, LadderStack& st) {
+    BB pending = bb_zero();
+    int res = ladder_expand(g, root_is_capture, H, P, ko, first_move, prey_q, remaining0, pending);
+    if (res != kLadderPush) return res;
+    return ladder_dfs(g, H, P, ko, pending, prey_q, root_is_capture, remaining0 - 1, budget, 1, st, NeverCancel());
+}
+
+// The prey groups is_ladder_capture(action) / is_ladder_escape(action) look at when called with
+// prey=None (go.py:355-361, 422-428): adjacent opponent groups with exactly two liberties
+// (capture) / own groups with exactly one (escape), each once.  Returns how many; prey_out[i] is
+// a stone of the i-th group.
+RAG_FN int ladder_root_preys(const Geo& g, BB own, BB opp, int action_q, bool is_escape, int prey_out[4]) {
     const BB side = is_escape ? own : opp;
     const BB empty = andnot(bb_board(g), own | opp);
     const int want = is_escape ? 1 : 2;
     BB done = bb_zero();
+    int n = 0;
     for (int d = 0; d < 4; d++) {
         int nq = q_neighbor(action_q, d, g.S);
         if (nq < 0 || !bb_test(side, nq) || bb_test(done, nq)) continue;
         BB grp = bb_flood(bb_single(nq, g), side, g);
         done = done | grp;
-        if (bb_count(bb_nbrs(grp, g) & empty) != want) continue;
-        // capture: side to move hunts `opp`; escape: side to move is the prey
-        bool r = is_escape ? ladder_search(g, opp, own, ko, action_q, nq, false, st)
-                           : ladder_search(g, own, opp, ko, action_q, nq, true, st);
-        if (r) return true;
+        if (bb_count(bb_nbrs(grp, g) & empty) == want) prey_out[n++] = nq;
     }
-    return false;
+    return n;
+}
+
+// Top level of is_ladder_capture(action) / is_ladder_escape(action): true if the search succeeds
+// for ANY of those groups.  Returns 0, 1, or kLadderAborted when a search ran out of `budget`.
+RAG_FN_NOINLINE int ladder_root(const Geo& g, BB own, BB opp, int ko, int action_q, bool is_escape,
+                                int budget, LadderStack& st) {
+    int preys[4];
+    const int np = ladder_root_preys(g, own, opp, action_q, is_escape, preys);
+    for (int i = 0; i < np; i++) {
+        // capture: side to move hunts `opp`; escape: side to move is the prey
+        int r = is_escape ? ladder_search(g, opp, own, ko, action_q, preys[i], false, kLadderDepth, budget, st)
+                          : ladder_search(g, own, opp, ko, action_q, preys[i], true, kLadderDepth, budget, st);
+        if (r != kLadderValue0) return r;
+    }
+    return kLadderValue0;
 }
 
 }  // namespace rag

@@ -1,0 +1,144 @@
+"""Two-stage evaluation pipeline: features of batch k+1 overlap the convolutions of batch k.
+
+`rag_eval_batch` runs the two halves of the hot path back to back on one stream.  They stress
+different parts of the SM -- the feature kernels are integer/latency work (a few long ladder
+searches leave most of the chip idle), the convolutions are tensor-core work -- so a service
+that evaluates a stream of batches runs them on two CUDA streams with double-buffered
+intermediates.  This is host-side plumbing over the same C-ABI entry points
+(`rag_features` with RAG_LAYOUT_CONV_IN, then `rag_net_forward_rows`); results are identical.
+"""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _cabi
+from .preprocessing import LAYOUT_CONV_IN
+from .state import STATE_WORDS, _ptr, _require_cuda
+
+
+class _Slot(object):
+    def __init__(self, L, handle, n, size, device, out_cols):
+        rows = int(L.rag_net_input_rows(handle, n))
+        ch = int(L.rag_net_input_channels(handle))
+        self.packed = torch.empty((n, STATE_WORDS), dtype=torch.int32, device=device)
+        self.rows = torch.empty((rows, ch), dtype=torch.float16, device=device)        # 16-bit payload, either dtype
+        self.fws = torch.empty(int(L.rag_features_workspace_bytes(n)), dtype=torch.uint8, device=device)
+        self.out = torch.empty((n, out_cols) if out_cols else (n,), dtype=torch.float32, device=device)
+        self.host_out = torch.empty_like(self.out, device="cpu").pin_memory()
+        self.ana_done = torch.cuda.Event()
+        self.feat_done = torch.cuda.Event()
+        self.net_done = torch.cuda.Event()
+        self.out_copied = torch.cuda.Event()
+        self.used = False
+
+
+class EvalPipeline(object):
+    """Evaluates fixed-size batches of packed states with a policy or value network.
+
+        pipe = EvalPipeline(net, batch_size)
+        for packed in batches:                 # device or pinned-host int32 (n, 192) tensors
+            ticket = pipe.submit(packed, to_host=True)
+        out = pipe.result(ticket)              # numpy / tensor of the ticket's batch
+
+    At most two batches are in flight; `submit` blocks the host only when it would overwrite a
+    result that has not been collected on the device yet.
+    """
+
+    def __init__(self, net, batch_size, device=None, size=None):
+        _require_cuda()
+        self.net, self.model, self.n = net, net.model, int(batch_size)
+        self.device = torch.device(device or "cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.size = int(size or self.model.board)
+        self.L = _cabi.lib()
+        self.handle = self.model._ensure_handle(self.device)
+        self.plane_src = np.ascontiguousarray(net.preprocessor.plane_src, np.int32)
+        if len(self.plane_src) != self.model.input_dim:
+            raise ValueError("feature list gives %d planes, the network takes %d" % (len(self.plane_src), self.model.input_dim))
+        cols = self.model.board ** 2 if self.model.head == "policy" else 0
+        with torch.cuda.device(self.device):
+            self.slots = [_Slot(self.L, self.handle, self.n, self.size, self.device, cols) for _ in range(2)]
+            self.nws = torch.empty(int(self.L.rag_net_workspace_bytes(self.handle, self.n)), dtype=torch.uint8, device=self.device)
+            # Priorities decide who gets an SM when several kernels have CTAs pending.  The analysis
+            # kernel is short but needs shared memory a resident convolution CTA leaves no room for,
+            # so it goes first (it slips in at a layer boundary); the convolutions come next; the
+            # ladder reader and the emit -- no shared memory, mostly waiting -- fill in around them.
+            self.s_ana = torch.cuda.Stream(priority=-2)
+            self.s_net = torch.cuda.Stream(priority=-1)
+            self.s_feat, self.s_copy = torch.cuda.Stream(priority=0), torch.cuda.Stream(priority=0)
+        self.pad = int(self.L.rag_net_input_pad(self.handle))
+        self.channels = int(self.L.rag_net_input_channels(self.handle))
+        self.dtype_code = 0 if self.model.dtype == "bf16" else 1
+        self.count = 0
+
+    def submit(self, packed, to_host=False):
+        """Enqueue one batch; returns a ticket for `result`."""
+        if tuple(packed.shape) != (self.n, STATE_WORDS):
+            raise ValueError("expected a (%d, %d) int32 tensor" % (self.n, STATE_WORDS))
+        k = self.count
+        slot = self.slots[k % 2]
+        L, vp = self.L, ctypes.c_void_p
+        src = self.plane_src.ctypes.data_as(vp)
+        with torch.cuda.device(self.device):
+            # stage 1a: (copy in,) analysis
+            with torch.cuda.stream(self.s_ana):
+                if slot.used:
+                    self.s_ana.wait_event(slot.net_done)           # the forward that read slot.rows has finished
+                if packed.device.type == "cpu":
+                    slot.packed.copy_(packed, non_blocking=True)
+                    states = slot.packed
+                else:
+                    states = packed
+                    self.s_ana.wait_stream(torch.cuda.current_stream())       # whoever produced `packed`
+                _cabi.check(L.rag_features_analyze(_ptr(states), self.n, self.size, 2, _ptr(slot.fws), slot.fws.numel(),
+                                                   vp(self.s_ana.cuda_stream)))
+                slot.ana_done.record(self.s_ana)
+            # stage 1b: ladder reader + emit pixel rows
+            with torch.cuda.stream(self.s_feat):
+                self.s_feat.wait_event(slot.ana_done)
+                _cabi.check(L.rag_features_ladders(_ptr(states), self.n, self.size, _ptr(slot.fws), slot.fws.numel(),
+                                                   vp(self.s_feat.cuda_stream)))
+                _cabi.check(L.rag_features_emit(_ptr(slot.fws), self.n, self.size, src, len(self.plane_src), LAYOUT_CONV_IN,
+                                                self.dtype_code, self.pad, self.channels, _ptr(slot.rows),
+                                                vp(self.s_feat.cuda_stream)))
+                slot.feat_done.record(self.s_feat)
+            # stage 2: convolutions + head
+            with torch.cuda.stream(self.s_net):
+                self.s_net.wait_event(slot.feat_done)
+                if slot.used:
+                    self.s_net.wait_event(slot.out_copied)         # the previous result of this slot has been copied out
+                _cabi.check(L.rag_net_forward_rows(self.handle, _ptr(slot.rows), self.n, _ptr(slot.out), _ptr(self.nws),
+                                                   self.nws.numel(), vp(self.s_net.cuda_stream)))
+                slot.net_done.record(self.s_net)
+            with torch.cuda.stream(self.s_copy):
+                self.s_copy.wait_event(slot.net_done)
+                if to_host:
+                    slot.host_out.copy_(slot.out, non_blocking=True)
+                slot.out_copied.record(self.s_copy)
+        slot.used = True
+        slot.to_host = to_host
+        self.count += 1
+        return k
+
+    def result(self, ticket):
+        """Waits for batch `ticket` (must be one of the last two submitted) and returns its output:
+        the pinned host tensor if it was submitted with to_host=True, else the device tensor."""
+        if ticket < self.count - 2 or ticket >= self.count:
+            raise ValueError("ticket %d is no longer (or not yet) in flight" % ticket)
+        slot = self.slots[ticket % 2]
+        slot.out_copied.synchronize()
+        return slot.host_out if slot.to_host else slot.out
+
+    def mark(self):
+        """A CUDA event recorded behind everything submitted so far (for timing)."""
+        ev = torch.cuda.Event(enable_timing=True)
+        with torch.cuda.device(self.device):
+            for st in (self.s_ana, self.s_feat, self.s_net):
+                self.s_copy.wait_stream(st)
+            ev.record(self.s_copy)
+            self.s_ana.wait_event(ev)           # later submissions start after the mark
+        return ev
+
+    def drain(self):
+        for s in (self.s_ana, self.s_feat, self.s_net, self.s_copy):
+            s.synchronize()

@@ -22,18 +22,23 @@ def lib():
         L.hostsim_features.restype = ctypes.c_int
         L.hostsim_features.argtypes = [ctypes.c_int, ctypes.c_int, np.ctypeslib.ndpointer(np.int8, flags="C"),
                                        np.ctypeslib.ndpointer(np.int16, flags="C"), i32p, i32p,
-                                       np.ctypeslib.ndpointer(np.uint8, flags="C"), ctypes.c_void_p]
+                                       np.ctypeslib.ndpointer(np.uint8, flags="C"), ctypes.c_void_p, ctypes.c_void_p,
+                                       ctypes.c_int64]
         _lib = L
     return _lib
 
 
-def features49(board, age, ko, player):
+def features49(board, age, ko, player, item_cap=0):
     """uint8 (n, 49, S, S): the 48 default planes + legal, computed by the lane-emulated device code."""
     board = np.ascontiguousarray(board, np.int8)
     n, S = board.shape[0], board.shape[-1]
     out = np.empty((n, 49, S, S), np.uint8)
-    stats = np.zeros(2, np.int64)
+    stats = np.zeros(16, np.int64)
+    items = np.zeros(item_cap, np.int64) if item_cap else None
     lib().hostsim_features(n, S, board.reshape(n, -1), np.ascontiguousarray(age, np.int16).reshape(n, -1),
                            np.ascontiguousarray(ko, np.int32), np.ascontiguousarray(player, np.int32),
-                           out.reshape(-1), stats.ctypes.data_as(ctypes.c_void_p))
+                           out.reshape(-1), stats.ctypes.data_as(ctypes.c_void_p),
+                           items.ctypes.data_as(ctypes.c_void_p) if item_cap else None, item_cap)
+    if item_cap:
+        return out, stats, items[:min(item_cap, int(stats[3]))]
     return out, stats

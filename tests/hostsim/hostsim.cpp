@@ -13,7 +13,7 @@
 using namespace rag;
 
 extern "C" int hostsim_features(int n, int S, const int8_t* board, const int16_t* age, const int32_t* ko,
-                                const int32_t* player, uint8_t* out, int64_t* stats)
+                                const int32_t* player, uint8_t* out, int64_t* stats, int64_t* item_nodes, int64_t item_cap)
 {
     const int np = S * S;
     Geo g = make_geo(S);
@@ -46,7 +46,14 @@ extern "C" int hostsim_features(int n, int S, const int8_t* board, const int16_t
                 int q = bb_first(rem);
                 if (q < 0) break;
                 rem = andnot(rem, bb_single(q, g));
-                bool r = ladder_root(g, own, opp, ko_q, q, kind == 1, *lst);
+                long long n0 = g_ladder_stats.nodes; g_ladder_stats.max_depth = 0;
+                bool r = ladder_root(g, own, opp, ko_q, q, kind == 1, -1, *lst) == kLadderValue1;
+                if (stats) {
+                    long long dn = g_ladder_stats.nodes - n0;
+                    stats[2] += dn; stats[3] += 1;
+                    if (dn > stats[4]) { stats[4] = dn; stats[5] = b; stats[6] = q; stats[7] = kind; stats[8] = g_ladder_stats.max_depth; }
+                    if (item_nodes && stats[3] <= item_cap) item_nodes[stats[3] - 1] = dn;
+                }
                 if (r) planes[(kind ? kPlaneLadderEscape : kPlaneLadderCapture) * 32 + (q >> 5)] |= 1u << (q & 31);
             }
         }
@@ -80,4 +87,35 @@ extern "C" int hostsim_play(int S, int8_t* board, int32_t* ko, int32_t* player, 
     *ko = ko_q < 0 ? -1 : (ko_q >> 5) * S + (ko_q & 31);
     *player = -*player;
     return 0;
+}
+
+// ---- experiment: how many DISTINCT (position, side, move) nodes does one ladder search visit?
+#include <unordered_set>
+#include <string>
+static std::unordered_set<std::string>* g_seen = nullptr;
+static void seen_hook(const uint32_t* h, const uint32_t* p, int ko, int is_capture, int mv) {
+    std::string k((const char*)h, 19 * 4);
+    k.append((const char*)p, 19 * 4);
+    k.append((const char*)&ko, 4); k.append((const char*)&is_capture, 4); k.append((const char*)&mv, 4);
+    g_seen->insert(k);
+}
+extern "C" long long hostsim_ladder_distinct(int S, const int8_t* board, int ko, int player, int q, int kind, long long* nodes, long long* per_depth)
+{
+    for (int i = 0; i < 96; i++) g_ladder_stats.per_depth[i] = 0;
+    g_ladder_stats.cur_depth = 0;
+    Geo g = make_geo(S);
+    BB own = bb_zero(), opp = bb_zero();
+    for (int x = 0; x < S; x++) for (int y = 0; y < S; y++) {
+        int v = board[x * S + y];
+        if (v == player) own.w[x] |= 1u << y; else if (v) opp.w[x] |= 1u << y;
+    }
+    int ko_q = ko < 0 ? -1 : ((ko / S) << 5) | (ko % S);
+    std::unordered_set<std::string> seen; g_seen = &seen; g_ladder_node_hook = seen_hook;
+    LadderStack* lst = (LadderStack*)malloc(sizeof(LadderStack));
+    long long n0 = g_ladder_stats.nodes;
+    ladder_root(g, own, opp, ko_q, q, kind == 1, -1, *lst);
+    *nodes = g_ladder_stats.nodes - n0;
+    if (per_depth) for (int i = 0; i < 96; i++) per_depth[i] = g_ladder_stats.per_depth[i];
+    g_ladder_node_hook = nullptr; free(lst);
+    return (long long)seen.size();
 }

@@ -256,3 +256,29 @@ def test_errors_come_back_as_exceptions():
         CNNPolicy(["board"], layers=2, filters_per_layer=512, seed=1).forward(np.zeros((1, 3, 19, 19), np.float32))
     assert net.forward(np.zeros((0, 3, 19, 19), np.float32)).shape == (0, 361)
     assert torch.cuda.is_available()
+
+
+def test_two_stream_pipeline_gives_the_same_results():
+    """rocalphago_b200/pipeline.py only re-schedules the same entry points; outputs are identical
+    to the single-stream fused call, for device-resident and for host (pinned) inputs."""
+    from rocalphago_b200.pipeline import EvalPipeline
+    n = 96
+    net = CNNPolicy(go_oracle.DEFAULT_FEATURES, layers=4, filters_per_layer=64, dtype="fp16", seed=31)
+    batches = [BatchedGameState.random_playouts(n, seed=500 + i, max_ply=300, stride=4) for i in range(5)]
+    want = [net.model.eval_batch_device(b, net.preprocessor.plane_src).cpu().numpy() for b in batches]
+    pipe = EvalPipeline(net, n)
+    tickets, got = [], {}
+    for i, b in enumerate(batches):
+        src = b.packed if i % 2 == 0 else b.packed.cpu().pin_memory()
+        t = pipe.submit(src, to_host=(i % 2 == 1))
+        tickets.append(t)
+        if i >= 1:
+            got[tickets[i - 1]] = pipe.result(tickets[i - 1]).clone().cpu().numpy()
+    got[tickets[-1]] = pipe.result(tickets[-1]).clone().cpu().numpy()
+    pipe.drain()
+    for i in range(5):
+        assert np.array_equal(got[i], want[i]), i
+    with pytest.raises(ValueError):
+        pipe.result(0)                                          # long gone
+    with pytest.raises(ValueError):
+        pipe.submit(batches[0].packed[:10])
