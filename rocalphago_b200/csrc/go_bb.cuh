@@ -224,15 +224,20 @@ RAG_FN int q_diagonal(int q, int i, int S) {
 // the "stale ko" of SURVEY H3, comes out the same (go.py:542-561).
 RAG_FN bool bb_play(const Geo& g, BB& M, BB& O, int& ko, int q, int* captured) {
     if (q == ko) return false;
-    BB pt = bb_single(q, g);
+    const BB pt = bb_single(q, g);
     if (bb_any((M | O) & pt)) return false;
-    BB M2 = M | pt, O2 = O;
+    const BB M2 = M | pt;
+    BB O2 = O;
     int newko = -1, ncap = 0;
-    BB ptn = bb_nbrs(pt, g);
-    if (bb_any(ptn & O)) {
+    const BB ptn = bb_nbrs(pt, g);
+    const BB empty2 = andnot(bb_board(g), M2 | O);
+    // Only an enemy neighbour with no empty point next to that very stone can be captured;
+    // most moves have none, and then no group needs to be traced at all.
+    const BB maybe = andnot(ptn & O, bb_nbrs(empty2, g));
+    if (bb_any(maybe)) {
         for (int d = 0; d < 4; d++) {
             int nq = q_neighbor(q, d, g.S);
-            if (nq < 0 || !bb_test(O2, nq)) continue;
+            if (nq < 0 || !bb_test(maybe & O2, nq)) continue;
             BB grp = bb_flood(bb_single(nq, g), O2, g);
             BB empty = andnot(bb_board(g), M2 | O2);
             if (bb_any(bb_nbrs(grp, g) & empty)) continue;
@@ -248,8 +253,12 @@ RAG_FN bool bb_play(const Geo& g, BB& M, BB& O, int& ko, int q, int* captured) {
             }
         }
     }
-    BB me = bb_flood(pt, M2, g);
-    if (!bb_any(bb_nbrs(me, g) & andnot(bb_board(g), M2 | O2))) return false;   // suicide, go.py:219-240
+    // suicide (go.py:219-240): a capture or an empty neighbour leaves the stone a liberty;
+    // otherwise the group it joined must have one somewhere
+    if (ncap == 0 && !bb_any(ptn & empty2)) {
+        BB me = bb_flood(pt, M2, g);
+        if (!bb_any(bb_nbrs(me, g) & empty2)) return false;
+    }
     M = M2; O = O2; ko = newko;
     if (captured) *captured = ncap;
     return true;
@@ -481,6 +490,7 @@ RAG_FN bool bb_do_move(const Geo& g, FullState& s, int q) {
 struct LadderStack {
     BB hunter[kLadderDepth];
     BB prey[kLadderDepth];
+    BB group[kLadderDepth];      // the prey group itself, carried along instead of re-traced
     BB pending[kLadderDepth];
     int16_t ko[kLadderDepth];
 };
@@ -506,7 +516,7 @@ static void (*g_ladder_node_hook)(const uint32_t* h32, const uint32_t* p32, int 
 //   escape node  (go.py:413-460): prey plays; >=3 liberties -> 1, 1 liberty -> 0, else
 //       replies = the two liberties; value = no reply is a ladder capture.
 // `remaining` is the reference's remaining_attempts; legality is tested before it (H11).
-RAG_FN int ladder_expand(const Geo& g, bool is_capture, BB& H, BB& P, int& ko, int mv, int prey_q,
+RAG_FN int ladder_expand(const Geo& g, bool is_capture, BB& H, BB& P, BB& G, int& ko, int mv,
                          int remaining, BB& pending) {
     RAG_LADDER_COUNT_NODE();
 #if !RAG_DEVICE_BUILD
@@ -515,13 +525,28 @@ RAG_FN int ladder_expand(const Geo& g, bool is_capture, BB& H, BB& P, int& ko, i
     bool ok = is_capture ? bb_play(g, H, P, ko, mv, nullptr) : bb_play(g, P, H, ko, mv, nullptr);
     if (!ok) return kLadderValue0;
     if (remaining <= 0) return is_capture ? kLadderValue1 : kLadderValue0;
-    BB empty = andnot(bb_board(g), H | P);
-    BB grp = bb_flood(bb_single(prey_q, g), P, g);
-    BB gn = bb_nbrs(grp, g);
-    BB libs = gn & empty;
+    const BB empty = andnot(bb_board(g), H | P);
+    if (!is_capture) {
+        // The prey side moved.  Its group G grows only if the new stone touches it (a reply can
+        // also be a capture elsewhere); other groups of its colour the stone touches join too.
+        // A hunter move never changes G: the group keeps a liberty, so it is not what is captured.
+        const BB pt = bb_single(mv, g), ptn = bb_nbrs(pt, g);
+        if (bb_any(ptn & G)) {
+            const BB extra = andnot(ptn & P, G);
+            G = G | pt;
+            if (bb_any(extra)) G = G | bb_flood(extra, P, g);
+        }
+    }
+    const BB gn = bb_nbrs(G, g);
+    const BB libs = gn & empty;
     if (is_capture) {
         pending = libs;
-        BB rem = gn & H;
+        // hunter groups in atari that touch the prey (go.py:381-384).  A stone with two empty
+        // neighbours of its own cannot be in such a group, so only the others are traced.
+        const BB a = bb_from_north(empty, g, false), b = bb_from_south(empty, g, false);
+        const BB c = bb_from_west(empty, g, false), d = bb_from_east(empty, g, false);
+        const BB ge2 = (a & b) | (c & d) | ((a | b) & (c | d));
+        BB rem = andnot(gn & H, ge2);
         for (;;) {
             int h = bb_first(rem);
             if (h < 0) break;
@@ -562,10 +587,10 @@ __device__ __noinline__
 #else
 static
 #endif
-int ladder_dfs(const Geo& g, BB H, BB P, int ko, BB pending, int prey_q, bool frame_is_capture,
-                               int remaining_children, int budget, int nodes, LadderStack& st, Cancel cancel) {
+int ladder_dfs(const Geo& g, BB H, BB P, BB G, int ko, BB pending, bool frame_is_capture,
+               int remaining_children, int budget, int nodes, LadderStack& st, Cancel cancel) {
     int d = 0;
-    st.hunter[0] = H; st.prey[0] = P; st.pending[0] = pending; st.ko[0] = (int16_t)ko;
+    st.hunter[0] = H; st.prey[0] = P; st.group[0] = G; st.pending[0] = pending; st.ko[0] = (int16_t)ko;
     for (;;) {
         int v;
         int m = bb_first(st.pending[d]);
@@ -576,15 +601,15 @@ int ladder_dfs(const Geo& g, BB H, BB P, int ko, BB pending, int prey_q, bool fr
             nodes++;
             st.pending[d] = andnot(st.pending[d], bb_single(m, g));
             bool node_is_capture = frame_is_capture ^ ((d & 1) != 0);
-            H = st.hunter[d]; P = st.prey[d]; ko = st.ko[d];
+            H = st.hunter[d]; P = st.prey[d]; G = st.group[d]; ko = st.ko[d];
 #if !RAG_DEVICE_BUILD
             g_ladder_stats.cur_depth = d + 1;
 #endif
-            int res = ladder_expand(g, !node_is_capture, H, P, ko, m, prey_q, remaining_children - d, pending);
+            int res = ladder_expand(g, !node_is_capture, H, P, G, ko, m, remaining_children - d, pending);
             if (res == kLadderPush) {
                 d++;
                 RAG_LADDER_DEPTH(d);
-                st.hunter[d] = H; st.prey[d] = P; st.pending[d] = pending; st.ko[d] = (int16_t)ko;
+                st.hunter[d] = H; st.prey[d] = P; st.group[d] = G; st.pending[d] = pending; st.ko[d] = (int16_t)ko;
                 continue;
             }
             if (res == kLadderValue0) continue;              // this reply does not refute; try the next
@@ -599,19 +624,19 @@ int ladder_dfs(const Geo& g, BB H, BB P, int ko, BB pending, int prey_q, bool fr
     }
 }
 
-RAG_FN int ladder_search(const Geo& g, BB H, BB P, int ko, int first_move, int prey_q,
+// is_ladder_capture / is_ladder_escape of `first_move` on the prey group G (go.py:329-463).
+RAG_FN int ladder_search(const Geo& g, BB H, BB P, BB G, int ko, int first_move,
                          bool root_is_capture, int remaining0, int budget, LadderStack& st) {
     BB pending = bb_zero();
-    int res = ladder_expand(g, root_is_capture, H, P, ko, first_move, prey_q, remaining0, pending);
+    int res = ladder_expand(g, root_is_capture, H, P, G, ko, first_move, remaining0, pending);
     if (res != kLadderPush) return res;
-    return ladder_dfs(g, H, P, ko, pending, prey_q, root_is_capture, remaining0 - 1, budget, 1, st, NeverCancel());
+    return ladder_dfs(g, H, P, G, ko, pending, root_is_capture, remaining0 - 1, budget, 1, st, NeverCancel());
 }
 
 // The prey groups is_ladder_capture(action) / is_ladder_escape(action) look at when called with
 // prey=None (go.py:355-361, 422-428): adjacent opponent groups with exactly two liberties
-// (capture) / own groups with exactly one (escape), each once.  Returns how many; prey_out[i] is
-// a stone of the i-th group.
-RAG_FN int ladder_root_preys(const Geo& g, BB own, BB opp, int action_q, bool is_escape, int prey_out[4]) {
+// (capture) / own groups with exactly one (escape), each once.  Returns how many.
+RAG_FN int ladder_root_preys(const Geo& g, BB own, BB opp, int action_q, bool is_escape, BB groups_out[4]) {
     const BB side = is_escape ? own : opp;
     const BB empty = andnot(bb_board(g), own | opp);
     const int want = is_escape ? 1 : 2;
@@ -619,10 +644,10 @@ RAG_FN int ladder_root_preys(const Geo& g, BB own, BB opp, int action_q, bool is
     int n = 0;
     for (int d = 0; d < 4; d++) {
         int nq = q_neighbor(action_q, d, g.S);
-        if (nq < 0 || !bb_test(side, nq) || bb_test(done, nq)) continue;
+        if (nq < 0 || !bb_test(andnot(side, done), nq)) continue;
         BB grp = bb_flood(bb_single(nq, g), side, g);
         done = done | grp;
-        if (bb_count(bb_nbrs(grp, g) & empty) == want) prey_out[n++] = nq;
+        if (bb_count(bb_nbrs(grp, g) & empty) == want) groups_out[n++] = grp;
     }
     return n;
 }
@@ -631,12 +656,12 @@ RAG_FN int ladder_root_preys(const Geo& g, BB own, BB opp, int action_q, bool is
 // for ANY of those groups.  Returns 0, 1, or kLadderAborted when a search ran out of `budget`.
 RAG_FN_NOINLINE int ladder_root(const Geo& g, BB own, BB opp, int ko, int action_q, bool is_escape,
                                 int budget, LadderStack& st) {
-    int preys[4];
+    BB preys[4];
     const int np = ladder_root_preys(g, own, opp, action_q, is_escape, preys);
     for (int i = 0; i < np; i++) {
         // capture: side to move hunts `opp`; escape: side to move is the prey
-        int r = is_escape ? ladder_search(g, opp, own, ko, action_q, preys[i], false, kLadderDepth, budget, st)
-                          : ladder_search(g, own, opp, ko, action_q, preys[i], true, kLadderDepth, budget, st);
+        int r = is_escape ? ladder_search(g, opp, own, preys[i], ko, action_q, false, kLadderDepth, budget, st)
+                          : ladder_search(g, own, opp, preys[i], ko, action_q, true, kLadderDepth, budget, st);
         if (r != kLadderValue0) return r;
     }
     return kLadderValue0;
