@@ -189,6 +189,7 @@ def run_gpu(args):
     plane_src = net.preprocessor.plane_src
     h = model._ensure_handle(dev)
     _cabi.check(L.rag_net_set_profiling(h, 1))
+    L.rag_set_conv_pair(args.conv_pair)
 
     # synthetic inputs: `pool` distinct batches of random-playout positions generated on the device
     pool = max(2, args.pool)
@@ -232,6 +233,9 @@ def run_gpu(args):
         serial_ms = sum(a.elapsed_time(b) for a, b in ev) / K
         del ws, flush
 
+    if args.no_pipeline:
+        print(json.dumps({"serial_ms_per_step": serial_ms, "conv_pair": args.conv_pair}))
+        return
     pipe = EvalPipeline(net, n, device=dev)
     for i in range(W):
         pipe.submit(batches[i % pool].packed)
@@ -246,7 +250,9 @@ def run_gpu(args):
     e0 = pipe.mark()
     for k in range(K):
         pipe.submit(batches[k % pool].packed)
-        if K >= 8 and k in (K // 3, 2 * K // 3):          # two samples of the per-layer events (each costs one pipeline bubble)
+        if os.environ.get("BENCH_TRACE"):
+            print("submitted", k, file=sys.stderr, flush=True)
+        if K >= 8 and k in (K // 3, 2 * K // 3) and not os.environ.get("BENCH_NO_SAMPLE"):   # two samples of the per-layer events (each costs one pipeline bubble)
             layer_ms += layer_times(); samples += 1
     e1 = pipe.mark()
     pipe.drain()
@@ -344,6 +350,8 @@ def main():
     ap.add_argument("--ref-sample", type=int, default=256)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--serial", action="store_true", help="also time the single-stream rag_eval_batch step")
+    ap.add_argument("--conv-pair", type=int, default=1, help="0: one CTA per tile; 1: CTA pairs (cta_group::2)")
+    ap.add_argument("--no-pipeline", action="store_true", help="debug: skip the pipelined passes")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

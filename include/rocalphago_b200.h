@@ -206,6 +206,10 @@ long long rag_net_input_rows(const rag_net* net, int n);
 int rag_net_input_channels(const rag_net* net);
 int rag_net_input_pad(const rag_net* net);
 
+/* Tuning/test knob (process-wide): 1 = convolutions run on CTA pairs (tcgen05 cta_group::2, the
+ * default), 0 = one CTA per tile.  Results are identical.  Returns the previous setting. */
+int rag_set_conv_pair(int enable);
+
 /* Measurement aid: with profiling on, every forward records a CUDA event on its stream before
  * each convolution launch and after the last; rag_net_layer_times then gives the device time
  * of each of the `layers` convolution kernels of the most recent forward (waits for it).

@@ -118,13 +118,51 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
 }
 
 // kind::f16 instruction descriptor (cute::UMMA::InstrDescriptor): fp32 accumulate, K-major A and B
-__device__ __forceinline__ uint32_t umma_idesc(int dtype, int N) {
+__device__ __forceinline__ uint32_t umma_idesc(int dtype, int N, int M) {
     uint32_t fmt = dtype == RAG_DTYPE_BF16 ? 1u : 0u;
-    return (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(kTileM >> 4) << 24);
+    return (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
 // ---- the convolution kernel --------------------------------------------------------------------
+//
+// kPair = false: one CTA per tile of 128 rows (cta_group::1).
+// kPair = true : two CTAs of a cluster share one 256-row tile (cta_group::2).  Each CTA loads its
+//     own 128 rows of A and HALF of the weight tile (N/2 rows of B); the leader CTA issues one
+//     M=256 UMMA that reads both halves, and each CTA's TMEM receives its own 128 rows.  Per SM
+//     that halves the shared-memory traffic of the weights -- the resource this kernel runs out of
+//     first (each 40 KB stage is written once by TMA and read once by four UMMAs).
 
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t leader_bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(map), "r"(leader_bar), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tc_commit_pair(uint32_t bar) {      // arrives on the same barrier in both CTAs
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(bar), "h"((uint16_t)3) : "memory");
+}
+__device__ __forceinline__ void tc_mma_f16_pair(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t"
+        "}" ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_leader(uint32_t local_bar) {   // arrive on CTA 0's copy of the barrier
+    uint32_t remote;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local_bar), "r"(0));
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory");
+}
+constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;   // shared::cluster address of the same offset in CTA 0 of the pair
+
+template <bool kPair>
 __global__ void __launch_bounds__(kConvThreads, 1)
 conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const ConvParams p)
@@ -133,7 +171,8 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const uint32_t raw = smem_u32(smem_raw);
     const uint32_t base = (raw + 1023u) & ~1023u;                 // SWIZZLE_128B tiles need 1024-byte alignment
     uint8_t* smem = smem_raw + (base - raw);
-    const uint32_t stage_bytes = kATileBytes + (uint32_t)p.N * 128u;
+    const uint32_t b_rows = kPair ? (uint32_t)p.N / 2u : (uint32_t)p.N;       // rows of B this CTA holds
+    const uint32_t stage_bytes = kATileBytes + b_rows * 128u;
     uint8_t* after = smem + (size_t)p.stages * stage_bytes;
     uint64_t* bars = reinterpret_cast<uint64_t*>(after);          // full[stages], empty[stages], tfull[2], tempty[2]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * p.stages + 4);
@@ -141,6 +180,10 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     float* s_head = s_bias + p.N;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = kPair ? cluster_ctarank() : 0u;
+    const int n_workers = kPair ? (int)gridDim.x / 2 : (int)gridDim.x;        // tiles are dealt round-robin to CTAs / pairs
+    const int worker = kPair ? (int)blockIdx.x / 2 : (int)blockIdx.x;
+    const int rows_per_tile = kPair ? 2 * kTileM : kTileM;
     const uint32_t bar0 = smem_u32(bars);
     auto full_bar = [&](int s) { return bar0 + 8u * (uint32_t)s; };
     auto empty_bar = [&](int s) { return bar0 + 8u * (uint32_t)(p.stages + s); };
@@ -149,12 +192,17 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < p.stages; s++) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
-        for (int a = 0; a < 2; a++) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 4); }
+        for (int a = 0; a < 2; a++) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), kPair ? 8 : 4); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(kTmemCols));
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        if (kPair) {
+            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(kTmemCols));
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+        } else {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(kTmemCols));
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        }
     }
     for (int i = threadIdx.x; i < p.N; i += blockDim.x) {
         s_bias[i] = p.bias[i];
@@ -162,6 +210,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
     tc_fence_before();
     __syncthreads();
+    if (kPair) cluster_sync_all();                                 // the peer's barriers exist before anyone signals them
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     const int kblocks = p.taps * p.kchunks;
@@ -170,27 +219,35 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         // ===== TMA producer =====
         if (lane == 0) {
             uint32_t it = 0;
-            for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) {
-                const int r0 = kConvLeadRows + tile * kTileM;
+            for (int tile = worker; tile < p.tiles; tile += n_workers) {
+                const int r0 = kConvLeadRows + tile * rows_per_tile + (int)rank * kTileM;
                 for (int t = 0; t < p.taps; t++) {
                     for (int c = 0; c < p.kchunks; c++, it++) {
                         const int s = (int)(it % (uint32_t)p.stages);
                         const uint32_t ph = (it / (uint32_t)p.stages) & 1u;
                         mbar_wait(empty_bar(s), ph ^ 1u);
                         const uint32_t sa = base + (uint32_t)s * stage_bytes;
-                        mbar_expect_tx(full_bar(s), stage_bytes);
-                        tma_load_2d(sa, &tmA, c * kChunkK, r0 + p.shift[t], full_bar(s));
-                        tma_load_2d(sa + kATileBytes, &tmB, c * kChunkK, t * p.N, full_bar(s));
+                        if (kPair) {
+                            // both CTAs' bytes are counted on the leader's barrier
+                            if (rank == 0) mbar_expect_tx(full_bar(s), 2u * stage_bytes);
+                            const uint32_t lb = full_bar(s) & kPeerBitMask;
+                            tma_load_2d_pair(sa, &tmA, c * kChunkK, r0 + p.shift[t], lb);
+                            tma_load_2d_pair(sa + kATileBytes, &tmB, c * kChunkK, t * p.N + (int)(rank * b_rows), lb);
+                        } else {
+                            mbar_expect_tx(full_bar(s), stage_bytes);
+                            tma_load_2d(sa, &tmA, c * kChunkK, r0 + p.shift[t], full_bar(s));
+                            tma_load_2d(sa + kATileBytes, &tmB, c * kChunkK, t * p.N, full_bar(s));
+                        }
                     }
                 }
             }
         }
     } else if (warp == 1) {
-        // ===== MMA issuer =====
-        if (lane == 0) {
-            const uint32_t idesc = umma_idesc(p.dtype, p.N);
+        // ===== MMA issuer (the leader CTA's, for a pair) =====
+        if (lane == 0 && rank == 0) {
+            const uint32_t idesc = umma_idesc(p.dtype, p.N, rows_per_tile);
             uint32_t it = 0, lt = 0;
-            for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, lt++) {
+            for (int tile = worker; tile < p.tiles; tile += n_workers, lt++) {
                 const uint32_t a = lt & 1u, aph = (lt >> 1) & 1u;
                 mbar_wait(tempty_bar((int)a), aph ^ 1u);
                 tc_fence_after();
@@ -203,21 +260,23 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     const uint32_t sa = base + (uint32_t)s * stage_bytes;
                     const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + kATileBytes);
                     #pragma unroll
-                    for (int k = 0; k < kChunkK / 16; k++)        // +32 bytes along K inside the swizzled row
-                        tc_mma_f16(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((kb | k) != 0));
-                    tc_commit(empty_bar(s));                       // frees the stage once these MMAs have read it
+                    for (int k = 0; k < kChunkK / 16; k++) {      // +32 bytes along K inside the swizzled row
+                        if (kPair) tc_mma_f16_pair(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((kb | k) != 0));
+                        else tc_mma_f16(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((kb | k) != 0));
+                    }
+                    if (kPair) tc_commit_pair(empty_bar(s)); else tc_commit(empty_bar(s));   // frees the stage (in both CTAs)
                 }
-                tc_commit(tfull_bar((int)a));                      // accumulator complete
+                if (kPair) tc_commit_pair(tfull_bar((int)a)); else tc_commit(tfull_bar((int)a));   // accumulator complete
             }
         }
     } else {
         // ===== epilogue =====
         const int quarter = warp & 3;                              // TMEM lanes this warp may read
         uint32_t lt = 0;
-        for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, lt++) {
+        for (int tile = worker; tile < p.tiles; tile += n_workers, lt++) {
             const uint32_t a = lt & 1u, aph = (lt >> 1) & 1u;
             // which pixel is my row?
-            const long long rel = (long long)tile * kTileM + quarter * 32 + lane;
+            const long long rel = (long long)tile * rows_per_tile + (long long)rank * kTileM + quarter * 32 + lane;
             const int spp = p.Sp_in * p.Sp_in;
             const int pos = (int)(rel / spp), rem = (int)(rel - (long long)pos * spp);
             const int x = rem / p.Sp_in, y = rem - x * p.Sp_in;
@@ -274,14 +333,16 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(tempty_bar((int)a));
+            if (lane == 0) { if (kPair) mbar_arrive_leader(tempty_bar((int)a)); else mbar_arrive(tempty_bar((int)a)); }
         }
     }
     tc_fence_before();
     __syncthreads();
+    if (kPair) cluster_sync_all();                                 // nobody frees TMEM or leaves while the peer still uses it
     if (warp == 1) {
         tc_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols));
+        if (kPair) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols));
+        else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols));
     }
 }
 
@@ -430,6 +491,8 @@ static size_t conv_smem_bytes(int N, int stages) {
     return 1024 + (size_t)stages * (kATileBytes + (size_t)N * 128) + (2 * stages + 4) * 8 + 16 + 2 * (size_t)N * 4;
 }
 
+static int g_conv_pair = 1;      // rag_set_conv_pair: use CTA pairs (cta_group::2) where the layer allows
+
 static int pick_stages(int N) {
     for (int st = 6; st >= 2; st--)
         if (conv_smem_bytes(N, st) <= 225 * 1024) return st;
@@ -506,14 +569,34 @@ static int run_layers(rag_net* net, const uint16_t* d_in, int n, float* d_out, c
         for (int i = 0; i < ly.width; i++)
             for (int j = 0; j < ly.width; j++) p.shift[i * ly.width + j] = (i - pad_in) * Sp_in + (j - pad_in);
 
+        // a CTA pair (cta_group::2) needs an even split of the weight tile into 8-row groups
+        const bool pair = g_conv_pair && (ly.n_pad % 32 == 0) && net->sms >= 2;
+        if (pair) {
+            p.tiles = (int)((p.body_rows + 2 * kTileM - 1) / (2 * kTileM));
+            p.stages = pick_stages(ly.n_pad / 2);
+        }
         CUtensorMap tmA, tmB;
         if (int rc = make_map(&tmA, cur, conv_rows(n, S, pad_in), ly.cin_pad, kTileM, net->desc.dtype)) return rc;
-        if (int rc = make_map(&tmB, ly.d_w, (long long)ly.taps * ly.n_pad, ly.cin_pad, ly.n_pad, net->desc.dtype)) return rc;
-        const size_t smem = conv_smem_bytes(ly.n_pad, p.stages);
-        RAG_CUDA_CHECK(cudaFuncSetAttribute(conv_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        const int grid = p.tiles < net->sms ? p.tiles : net->sms;
+        if (int rc = make_map(&tmB, ly.d_w, (long long)ly.taps * ly.n_pad, ly.cin_pad, pair ? ly.n_pad / 2 : ly.n_pad, net->desc.dtype)) return rc;
         if (net->profiling) RAG_CUDA_CHECK(cudaEventRecord(net->events[l], s));
-        conv_umma_kernel<<<grid, kConvThreads, smem, s>>>(tmA, tmB, p);
+        if (pair) {
+            const size_t smem = conv_smem_bytes(ly.n_pad / 2, p.stages) + (size_t)ly.n_pad * 4;      // bias/head tables are N wide
+            RAG_CUDA_CHECK(cudaFuncSetAttribute(conv_umma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            const int pairs = p.tiles < net->sms / 2 ? p.tiles : net->sms / 2;
+            cudaLaunchConfig_t cfg;
+            memset(&cfg, 0, sizeof cfg);
+            cfg.gridDim = dim3(2 * pairs); cfg.blockDim = dim3(kConvThreads); cfg.dynamicSmemBytes = smem; cfg.stream = s;
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeClusterDimension;
+            attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+            cfg.attrs = attr; cfg.numAttrs = 1;
+            RAG_CUDA_CHECK(cudaLaunchKernelEx(&cfg, conv_umma_kernel<true>, tmA, tmB, p));
+        } else {
+            const size_t smem = conv_smem_bytes(ly.n_pad, p.stages);
+            RAG_CUDA_CHECK(cudaFuncSetAttribute(conv_umma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            const int grid = p.tiles < net->sms ? p.tiles : net->sms;
+            conv_umma_kernel<false><<<grid, kConvThreads, smem, s>>>(tmA, tmB, p);
+        }
         RAG_CUDA_CHECK(cudaGetLastError());
         if (net->profiling && last) RAG_CUDA_CHECK(cudaEventRecord(net->events[L], s));
         cur = dst;
@@ -658,6 +741,8 @@ size_t rag_net_workspace_bytes(const rag_net* net, int n)
     if (!net || n <= 0) return 0;
     return carve_net(net, n, nullptr, true).total;
 }
+
+int rag_set_conv_pair(int enable) { int old = g_conv_pair; g_conv_pair = enable != 0; return old; }
 
 int rag_net_set_profiling(rag_net* net, int enable)
 {

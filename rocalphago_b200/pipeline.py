@@ -59,13 +59,12 @@ class EvalPipeline(object):
         with torch.cuda.device(self.device):
             self.slots = [_Slot(self.L, self.handle, self.n, self.size, self.device, cols) for _ in range(2)]
             self.nws = torch.empty(int(self.L.rag_net_workspace_bytes(self.handle, self.n)), dtype=torch.uint8, device=self.device)
-            # Priorities decide who gets an SM when several kernels have CTAs pending.  The analysis
-            # kernel is short but needs shared memory a resident convolution CTA leaves no room for,
-            # so it goes first (it slips in at a layer boundary); the convolutions come next; the
-            # ladder reader and the emit -- no shared memory, mostly waiting -- fill in around them.
-            self.s_ana = torch.cuda.Stream(priority=-2)
-            self.s_net = torch.cuda.Stream(priority=-1)
-            self.s_feat, self.s_copy = torch.cuda.Stream(priority=0), torch.cuda.Stream(priority=0)
+            # All four streams have the same priority.  (Giving the convolutions a higher one looked
+            # attractive, but with the CTA-pair convolution kernel -- a cluster launch -- and the
+            # persistent ladder kernel in flight together, prioritised streams stopped making
+            # progress on B200 / driver 580; equal priorities never did in any run.)
+            self.s_ana, self.s_net = torch.cuda.Stream(), torch.cuda.Stream()
+            self.s_feat, self.s_copy = torch.cuda.Stream(), torch.cuda.Stream()
         self.pad = int(self.L.rag_net_input_pad(self.handle))
         self.channels = int(self.L.rag_net_input_channels(self.handle))
         self.dtype_code = 0 if self.model.dtype == "bf16" else 1
