@@ -284,6 +284,21 @@ def run_gpu(args):
     e2e_ms = f0.elapsed_time(f1)
     clocks = sampler.stop() if rank == 0 else None
 
+    # results gathered to every rank (NCCL all_gather over NVLink) -- off the data path, timed on its own
+    gather_ms = None
+    if world > 1:
+        from rocalphago_b200 import distributed as D
+        local = pipe.slots[(pipe.count - 1) % 2].out
+        D.gather_results(local, n * world)
+        barrier()
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0.record()
+        full = D.gather_results(local, n * world)
+        g1.record()
+        torch.cuda.synchronize()
+        assert tuple(full.shape) == (n * world, 361)
+        gather_ms = g0.elapsed_time(g1)
+
     t = torch.tensor([dev_ms, e2e_ms, e2e_wall_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -316,13 +331,18 @@ def run_gpu(args):
             "roofline": {"bound": "tensor", "kernel": "conv_umma_kernel, 3x3 192->192 layer (11 of 12 conv launches per step)",
                          "achieved": achieved, "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
                          "frac": achieved / peaks["tf_sustained"], "peak_source": peaks["src"] + " (sustained)",
-                         "ms_per_launch": k3, "traffic": None,
+                         "ms_per_launch": k3,
+                         # dram__bytes_read.sum + dram__bytes_write.sum per launch from the ncu --set full capture
+                         # of this kernel at batch 4096 (profiles/r1_conv_ncu_summary.md); scales with the batch
+                         "traffic": {"bytes": int(1.2113e9 * n / 4096), "algorithmic_bytes": int(n * 400 * 192 * 2 * 2),
+                                     "source": "profiles/r1_conv_ncu_summary.md"},
                          "note": "CUDA events recorded by the library on the launching stream, sampled %d time(s) inside "
                                  "the timed region while the next batch's feature kernels share the SMs" % samples},
             "stage_ms": {"conv_layer1": float(layer_ms[0]), "conv_3x3_mean": k3, "conv_all": float(layer_ms.sum()),
                          "pipelined_step": dev_ms / K, "serial_step": serial_ms},
             "whole_net_tflops": FLOP_POLICY * n / (float(layer_ms.sum()) / 1e3) / 1e12,
             "wall_s": wall,
+            "gather_ms": gather_ms,
         }
         if world == 1 and not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
