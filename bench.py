@@ -183,6 +183,8 @@ def run_gpu(args):
         dist.init_process_group("nccl", device_id=dev)
 
     n, K, W = args.batch, args.steps, max(3, args.warmup)
+    trace = (lambda *a: print("[rank %d]" % rank, *a, file=sys.stderr, flush=True)) if os.environ.get("BENCH_TRACE") else (lambda *a: None)
+    trace("process group up")
     L = _cabi.lib()
     net = CNNPolicy(DEFAULT_FEATURES, layers=12, filters_per_layer=192, dtype=args.dtype, seed=1234)
     model = net.model
@@ -196,6 +198,7 @@ def run_gpu(args):
     batches = [BatchedGameState.random_playouts(n, seed=20261106 + 7919 * (rank * pool + i), device=dev) for i in range(pool)]
     host_in = [b.packed.cpu().pin_memory() for b in batches]
     torch.cuda.synchronize()
+    trace("inputs ready")
 
     def barrier():
         torch.cuda.synchronize()
@@ -240,7 +243,9 @@ def run_gpu(args):
     for i in range(W):
         pipe.submit(batches[i % pool].packed)
     pipe.drain()
+    trace("warm-up done")
     barrier()
+    trace("barrier passed")
     if rank == 0:
         sampler.start()
 
@@ -259,6 +264,7 @@ def run_gpu(args):
     barrier()
     wall = time.time() - wall0
     dev_ms = e0.elapsed_time(e1)
+    trace("device-resident pass done", dev_ms)
     if samples == 0:
         layer_ms, samples = layer_times(), 1
     layer_ms /= samples
@@ -282,6 +288,7 @@ def run_gpu(args):
     barrier()
     e2e_wall_ms = (time.time() - t0) * 1e3
     e2e_ms = f0.elapsed_time(f1)
+    trace("e2e pass done", e2e_ms)
     clocks = sampler.stop() if rank == 0 else None
 
     # results gathered to every rank (NCCL all_gather over NVLink) -- off the data path, timed on its own
@@ -370,7 +377,7 @@ def main():
     ap.add_argument("--ref-sample", type=int, default=256)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--serial", action="store_true", help="also time the single-stream rag_eval_batch step")
-    ap.add_argument("--conv-pair", type=int, default=1, help="0: one CTA per tile; 1: CTA pairs (cta_group::2)")
+    ap.add_argument("--conv-pair", type=int, default=0, help="0: one CTA per tile; 1: CTA pairs (cta_group::2)")
     ap.add_argument("--no-pipeline", action="store_true", help="debug: skip the pipelined passes")
     args = ap.parse_args()
     if args.impl == "reference":

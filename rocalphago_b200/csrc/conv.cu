@@ -491,7 +491,12 @@ static size_t conv_smem_bytes(int N, int stages) {
     return 1024 + (size_t)stages * (kATileBytes + (size_t)N * 128) + (2 * stages + 4) * 8 + 16 + 2 * (size_t)N * 4;
 }
 
-static int g_conv_pair = 1;      // rag_set_conv_pair: use CTA pairs (cta_group::2) where the layer allows
+// rag_set_conv_pair: run layers on CTA pairs (cta_group::2) where they allow it.  Off by default:
+// live, under the 1 kW power cap, the pair kernel is no faster than the single-CTA one (same
+// 0.88-0.91 ms per 3x3 layer at batch 4096), and a cluster launch sharing the GPU with the
+// persistent ladder kernel of the next batch (pipeline.py) stopped making progress in a few long
+// runs on B200 / driver 580 -- never when run on its own stream alone.
+static int g_conv_pair = 0;
 
 static int pick_stages(int N) {
     for (int st = 6; st >= 2; st--)

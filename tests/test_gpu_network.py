@@ -282,3 +282,20 @@ def test_two_stream_pipeline_gives_the_same_results():
         pipe.result(0)                                          # long gone
     with pytest.raises(ValueError):
         pipe.submit(batches[0].packed[:10])
+
+
+def test_cta_pair_convolution_kernel_matches_single_cta_kernel():
+    """rag_set_conv_pair(1) switches the layers to the cta_group::2 kernel; outputs are bit-identical."""
+    from rocalphago_b200 import _cabi
+    L = _cabi.lib()
+    n = 700                                                     # several 256-row tiles per CTA pair
+    net = CNNPolicy(go_oracle.DEFAULT_FEATURES, layers=3, filters_per_layer=192, dtype="fp16", seed=41)
+    batch = BatchedGameState.random_playouts(n, seed=77)
+    old = L.rag_set_conv_pair(0)
+    try:
+        single = net.model.eval_batch_device(batch, net.preprocessor.plane_src).cpu().numpy()
+        L.rag_set_conv_pair(1)
+        pair = net.model.eval_batch_device(batch, net.preprocessor.plane_src).cpu().numpy()
+    finally:
+        L.rag_set_conv_pair(old)
+    assert np.array_equal(single, pair)
