@@ -364,6 +364,69 @@ def run_gpu(args):
         dist.destroy_process_group()
 
 
+def run_features(args):
+    """BASELINE config 4: feature extraction only (all 48 planes incl. ladders) -> uint8 NCHW.
+    Roofline: the emit kernel, the HBM-bound kernel of the feature path (17,568 B per position)."""
+    import torch
+    import torch.distributed as dist
+    from rocalphago_b200 import BatchedGameState, Preprocess, _cabi
+    from rocalphago_b200 import preprocessing as P
+    from rocalphago_b200.state import _ptr, _stream
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    n, K, W = args.batch, args.steps, max(3, args.warmup)
+    L = _cabi.lib()
+    pp = Preprocess()
+    pool = [BatchedGameState.random_playouts(n, seed=20261106 + 7919 * (rank * 4 + i), device=dev) for i in range(4)]
+    ws = pp._ws.get(n, dev)
+    out = torch.empty((n, 48, 19, 19), dtype=torch.uint8, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def step(b, ev=None):
+        _cabi.check(L.rag_features_analyze(_ptr(b.packed), n, 19, 1, _ptr(ws), ws.numel(), _stream()))
+        if ev: ev[0].record()
+        pp.emit(ws, n, 19, P.LAYOUT_NCHW_U8, out=out)
+        if ev: ev[1].record()
+    for i in range(W):
+        step(pool[i % 4])
+    torch.cuda.synchronize()
+    if world > 1: dist.barrier()
+    sampler = ClockSampler(local)
+    if rank == 0: sampler.start()
+    E = lambda: torch.cuda.Event(enable_timing=True)
+    evs = [(E(), E(), E(), E()) for _ in range(K)]
+    for k in range(K):
+        flush.zero_()
+        evs[k][0].record(); step(pool[k % 4], (evs[k][1], evs[k][2])); evs[k][3].record()
+    torch.cuda.synchronize()
+    if world > 1: dist.barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    tot = sum(e[0].elapsed_time(e[3]) for e in evs); emit = sum(e[1].elapsed_time(e[2]) for e in evs) / K
+    t = torch.tensor([tot], dtype=torch.float64, device=dev)
+    if world > 1: dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    tot = float(t.cpu())
+    if rank == 0:
+        peaks = load_peaks()
+        achieved = FEATURE_BYTES * n / (emit / 1e3) / 1e9
+        print(json.dumps({
+            "metric": "positions/sec: 48-plane feature extraction only, 19x19", "value": n * K * world / (tot / 1e3),
+            "unit": "positions/s", "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": tot / K, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "feature-extraction-only sweep (BASELINE config 4): 48 planes incl. ladders -> uint8 NCHW, "
+                                   "%d positions/GPU/step, device-generated random playouts" % n,
+                       "l2": "256 MiB buffer written between timed steps"},
+            "gpu_launches": 3 * K, "clocks": clocks,
+            "roofline": {"bound": "hbm", "kernel": "emit_u8_kernel", "achieved": achieved, "peak": peaks["hbm"], "unit": "GB/s",
+                         "frac": achieved / peaks["hbm"], "ms_per_launch": emit, "traffic": None,
+                         "peak_source": peaks["src"], "note": "17,568 algorithmic bytes per position (SURVEY 8d)"},
+            "stage_ms": {"analyze_plus_ladders": tot / K - emit, "emit_u8": emit}}))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -376,12 +439,18 @@ def main():
     ap.add_argument("--cpu-sample", type=int, default=512)
     ap.add_argument("--ref-sample", type=int, default=256)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="policy", choices=["policy", "features"],
+                    help="policy: the flagship (features + 13x192 policy forward); features: BASELINE config 4")
     ap.add_argument("--serial", action="store_true", help="also time the single-stream rag_eval_batch step")
     ap.add_argument("--conv-pair", type=int, default=0, help="0: one CTA per tile; 1: CTA pairs (cta_group::2)")
     ap.add_argument("--no-pipeline", action="store_true", help="debug: skip the pipelined passes")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload == "features":
+        if args.batch == 4096:
+            args.batch = 32768
+        run_features(args)
     else:
         run_gpu(args)
 

@@ -191,32 +191,77 @@ emit_nchw_kernel(const uint32_t* __restrict__ planes, long long total, int S, Pl
     }
 }
 
+// uint8 NCHW, the layout of Preprocess.state_to_tensor: one CTA per position.  The F x S*S bytes
+// of a position are assembled in shared memory (each thread expands (plane, row) words into S
+// bytes), then leave as one contiguous, 16-byte-vectorised stream -- the HBM-bound kernel of the
+// feature path (17,328 B out and 3.6 KB of row words in per position at F = 48).
+__global__ void __launch_bounds__(256)
+emit_u8_kernel(const uint32_t* __restrict__ planes, int n, int S, PlaneMap map, uint8_t* __restrict__ out)
+{
+    extern __shared__ __align__(16) uint8_t sm_bytes[];
+    const int S2 = S * S, per_pos = map.F * S2;
+    for (int pos = blockIdx.x; pos < n; pos += gridDim.x) {
+        const uint32_t* pl = planes + (size_t)pos * kPlaneWords;
+        for (int t = threadIdx.x; t < map.F * S; t += blockDim.x) {
+            const int f = t / S, x = t - f * S;
+            uint32_t w = __ldg(pl + map.src[f] * 32 + x);
+            uint8_t* dst = sm_bytes + f * S2 + x * S;
+            for (int y = 0; y < S; y++) dst[y] = (uint8_t)((w >> y) & 1u);
+        }
+        __syncthreads();
+        uint8_t* o = out + (size_t)pos * per_pos;
+        // the position's block starts 16-byte aligned iff per_pos * pos is; handle the general case
+        const int head = (int)((16 - ((size_t)o & 15)) & 15);
+        const int body = per_pos > head ? (per_pos - head) / 16 : 0;
+        if ((int)threadIdx.x < head && (int)threadIdx.x < per_pos) o[threadIdx.x] = sm_bytes[threadIdx.x];
+        for (int c = threadIdx.x; c < body; c += blockDim.x) {
+            const uint8_t* sp = sm_bytes + head + c * 16;
+            uint4 v;
+            if (head == 0) v = *reinterpret_cast<const uint4*>(sp);
+            else {
+                uint32_t w4[4];
+                #pragma unroll
+                for (int k = 0; k < 4; k++)
+                    w4[k] = (uint32_t)sp[4 * k] | ((uint32_t)sp[4 * k + 1] << 8) | ((uint32_t)sp[4 * k + 2] << 16) | ((uint32_t)sp[4 * k + 3] << 24);
+                v = make_uint4(w4[0], w4[1], w4[2], w4[3]);
+            }
+            *reinterpret_cast<uint4*>(o + head + c * 16) = v;
+        }
+        for (int i = head + body * 16 + threadIdx.x; i < per_pos; i += blockDim.x) o[i] = sm_bytes[i];
+        __syncthreads();
+    }
+}
+
 // Conv input ("pixel rows", see conv.cu): 16-bit rows of C channels, row = lead + pos*Sp*Sp +
 // x*Sp + y with Sp = S + pad.  Every row of the body is written -- real pixels with the planes
-// as 1.0/0.0, padding pixels with zeros.  One thread = one 16-byte chunk (8 channels) of a row.
+// as 1.0/0.0, padding pixels with zeros.  A warp owns a board row x: lane l keeps the row words of
+// channels 2l and 2l+1 (and 2l+64, 2l+65 when C = 128) and writes one 4-byte pair per pixel, so every
+// store instruction of the warp is one full 128-byte line of a pixel row.
 __global__ void __launch_bounds__(256)
 emit_conv_kernel(const uint32_t* __restrict__ planes, int n, int S, int pad, int C, PlaneMap map,
                  uint16_t one, uint16_t* __restrict__ out)
 {
-    const int Sp = S + pad, spp = Sp * Sp, chunks = C / 8;
-    const long long total = (long long)n * spp * chunks;
-    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total;
-         t += (long long)gridDim.x * blockDim.x) {
-        int ch = (int)(t % chunks);
-        long long pix = t / chunks;
-        int pos = (int)(pix / spp), rem = (int)(pix - (long long)pos * spp);
-        int x = rem / Sp, y = rem - x * Sp;
+    const int Sp = S + pad, spp = Sp * Sp;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, warps = blockDim.x >> 5;
+    const uint32_t one_lo = one, one_hi = (uint32_t)one << 16;
+    for (int pos = blockIdx.x; pos < n; pos += gridDim.x) {
         const uint32_t* pl = planes + (size_t)pos * kPlaneWords;
-        __align__(16) uint16_t v[8];
-        const bool real = x < S && y < S;
-        #pragma unroll
-        for (int j = 0; j < 8; j++) {
-            int f = ch * 8 + j;
-            uint32_t bit = 0;
-            if (real && f < map.F) bit = (__ldg(pl + map.src[f] * 32 + x) >> y) & 1u;
-            v[j] = bit ? one : (uint16_t)0;
+        uint32_t* obase = reinterpret_cast<uint32_t*>(out + ((size_t)kConvLeadRows + (size_t)pos * spp) * C);
+        for (int x = warp; x < Sp; x += warps) {
+            for (int half = 0; half < C / 64; half++) {
+                const int c0 = half * 64 + 2 * lane;
+                uint32_t w0 = 0, w1 = 0;
+                if (x < S) {
+                    if (c0 < map.F) w0 = __ldg(pl + map.src[c0] * 32 + x);
+                    if (c0 + 1 < map.F) w1 = __ldg(pl + map.src[c0 + 1] * 32 + x);
+                }
+                uint32_t* orow = obase + (size_t)x * Sp * (C / 2) + half * 32 + lane;
+                for (int y = 0; y < Sp; y++) {
+                    const uint32_t v = (((w0 >> y) & 1u) ? one_lo : 0u) | (((w1 >> y) & 1u) ? one_hi : 0u);
+                    orow[(size_t)y * (C / 2)] = v;             // bits >= S of a row word are zero: padding columns come out 0
+                }
+            }
         }
-        *reinterpret_cast<uint4*>(out + ((long long)kConvLeadRows + pix) * C + ch * 8) = *reinterpret_cast<const uint4*>(v);
     }
 }
 
@@ -466,9 +511,15 @@ int rag_features_emit(const void* d_workspace, int n, int size, const int32_t* h
     const uint32_t* planes = (const uint32_t*)((const char*)d_workspace + kCounterBytes);
     const long long total = (long long)n * F * size * size;
     if (layout == RAG_LAYOUT_NCHW_U8) {
-        long long threads = (total + 15) / 16;
-        int blocks = (int)((threads + 255) / 256);
-        emit_nchw_kernel<uint8_t, 16><<<blocks, 256, 0, s>>>(planes, total, size, map, (uint8_t*)d_out);
+        const size_t smem = (size_t)F * size * size + 16;
+        if (smem <= 48 * 1024) {
+            int blocks = n < 148 * 8 ? n : 148 * 8;
+            emit_u8_kernel<<<blocks, 256, smem, s>>>(planes, n, size, map, (uint8_t*)d_out);
+        } else {
+            long long threads = (total + 15) / 16;
+            int blocks = (int)((threads + 255) / 256);
+            emit_nchw_kernel<uint8_t, 16><<<blocks, 256, 0, s>>>(planes, total, size, map, (uint8_t*)d_out);
+        }
     } else if (layout == RAG_LAYOUT_NCHW_F32) {
         long long threads = (total + 3) / 4;
         int blocks = (int)((threads + 255) / 256);
@@ -484,8 +535,7 @@ int rag_features_emit(const void* d_workspace, int n, int size, const int32_t* h
         RAG_CUDA_CHECK(cudaMemsetAsync(o, 0, (size_t)kConvLeadRows * conv_channels * 2, s));
         RAG_CUDA_CHECK(cudaMemsetAsync(o + (kConvLeadRows + body) * conv_channels, 0,
                                        (size_t)(rows - kConvLeadRows - body) * conv_channels * 2, s));
-        long long threads = body * (conv_channels / 8);
-        int blocks = (int)((threads + 255) / 256);
+        int blocks = n < 148 * 8 ? n : 148 * 8;
         emit_conv_kernel<<<blocks, 256, 0, s>>>(planes, n, size, conv_pad, conv_channels, map, one, (uint16_t*)d_out);
     } else {
         return fail(RAG_EINVAL, "unknown layout %d", layout);
