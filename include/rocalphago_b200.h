@@ -78,9 +78,9 @@ int rag_unpack_states(int n, int size, const uint32_t* h_packed, int8_t* h_board
 
 #define RAG_LAYOUT_NCHW_U8   0   /* uint8  [n][F][S*S]            (game_converter.py:76's storage dtype) */
 #define RAG_LAYOUT_NCHW_F32  1   /* float  [n][F][S*S]            (what NeuralNetBase.forward is fed)   */
-#define RAG_LAYOUT_CONV_IN   2   /* 16-bit [rag_conv_rows(n,S,pad)][conv_channels] zero-padded pixel rows:
-                                    the first conv layer's TMA source (layout described at
-                                    rag_conv_rows); element type chosen by `conv_dtype`                 */
+#define RAG_LAYOUT_CONV_IN   2   /* 16-bit [rag_conv_rows(n,S)][conv_channels] dense pixel rows (NHWC): row
+                                    b*S*S + x*S + y holds point (x, y) of board b; the first conv
+                                    layer's TMA source; element type chosen by `conv_dtype`            */
 
 #define RAG_DTYPE_BF16 0
 #define RAG_DTYPE_FP16 1
@@ -99,14 +99,13 @@ int rag_features_analyze(const uint32_t* d_states, int n, int size, int with_lad
 int rag_features_ladders(const uint32_t* d_states, int n, int size, void* d_workspace,
                          size_t workspace_bytes, void* stream);
 /* Step 2: write the listed planes from the workspace in the requested layout.
- * conv_dtype / conv_pad / conv_channels are read only for RAG_LAYOUT_CONV_IN
- * (conv_pad = first layer's filter_width // 2; conv_channels = 64 or 128 >= F). */
+ * conv_dtype / conv_channels are read only for RAG_LAYOUT_CONV_IN (conv_channels = 64 or 128 >= F;
+ * channels past F are written as zero). */
 int rag_features_emit(const void* d_workspace, int n, int size, const int32_t* h_plane_src, int F,
-                      int layout, int conv_dtype, int conv_pad, int conv_channels, void* d_out,
-                      void* stream);
+                      int layout, int conv_dtype, int conv_channels, void* d_out, void* stream);
 /* Both steps (the ladder reader runs iff plane 44 or 45 is listed). */
 int rag_features(const uint32_t* d_states, int n, int size, const int32_t* h_plane_src, int F,
-                 int layout, int conv_dtype, int conv_pad, int conv_channels, void* d_out,
+                 int layout, int conv_dtype, int conv_channels, void* d_out,
                  void* d_workspace, size_t workspace_bytes, void* stream);
 
 /* rag_features for callers that must not allocate.  (No counterpart in the reference: its
@@ -131,16 +130,12 @@ int rag_features(const uint32_t* d_states, int n, int size, const int32_t* h_pla
  *     yourself.  Contents left by an earlier call never leak into a later result.
  * Arguments and results are exactly those of rag_features. */
 int rag_features_static(const uint32_t* d_states, int n, int size, const int32_t* h_plane_src, int F,
-                        int layout, int conv_dtype, int conv_pad, int conv_channels, void* d_out,
-                        void* stream);
+                        int layout, int conv_dtype, int conv_channels, void* d_out, void* stream);
 int rag_features_static_max_positions(void);
 
-/* Rows of the zero-padded pixel-row layout for n boards of size S with `pad` zero
- * columns/rows per board: pixel (x, y) of board b is row
- *     128 + b*(S+pad)*(S+pad) + x*(S+pad) + y
- * and every other row is zero (the emit writes the zeros too, so the buffer needs
- * no preparation by its owner). */
-long long rag_conv_rows(int n, int size, int pad);
+/* Rows a RAG_LAYOUT_CONV_IN buffer for n boards must have: n*S*S rounded up to a multiple of 256
+ * (rows past n*S*S are never written nor used). */
+long long rag_conv_rows(int n, int size);
 
 /* ------------------------------------------------------------------ state updates
  *
@@ -201,10 +196,9 @@ int rag_net_num_weight_arrays(const rag_net* net);
 int rag_net_load_weights(rag_net* net, const float* const* h_arrays, int n_arrays);
 
 size_t rag_net_workspace_bytes(const rag_net* net, int n);
-/* layout of the input the *_rows entry expects: rag_conv_rows(n, board, pad) rows of `channels` */
+/* layout of the input the *_rows entry expects: rag_conv_rows(n, board) rows of `channels` */
 long long rag_net_input_rows(const rag_net* net, int n);
 int rag_net_input_channels(const rag_net* net);
-int rag_net_input_pad(const rag_net* net);
 
 /* Tuning/test knob (process-wide): 0 = one CTA per tile (default); 1 = convolutions run on CTA
  * pairs (tcgen05 cta_group::2: half the weight tile per CTA, one M=256 UMMA per pair).  Results
@@ -227,7 +221,7 @@ size_t rag_net_logits_offset(const rag_net* net, int n);
  * d_out float [n][S*S] probabilities (policy) or [n] values in [-1, 1] (value). */
 int rag_net_forward(rag_net* net, const float* d_nchw, int n, float* d_out, void* d_workspace,
                     size_t workspace_bytes, void* stream);
-/* The same from pixel rows (RAG_LAYOUT_CONV_IN with this net's dtype / pad / channels). */
+/* The same from pixel rows (RAG_LAYOUT_CONV_IN with this net's dtype / channels). */
 int rag_net_forward_rows(rag_net* net, const void* d_in_rows, int n, float* d_out, void* d_workspace,
                          size_t workspace_bytes, void* stream);
 

@@ -46,11 +46,11 @@ def lib():
         "rag_features_workspace_bytes": (sz, [i32]),
         "rag_features_analyze": (i32, [vp, i32, i32, i32, vp, sz, vp]),
         "rag_features_ladders": (i32, [vp, i32, i32, vp, sz, vp]),
-        "rag_features_emit": (i32, [vp, i32, i32, vp, i32, i32, i32, i32, i32, vp, vp]),
-        "rag_features": (i32, [vp, i32, i32, vp, i32, i32, i32, i32, i32, vp, vp, sz, vp]),
-        "rag_features_static": (i32, [vp, i32, i32, vp, i32, i32, i32, i32, i32, vp, vp]),
+        "rag_features_emit": (i32, [vp, i32, i32, vp, i32, i32, i32, i32, vp, vp]),
+        "rag_features": (i32, [vp, i32, i32, vp, i32, i32, i32, i32, vp, vp, sz, vp]),
+        "rag_features_static": (i32, [vp, i32, i32, vp, i32, i32, i32, i32, vp, vp]),
         "rag_features_static_max_positions": (i32, []),
-        "rag_conv_rows": (i64, [i32, i32, i32]),
+        "rag_conv_rows": (i64, [i32, i32]),
         "rag_do_move": (i32, [vp, i32, i32, vp, vp, vp]),
         "rag_random_playouts": (i32, [vp, i32, i32, u64, i32, i32, vp, i32, vp]),
         "rag_playout_quota": (i32, [i32, i32]),
@@ -65,7 +65,6 @@ def lib():
         "rag_net_layer_times": (i32, [vp, vp, i32]),
         "rag_net_input_rows": (i64, [vp, i32]),
         "rag_net_input_channels": (i32, [vp]),
-        "rag_net_input_pad": (i32, [vp]),
         "rag_net_forward": (i32, [vp, vp, i32, vp, vp, sz, vp]),
         "rag_net_forward_rows": (i32, [vp, vp, i32, vp, vp, sz, vp]),
         "rag_eval_workspace_bytes": (sz, [vp, i32]),

@@ -3,18 +3,18 @@
 // Replaces the Keras/Theano graph built by AlphaGo/models/policy.py:94-138 (CNNPolicy.create_network)
 // and AlphaGo/models/value.py:14-28 and run by AlphaGo/models/nn_util.py:48-58 (K.function).
 //
-// Data layout ("pixel rows"): an activation tensor is a 2-D matrix [row][channel] of 16-bit
-// values; pixel (x, y) of board b is row  128 + b*Sp*Sp + x*Sp + y  with Sp = S + pad, pad =
-// filter_width/2 of the layer that READS it, and every other row is zero.  A (dx, dy) filter
-// tap is then the same matrix shifted by dx*Sp + dy rows, so a k x k 'same' convolution is
-//       out[r, :] = act( bias + sum_taps  in[r + shift_t, :] . W_t^T )
-// -- k*k plain GEMMs that share one accumulator.  No im2col buffer exists anywhere: the TMA
-// engine fetches the shifted [128 rows x 64 channels] operand tiles straight from the
-// activation matrix, and the zero rows stand in for 'same' padding.
+// Data layout ("pixel rows"): an activation tensor is a dense 2-D matrix [n*S*S][channels] of
+// 16-bit values, row b*S*S + x*S + y for point (x, y) of board b -- NHWC with nothing in between.
+// A k x k 'same' convolution is then
+//       out[r, :] = act( bias + sum_taps  in[r shifted by (dx, dy), :] . W_t^T )
+// -- k*k GEMMs that share one accumulator -- and the shifted operand is produced by the TMA
+// engine in im2col mode: one instruction fetches, for 128 consecutive output points, the input
+// point (x + dx, y + dy) of each, crossing row and board boundaries and writing zeros where the
+// point falls off the board.  No im2col buffer, no padded copies, no wasted MMA rows.
 //
 // Kernel (one persistent CTA per SM, 6 warps):
-//   warp 0      TMA producer: per (tap, 64-channel chunk) one A tile (shifted activations) and
-//               one B tile (that tap's weights) into a ring of 128B-swizzled smem stages
+//   warp 0      TMA producer: per (tap, 64-channel chunk) one im2col A tile (shifted activations)
+//               and one B tile (that tap's weights) into a ring of 128B-swizzled smem stages
 //   warp 1      tcgen05.mma issuer (one elected lane): M=128 x N=filters x K=16 UMMAs, fp32
 //               accumulators in TMEM, double-buffered so the epilogue of tile i overlaps the
 //               MMAs of tile i+1
@@ -43,16 +43,15 @@ constexpr int kConvThreads = 192;
 constexpr int kATileBytes = kTileM * kChunkK * 2;     // 16 KiB
 
 struct ConvParams {
-    int tiles, taps, kchunks, N, stages, dtype;
-    int S, Sp_in, Sp_out, n;
+    int tiles, width, kchunks, N, stages, dtype;
+    int S, n;                 // board size, boards
     int mode;                 // 0: write 16-bit pixel rows; 1: fused 1x1 head -> fp32 logits
     int relu;
-    long long body_rows;      // n * Sp_in * Sp_in
+    long long rows;           // n * S * S
     const float* bias;        // [N]
     const float* head_w;      // [N]   (mode 1)
     float head_b;
     void* out;
-    int shift[kMaxTaps];
 };
 
 // ---- PTX wrappers ----------------------------------------------------------------------------
@@ -83,6 +82,20 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
     asm volatile(
         "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
         ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
+// im2col-mode load: `pixels` consecutive base points starting at (w, h, n), each displaced by the
+// filter tap (w_off, h_off); off-board points read as zero
+__device__ __forceinline__ void tma_load_im2col(uint32_t dst, const CUtensorMap* map, int c, int w, int h, int n,
+                                                uint16_t w_off, uint16_t h_off, uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};"
+        ::"r"(dst), "l"(map), "r"(bar), "r"(c), "r"(w), "r"(h), "r"(n), "h"(w_off), "h"(h_off) : "memory");
+}
+__device__ __forceinline__ void tma_load_im2col_pair(uint32_t dst, const CUtensorMap* map, int c, int w, int h, int n,
+                                                     uint16_t w_off, uint16_t h_off, uint32_t leader_bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.im2col.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};"
+        ::"r"(dst), "l"(map), "r"(leader_bar), "r"(c), "r"(w), "r"(h), "r"(n), "h"(w_off), "h"(h_off) : "memory");
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -213,30 +226,38 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if (kPair) cluster_sync_all();                                 // the peer's barriers exist before anyone signals them
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
-    const int kblocks = p.taps * p.kchunks;
+    const int kblocks = p.width * p.width * p.kchunks;
 
     if (warp == 0) {
         // ===== TMA producer =====
         if (lane == 0) {
             uint32_t it = 0;
+            const int pad = p.width / 2, S2 = p.S * p.S;
             for (int tile = worker; tile < p.tiles; tile += n_workers) {
-                const int r0 = kConvLeadRows + tile * rows_per_tile + (int)rank * kTileM;
-                for (int t = 0; t < p.taps; t++) {
-                    for (int c = 0; c < p.kchunks; c++, it++) {
-                        const int s = (int)(it % (uint32_t)p.stages);
-                        const uint32_t ph = (it / (uint32_t)p.stages) & 1u;
-                        mbar_wait(empty_bar(s), ph ^ 1u);
-                        const uint32_t sa = base + (uint32_t)s * stage_bytes;
-                        if (kPair) {
-                            // both CTAs' bytes are counted on the leader's barrier
-                            if (rank == 0) mbar_expect_tx(full_bar(s), 2u * stage_bytes);
-                            const uint32_t lb = full_bar(s) & kPeerBitMask;
-                            tma_load_2d_pair(sa, &tmA, c * kChunkK, r0 + p.shift[t], lb);
-                            tma_load_2d_pair(sa + kATileBytes, &tmB, c * kChunkK, t * p.N + (int)(rank * b_rows), lb);
-                        } else {
-                            mbar_expect_tx(full_bar(s), stage_bytes);
-                            tma_load_2d(sa, &tmA, c * kChunkK, r0 + p.shift[t], full_bar(s));
-                            tma_load_2d(sa + kATileBytes, &tmB, c * kChunkK, t * p.N, full_bar(s));
+                // first output point of my 128 rows -> base point of the im2col walk (shifted by -pad)
+                const long long m0 = (long long)tile * rows_per_tile + (long long)rank * kTileM;
+                const int b0 = (int)(m0 / S2), r0 = (int)(m0 - (long long)b0 * S2);
+                const int x0 = r0 / p.S, y0 = r0 - x0 * p.S;
+                for (int i = 0; i < p.width; i++) {
+                    for (int j = 0; j < p.width; j++) {
+                        const int t = i * p.width + j;
+                        for (int c = 0; c < p.kchunks; c++, it++) {
+                            const int s = (int)(it % (uint32_t)p.stages);
+                            const uint32_t ph = (it / (uint32_t)p.stages) & 1u;
+                            mbar_wait(empty_bar(s), ph ^ 1u);
+                            const uint32_t sa = base + (uint32_t)s * stage_bytes;
+                            // tensor dims are (C, y, x, board): y is the fast spatial index
+                            if (kPair) {
+                                // both CTAs' bytes are counted on the leader's barrier
+                                if (rank == 0) mbar_expect_tx(full_bar(s), 2u * stage_bytes);
+                                const uint32_t lb = full_bar(s) & kPeerBitMask;
+                                tma_load_im2col_pair(sa, &tmA, c * kChunkK, y0 - pad, x0 - pad, b0, (uint16_t)j, (uint16_t)i, lb);
+                                tma_load_2d_pair(sa + kATileBytes, &tmB, c * kChunkK, t * p.N + (int)(rank * b_rows), lb);
+                            } else {
+                                mbar_expect_tx(full_bar(s), stage_bytes);
+                                tma_load_im2col(sa, &tmA, c * kChunkK, y0 - pad, x0 - pad, b0, (uint16_t)j, (uint16_t)i, full_bar(s));
+                                tma_load_2d(sa + kATileBytes, &tmB, c * kChunkK, t * p.N, full_bar(s));
+                            }
                         }
                     }
                 }
@@ -275,21 +296,14 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         uint32_t lt = 0;
         for (int tile = worker; tile < p.tiles; tile += n_workers, lt++) {
             const uint32_t a = lt & 1u, aph = (lt >> 1) & 1u;
-            // which pixel is my row?
-            const long long rel = (long long)tile * rows_per_tile + (long long)rank * kTileM + quarter * 32 + lane;
-            const int spp = p.Sp_in * p.Sp_in;
-            const int pos = (int)(rel / spp), rem = (int)(rel - (long long)pos * spp);
-            const int x = rem / p.Sp_in, y = rem - x * p.Sp_in;
-            const bool in_body = rel < p.body_rows;
-            const bool real = in_body && x < p.S && y < p.S;
+            // my row of the tile = one point of one board; rows past the last board are not written
+            const long long row = (long long)tile * rows_per_tile + (long long)rank * kTileM + quarter * 32 + lane;
+            const bool real = row < p.rows;
             mbar_wait(tfull_bar((int)a), aph);
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + a * (uint32_t)p.N;
             if (p.mode == 0) {
-                // every row of the output body is written: real pixels with data, padding with zeros
-                const bool writes = in_body && x < p.Sp_out && y < p.Sp_out;
-                uint16_t* orow = reinterpret_cast<uint16_t*>(p.out) +
-                    ((long long)kConvLeadRows + (long long)pos * p.Sp_out * p.Sp_out + x * p.Sp_out + y) * p.N;
+                uint16_t* orow = reinterpret_cast<uint16_t*>(p.out) + row * p.N;
                 for (int c0 = 0; c0 < p.N; c0 += 32) {
                     uint32_t v[32];
                     tc_ld32(taddr + (uint32_t)c0, v);
@@ -300,7 +314,6 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         float f0 = __uint_as_float(v[2 * j]) + s_bias[c0 + 2 * j];
                         float f1 = __uint_as_float(v[2 * j + 1]) + s_bias[c0 + 2 * j + 1];
                         if (p.relu) { f0 = fmaxf(f0, 0.f); f1 = fmaxf(f1, 0.f); }
-                        if (!real) { f0 = 0.f; f1 = 0.f; }
                         if (p.dtype == RAG_DTYPE_BF16) {
                             __nv_bfloat162 h = __floats2bfloat162_rn(f0, f1);
                             packed[j] = *reinterpret_cast<uint32_t*>(&h);
@@ -309,7 +322,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                             packed[j] = *reinterpret_cast<uint32_t*>(&h);
                         }
                     }
-                    if (writes) {
+                    if (real) {
                         uint4* dst = reinterpret_cast<uint4*>(orow + c0);
                         #pragma unroll
                         for (int j = 0; j < 4; j++)
@@ -329,7 +342,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         acc = fmaf(f, s_head[c0 + j], acc);
                     }
                 }
-                if (real) reinterpret_cast<float*>(p.out)[(long long)pos * p.S * p.S + x * p.S + y] = acc + p.head_b;
+                if (real) reinterpret_cast<float*>(p.out)[row] = acc + p.head_b;      // Flatten: index b*S*S + x*S + y
             }
             tc_fence_before();
             __syncwarp();
@@ -350,25 +363,23 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
 // (N, F, S, S) float -> pixel rows (what NeuralNetBase.forward is handed, nn_util.py:57-58)
 __global__ void __launch_bounds__(256)
-nchw_to_rows_kernel(const float* __restrict__ in, int n, int F, int S, int pad, int C, int dtype, uint16_t* __restrict__ out)
+nchw_to_rows_kernel(const float* __restrict__ in, int n, int F, int S, int C, int dtype, uint16_t* __restrict__ out)
 {
-    const int Sp = S + pad, spp = Sp * Sp, chunks = C / 8, S2 = S * S;
-    const long long total = (long long)n * spp * chunks;
+    const int S2 = S * S, chunks = C / 8;
+    const long long total = (long long)n * S2 * chunks;
     for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
         const int ch = (int)(t % chunks);
         const long long pix = t / chunks;
-        const int pos = (int)(pix / spp), rem = (int)(pix - (long long)pos * spp);
-        const int x = rem / Sp, y = rem - x * Sp;
+        const int pos = (int)(pix / S2), r = (int)(pix - (long long)pos * S2);
         __align__(16) uint16_t v[8];
         #pragma unroll
         for (int j = 0; j < 8; j++) {
             const int f = ch * 8 + j;
-            float val = 0.f;
-            if (x < S && y < S && f < F) val = in[((long long)pos * F + f) * S2 + x * S + y];
+            float val = f < F ? in[((long long)pos * F + f) * S2 + r] : 0.f;
             if (dtype == RAG_DTYPE_BF16) { __nv_bfloat16 h = __float2bfloat16_rn(val); v[j] = *reinterpret_cast<uint16_t*>(&h); }
             else { __half h = __float2half_rn(val); v[j] = *reinterpret_cast<uint16_t*>(&h); }
         }
-        *reinterpret_cast<uint4*>(out + ((long long)kConvLeadRows + pix) * C + ch * 8) = *reinterpret_cast<const uint4*>(v);
+        *reinterpret_cast<uint4*>(out + pix * C + ch * 8) = *reinterpret_cast<const uint4*>(v);
     }
 }
 
@@ -428,22 +439,20 @@ value_head_kernel(const float* __restrict__ logits, const float* __restrict__ w1
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const int*, const int*, cuuint32_t, cuuint32_t, const cuuint32_t*,
+                                   CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
-static EncodeTiledFn encode_tiled() {
-    static EncodeTiledFn fn = nullptr;
-    if (!fn) {
-        void* sym = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &q) == cudaSuccess &&
-            q == cudaDriverEntryPointSuccess)
-            fn = (EncodeTiledFn)sym;
-    }
-    return fn;
+static void* driver_symbol(const char* name) {
+    void* sym = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint(name, &sym, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) return nullptr;
+    return sym;
 }
 
-// 2-D row-major 16-bit matrix [rows][cols], box = [box_rows][64 columns], 128-byte swizzle
+// weights: 2-D row-major 16-bit matrix [rows][cols], box = [box_rows][64 columns], 128-byte swizzle
 static int make_map(CUtensorMap* map, const void* ptr, long long rows, int cols, int box_rows, int dtype) {
-    EncodeTiledFn enc = encode_tiled();
+    static EncodeTiledFn enc = (EncodeTiledFn)driver_symbol("cuTensorMapEncodeTiled");
     if (!enc) return fail(RAG_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
     cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
     cuuint64_t strides[1] = {(cuuint64_t)cols * 2};
@@ -453,6 +462,25 @@ static int make_map(CUtensorMap* map, const void* ptr, long long rows, int cols,
                      const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                      CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(RAG_ECUDA, "cuTensorMapEncodeTiled failed with CUresult %d (rows %lld cols %d box %d)", (int)r, rows, cols, box_rows);
+    return RAG_OK;
+}
+
+// activations: NHWC [n][S][S][C] seen through an im2col window for a width x width 'same' filter:
+// base points range over [-pad, S - 1 - pad] in both directions (lower corner -pad, upper corner
+// -pad), every load brings kTileM points x 64 channels, off-board points are zero-filled
+static int make_map_im2col(CUtensorMap* map, const void* ptr, int n, int S, int C, int width, int dtype) {
+    static EncodeIm2colFn enc = (EncodeIm2colFn)driver_symbol("cuTensorMapEncodeIm2col");
+    if (!enc) return fail(RAG_ECUDA, "cuTensorMapEncodeIm2col is not available from this driver");
+    const int pad = width / 2;
+    cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)S, (cuuint64_t)S, (cuuint64_t)n};
+    cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)S * C * 2, (cuuint64_t)S * S * C * 2};
+    int lower[2] = {-pad, -pad}, upper[2] = {-pad, -pad};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = enc(map, dtype == RAG_DTYPE_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4,
+                     const_cast<void*>(ptr), dims, strides, lower, upper, (cuuint32_t)kChunkK, (cuuint32_t)kTileM, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(RAG_ECUDA, "cuTensorMapEncodeIm2col failed with CUresult %d (n %d S %d C %d width %d)", (int)r, n, S, C, width);
     return RAG_OK;
 }
 
@@ -511,20 +539,18 @@ struct NetBuffers {
     size_t act_bytes, in_bytes, total;
 };
 
-static long long max_hidden_rows(const rag_net* net, int n) {
-    long long m = 0;
-    for (size_t l = 1; l < net->layers.size(); l++) {
-        long long r = conv_rows(n, net->desc.board, net->layers[l].width / 2);
-        if (r > m) m = r;
-    }
-    return m;
+// rows of a dense pixel-row buffer for n boards, rounded up to whole tiles
+static long long dense_rows(int n, int S) {
+    long long r = (long long)n * S * S;
+    return (r + 2 * kTileM - 1) / (2 * kTileM) * (2 * kTileM);
 }
 
 static NetBuffers carve_net(const rag_net* net, int n, void* ws, bool with_input) {
     NetBuffers b;
     auto al = [](size_t v) { return (v + 1023) / 1024 * 1024; };
-    b.act_bytes = al((size_t)max_hidden_rows(net, n) * net->max_c * 2);
-    b.in_bytes = with_input ? al((size_t)conv_rows(n, net->desc.board, net->layers[0].width / 2) * net->layers[0].cin_pad * 2) : 0;
+    const long long rows = dense_rows(n, net->desc.board);
+    b.act_bytes = al((size_t)rows * net->max_c * 2);
+    b.in_bytes = with_input ? al((size_t)rows * net->layers[0].cin_pad * 2) : 0;
     size_t logits_bytes = al((size_t)n * net->desc.board * net->desc.board * 4);
     char* p = (char*)ws;
     b.act[0] = (uint16_t*)p; p += b.act_bytes;
@@ -535,53 +561,33 @@ static NetBuffers carve_net(const rag_net* net, int n, void* ws, bool with_input
     return b;
 }
 
-// zero the rows before and after the body of a pixel-row buffer (the only rows a conv reads
-// that no kernel writes)
-static int zero_margins(uint16_t* buf, int n, int S, int pad, int C, cudaStream_t s) {
-    long long sp = S + pad, body = (long long)n * sp * sp, rows = conv_rows(n, S, pad);
-    RAG_CUDA_CHECK(cudaMemsetAsync(buf, 0, (size_t)kConvLeadRows * C * 2, s));
-    RAG_CUDA_CHECK(cudaMemsetAsync(buf + (kConvLeadRows + body) * C, 0, (size_t)(rows - kConvLeadRows - body) * C * 2, s));
-    return RAG_OK;
-}
-
 static int run_layers(rag_net* net, const uint16_t* d_in, int n, float* d_out, const NetBuffers& b, cudaStream_t s) {
     const int S = net->desc.board, L = (int)net->layers.size();
     const uint16_t* cur = d_in;
     for (int l = 0; l < L; l++) {
         const Layer& ly = net->layers[l];
         const bool last = l == L - 1;
-        const int pad_in = ly.width / 2, Sp_in = S + pad_in;
-        const int pad_out = last ? 0 : net->layers[l + 1].width / 2, Sp_out = S + pad_out;
         uint16_t* dst = last ? nullptr : b.act[l & 1];
-        if (!last) {
-            if (int rc = zero_margins(dst, n, S, pad_out, ly.n_pad, s)) return rc;
-            // the epilogue writes output rows (x, y) for x, y < S + pad_in only; a wider padding on
-            // the next layer (a 3x3 layer feeding a 5x5 one) leaves rows it reads unwritten
-            if (pad_out > pad_in)
-                RAG_CUDA_CHECK(cudaMemsetAsync(dst, 0, (size_t)conv_rows(n, S, pad_out) * ly.n_pad * 2, s));
-        }
 
         ConvParams p;
         memset(&p, 0, sizeof p);
-        p.body_rows = (long long)n * Sp_in * Sp_in;
-        p.tiles = (int)((p.body_rows + kTileM - 1) / kTileM);
-        p.taps = ly.taps; p.kchunks = ly.cin_pad / kChunkK; p.N = ly.n_pad;
+        p.rows = (long long)n * S * S;
+        p.tiles = (int)((p.rows + kTileM - 1) / kTileM);
+        p.width = ly.width; p.kchunks = ly.cin_pad / kChunkK; p.N = ly.n_pad;
         p.stages = pick_stages(ly.n_pad); p.dtype = net->desc.dtype;
-        p.S = S; p.Sp_in = Sp_in; p.Sp_out = Sp_out; p.n = n;
+        p.S = S; p.n = n;
         p.mode = last ? 1 : 0; p.relu = 1;
         p.bias = ly.d_bias; p.head_w = net->d_head_w; p.head_b = net->head_b;
         p.out = last ? (void*)b.logits : (void*)dst;
-        for (int i = 0; i < ly.width; i++)
-            for (int j = 0; j < ly.width; j++) p.shift[i * ly.width + j] = (i - pad_in) * Sp_in + (j - pad_in);
 
         // a CTA pair (cta_group::2) needs an even split of the weight tile into 8-row groups
         const bool pair = g_conv_pair && (ly.n_pad % 32 == 0) && net->sms >= 2;
         if (pair) {
-            p.tiles = (int)((p.body_rows + 2 * kTileM - 1) / (2 * kTileM));
+            p.tiles = (int)((p.rows + 2 * kTileM - 1) / (2 * kTileM));
             p.stages = pick_stages(ly.n_pad / 2);
         }
         CUtensorMap tmA, tmB;
-        if (int rc = make_map(&tmA, cur, conv_rows(n, S, pad_in), ly.cin_pad, kTileM, net->desc.dtype)) return rc;
+        if (int rc = make_map_im2col(&tmA, cur, n, S, ly.cin_pad, ly.width, net->desc.dtype)) return rc;
         if (int rc = make_map(&tmB, ly.d_w, (long long)ly.taps * ly.n_pad, ly.cin_pad, pair ? ly.n_pad / 2 : ly.n_pad, net->desc.dtype)) return rc;
         if (net->profiling) RAG_CUDA_CHECK(cudaEventRecord(net->events[l], s));
         if (pair) {
@@ -778,9 +784,8 @@ size_t rag_net_logits_offset(const rag_net* net, int n)
     return (size_t)((char*)b.logits - (char*)nullptr);
 }
 
-long long rag_net_input_rows(const rag_net* net, int n) { return net ? conv_rows(n, net->desc.board, net->layers[0].width / 2) : 0; }
+long long rag_net_input_rows(const rag_net* net, int n) { return net ? dense_rows(n, net->desc.board) : 0; }
 int rag_net_input_channels(const rag_net* net) { return net ? net->layers[0].cin_pad : 0; }
-int rag_net_input_pad(const rag_net* net) { return net ? net->layers[0].width / 2 : 0; }
 
 static int net_ready(const rag_net* net, int n, const void* in, const void* out, const void* ws, size_t bytes) {
     if (!net) return fail(RAG_EINVAL, "null net");
@@ -805,10 +810,9 @@ int rag_net_forward(rag_net* net, const float* d_nchw, int n, float* d_out, void
     cudaStream_t s = (cudaStream_t)stream;
     NetBuffers b = carve_net(net, n, d_workspace, true);
     const Layer& l0 = net->layers[0];
-    const int S = net->desc.board, pad = l0.width / 2;
-    if (int rc = zero_margins(b.in_rows, n, S, pad, l0.cin_pad, s)) return rc;
-    long long threads = (long long)n * (S + pad) * (S + pad) * (l0.cin_pad / 8);
-    nchw_to_rows_kernel<<<(int)((threads + 255) / 256), 256, 0, s>>>(d_nchw, n, net->desc.in_planes, S, pad, l0.cin_pad, net->desc.dtype, b.in_rows);
+    const int S = net->desc.board;
+    long long threads = (long long)n * S * S * (l0.cin_pad / 8);
+    nchw_to_rows_kernel<<<(int)((threads + 255) / 256), 256, 0, s>>>(d_nchw, n, net->desc.in_planes, S, l0.cin_pad, net->desc.dtype, b.in_rows);
     RAG_CUDA_CHECK(cudaGetLastError());
     return run_layers(net, b.in_rows, n, d_out, b, s);
 }
@@ -835,7 +839,7 @@ int rag_eval_batch(rag_net* net, const uint32_t* d_states, int n, const int32_t*
     NetBuffers b = carve_net(net, n, ws + fbytes, true);
     const Layer& l0 = net->layers[0];
     if (int rc = rag_features(d_states, n, net->desc.board, h_plane_src, F, RAG_LAYOUT_CONV_IN, net->desc.dtype,
-                              l0.width / 2, l0.cin_pad, b.in_rows, ws, fbytes, stream)) return rc;
+                              l0.cin_pad, b.in_rows, ws, fbytes, stream)) return rc;
     return run_layers(net, b.in_rows, n, d_out, b, (cudaStream_t)stream);
 }
 

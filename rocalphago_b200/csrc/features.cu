@@ -232,33 +232,30 @@ emit_u8_kernel(const uint32_t* __restrict__ planes, int n, int S, PlaneMap map, 
     }
 }
 
-// Conv input ("pixel rows", see conv.cu): 16-bit rows of C channels, row = lead + pos*Sp*Sp +
-// x*Sp + y with Sp = S + pad.  Every row of the body is written -- real pixels with the planes
-// as 1.0/0.0, padding pixels with zeros.  A warp owns a board row x: lane l keeps the row words of
-// channels 2l and 2l+1 (and 2l+64, 2l+65 when C = 128) and writes one 4-byte pair per pixel, so every
+// Conv input ("pixel rows", see conv.cu): dense 16-bit rows of C channels, row pos*S*S + x*S + y,
+// planes as 1.0/0.0, channels >= F zero.  A warp owns a board row x: lane l keeps the row words of
+// channels 2l and 2l+1 (and 2l+64, 2l+65 when C = 128) and writes one 4-byte pair per point, so every
 // store instruction of the warp is one full 128-byte line of a pixel row.
 __global__ void __launch_bounds__(256)
-emit_conv_kernel(const uint32_t* __restrict__ planes, int n, int S, int pad, int C, PlaneMap map,
+emit_conv_kernel(const uint32_t* __restrict__ planes, int n, int S, int C, PlaneMap map,
                  uint16_t one, uint16_t* __restrict__ out)
 {
-    const int Sp = S + pad, spp = Sp * Sp;
+    const int S2 = S * S;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, warps = blockDim.x >> 5;
     const uint32_t one_lo = one, one_hi = (uint32_t)one << 16;
     for (int pos = blockIdx.x; pos < n; pos += gridDim.x) {
         const uint32_t* pl = planes + (size_t)pos * kPlaneWords;
-        uint32_t* obase = reinterpret_cast<uint32_t*>(out + ((size_t)kConvLeadRows + (size_t)pos * spp) * C);
-        for (int x = warp; x < Sp; x += warps) {
+        uint32_t* obase = reinterpret_cast<uint32_t*>(out + (size_t)pos * S2 * C);
+        for (int x = warp; x < S; x += warps) {
             for (int half = 0; half < C / 64; half++) {
                 const int c0 = half * 64 + 2 * lane;
                 uint32_t w0 = 0, w1 = 0;
-                if (x < S) {
-                    if (c0 < map.F) w0 = __ldg(pl + map.src[c0] * 32 + x);
-                    if (c0 + 1 < map.F) w1 = __ldg(pl + map.src[c0 + 1] * 32 + x);
-                }
-                uint32_t* orow = obase + (size_t)x * Sp * (C / 2) + half * 32 + lane;
-                for (int y = 0; y < Sp; y++) {
+                if (c0 < map.F) w0 = __ldg(pl + map.src[c0] * 32 + x);
+                if (c0 + 1 < map.F) w1 = __ldg(pl + map.src[c0 + 1] * 32 + x);
+                uint32_t* orow = obase + (size_t)x * S * (C / 2) + half * 32 + lane;
+                for (int y = 0; y < S; y++) {
                     const uint32_t v = (((w0 >> y) & 1u) ? one_lo : 0u) | (((w1 >> y) & 1u) ? one_hi : 0u);
-                    orow[(size_t)y * (C / 2)] = v;             // bits >= S of a row word are zero: padding columns come out 0
+                    orow[(size_t)y * (C / 2)] = v;
                 }
             }
         }
@@ -393,7 +390,7 @@ using namespace rag;
 extern "C" {
 
 const char* rag_last_error(void) { return last_error_buffer(); }
-int rag_abi_version(void) { return 1; }
+int rag_abi_version(void) { return 2; }
 
 int rag_pack_states(int n, int size, const int8_t* h_board, const int16_t* h_age, const int32_t* h_ko,
                     const int32_t* h_player, uint32_t* h_packed)
@@ -500,7 +497,7 @@ int rag_features_ladders(const uint32_t* d_states, int n, int size, void* d_work
 }
 
 int rag_features_emit(const void* d_workspace, int n, int size, const int32_t* h_plane_src, int F, int layout,
-                      int conv_dtype, int conv_pad, int conv_channels, void* d_out, void* stream)
+                      int conv_dtype, int conv_channels, void* d_out, void* stream)
 {
     if (n < 0 || (n > 0 && (!d_workspace || !d_out))) return fail(RAG_EINVAL, "null argument");
     if (int rc = check_size(size)) return rc;
@@ -527,16 +524,9 @@ int rag_features_emit(const void* d_workspace, int n, int size, const int32_t* h
     } else if (layout == RAG_LAYOUT_CONV_IN) {
         if (conv_channels != 64 && conv_channels != 128) return fail(RAG_EINVAL, "conv_channels must be 64 or 128");
         if (F > conv_channels) return fail(RAG_EINVAL, "%d planes do not fit %d channels", F, conv_channels);
-        if (conv_pad < 0 || conv_pad > 3) return fail(RAG_EINVAL, "conv_pad %d", conv_pad);
         uint16_t one = conv_dtype == RAG_DTYPE_FP16 ? (uint16_t)0x3C00 : (uint16_t)0x3F80;
-        const long long sp = size + conv_pad, body = (long long)n * sp * sp, rows = conv_rows(n, size, conv_pad);
-        uint16_t* o = (uint16_t*)d_out;
-        // the margins are the only rows a convolution reads that the kernel does not write
-        RAG_CUDA_CHECK(cudaMemsetAsync(o, 0, (size_t)kConvLeadRows * conv_channels * 2, s));
-        RAG_CUDA_CHECK(cudaMemsetAsync(o + (kConvLeadRows + body) * conv_channels, 0,
-                                       (size_t)(rows - kConvLeadRows - body) * conv_channels * 2, s));
         int blocks = n < 148 * 8 ? n : 148 * 8;
-        emit_conv_kernel<<<blocks, 256, 0, s>>>(planes, n, size, conv_pad, conv_channels, map, one, (uint16_t*)d_out);
+        emit_conv_kernel<<<blocks, 256, 0, s>>>(planes, n, size, conv_channels, map, one, (uint16_t*)d_out);
     } else {
         return fail(RAG_EINVAL, "unknown layout %d", layout);
     }
@@ -545,20 +535,20 @@ int rag_features_emit(const void* d_workspace, int n, int size, const int32_t* h
 }
 
 int rag_features(const uint32_t* d_states, int n, int size, const int32_t* h_plane_src, int F, int layout,
-                 int conv_dtype, int conv_pad, int conv_channels, void* d_out, void* d_workspace,
+                 int conv_dtype, int conv_channels, void* d_out, void* d_workspace,
                  size_t workspace_bytes_given, void* stream)
 {
     int with_ladders = 0;
     for (int i = 0; h_plane_src && i < F; i++)
         if (h_plane_src[i] == kPlaneLadderCapture || h_plane_src[i] == kPlaneLadderEscape) with_ladders = 1;
     if (int rc = rag_features_analyze(d_states, n, size, with_ladders, d_workspace, workspace_bytes_given, stream)) return rc;
-    return rag_features_emit(d_workspace, n, size, h_plane_src, F, layout, conv_dtype, conv_pad, conv_channels, d_out, stream);
+    return rag_features_emit(d_workspace, n, size, h_plane_src, F, layout, conv_dtype, conv_channels, d_out, stream);
 }
 
 int rag_features_static_max_positions(void) { return kStaticMaxPositions; }
 
 int rag_features_static(const uint32_t* d_states, int n, int size, const int32_t* h_plane_src, int F, int layout,
-                        int conv_dtype, int conv_pad, int conv_channels, void* d_out, void* stream)
+                        int conv_dtype, int conv_channels, void* d_out, void* stream)
 {
     if (n > kStaticMaxPositions)
         return fail(RAG_ENOMEM, "rag_features_static handles at most %d positions per call (got %d); "
@@ -571,11 +561,11 @@ int rag_features_static(const uint32_t* d_states, int n, int size, const int32_t
     // The array still holds whatever the previous call left.  What has to start from zero is
     // cleared on the stream by the analysis step itself (the queue counters); the bit-planes and
     // queue slots of positions < n are fully rewritten before anything reads them.
-    return rag_features(d_states, n, size, h_plane_src, F, layout, conv_dtype, conv_pad, conv_channels, d_out,
+    return rag_features(d_states, n, size, h_plane_src, F, layout, conv_dtype, conv_channels, d_out,
                         scratch, kStaticScratchBytes, stream);
 }
 
-long long rag_conv_rows(int n, int size, int pad) { return conv_rows(n, size, pad); }
+long long rag_conv_rows(int n, int size) { return conv_rows(n, size); }
 
 int rag_do_move(uint32_t* d_states, int n, int size, const int32_t* d_moves, int32_t* d_status, void* stream)
 {

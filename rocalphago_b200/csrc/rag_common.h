@@ -25,15 +25,11 @@ inline int fail(int code, const char* fmt, ...) {
                                __FILE__, __LINE__);                                              \
     } while (0)
 
-// Geometry of the zero-padded pixel-row layout the convolutions read (see conv.cu):
-// pixel (x, y) of board b lives in row  lead + b*Sp*Sp + x*Sp + y,  Sp = S + pad; every other
-// row is zero and is never written, so a kxk tap is a plain row shift of dx*Sp + dy.
-constexpr int kConvLeadRows = 128;
-constexpr int kConvTileRows = 128;
-inline long long conv_rows(int n, int S, int pad) {
-    long long sp = S + pad, body = (long long)n * sp * sp;
-    body = (body + kConvTileRows - 1) / kConvTileRows * kConvTileRows;
-    return kConvLeadRows + body + kConvTileRows;
+// Rows of a dense pixel-row buffer (conv.cu): n*S*S, rounded up to whole 256-row tiles so that the
+// last tile of a layer may be addressed in full.
+inline long long conv_rows(int n, int S) {
+    long long r = (long long)n * S * S;
+    return (r + 255) / 256 * 256;
 }
 
 }  // namespace rag

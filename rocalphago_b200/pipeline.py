@@ -65,7 +65,6 @@ class EvalPipeline(object):
             # progress on B200 / driver 580; equal priorities never did in any run.)
             self.s_ana, self.s_net = torch.cuda.Stream(), torch.cuda.Stream()
             self.s_feat, self.s_copy = torch.cuda.Stream(), torch.cuda.Stream()
-        self.pad = int(self.L.rag_net_input_pad(self.handle))
         self.channels = int(self.L.rag_net_input_channels(self.handle))
         self.dtype_code = 0 if self.model.dtype == "bf16" else 1
         self.count = 0
@@ -98,7 +97,7 @@ class EvalPipeline(object):
                 _cabi.check(L.rag_features_ladders(_ptr(states), self.n, self.size, _ptr(slot.fws), slot.fws.numel(),
                                                    vp(self.s_feat.cuda_stream)))
                 _cabi.check(L.rag_features_emit(_ptr(slot.fws), self.n, self.size, src, len(self.plane_src), LAYOUT_CONV_IN,
-                                                self.dtype_code, self.pad, self.channels, _ptr(slot.rows),
+                                                self.dtype_code, self.channels, _ptr(slot.rows),
                                                 vp(self.s_feat.cuda_stream)))
                 slot.feat_done.record(self.s_feat)
             # stage 2: convolutions + head

@@ -87,7 +87,7 @@ class Preprocess(object):
                                                          int(with_ladders), _ptr(ws), ws.numel(), _stream()))
         return ws
 
-    def emit(self, ws, n, size, layout=LAYOUT_NCHW_U8, plane_src=None, conv_dtype=DTYPE_BF16, conv_pad=2,
+    def emit(self, ws, n, size, layout=LAYOUT_NCHW_U8, plane_src=None, conv_dtype=DTYPE_BF16,
              conv_channels=64, out=None):
         src = self.plane_src if plane_src is None else np.ascontiguousarray(plane_src, np.int32)
         F = len(src)
@@ -99,12 +99,12 @@ class Preprocess(object):
             elif layout == LAYOUT_NCHW_F32:
                 out = torch.empty((n, F, size, size), dtype=torch.float32, device=dev)
             else:
-                rows = int(L.rag_conv_rows(n, size, conv_pad))
+                rows = int(L.rag_conv_rows(n, size))
                 out = torch.zeros((rows, conv_channels), device=dev,
                                   dtype=torch.bfloat16 if conv_dtype == DTYPE_BF16 else torch.float16)
         with torch.cuda.device(dev):
             _cabi.check(L.rag_features_emit(_ptr(ws), n, size, src.ctypes.data_as(ctypes.c_void_p), F, layout,
-                                            conv_dtype, conv_pad, conv_channels, _ptr(out), _stream()))
+                                            conv_dtype, conv_channels, _ptr(out), _stream()))
         return out
 
     def to_device(self, batch, layout=LAYOUT_NCHW_U8, **kw):

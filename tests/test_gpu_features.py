@@ -56,24 +56,21 @@ def test_feature_subsets_orders_repeats_and_float_layout():
 
 
 @pytest.mark.parametrize("dtype", [P.DTYPE_BF16, P.DTYPE_FP16])
-@pytest.mark.parametrize("size,pad", [(19, 2), (19, 1), (9, 2)])
-def test_conv_input_layout(size, pad, dtype):
-    """Zero-padded pixel rows: real pixels carry the planes as 1.0/0.0, every other row is zero."""
+@pytest.mark.parametrize("size,channels", [(19, 64), (19, 128), (9, 64)])
+def test_conv_input_layout(size, channels, dtype):
+    """Dense pixel rows (NHWC): row b*S*S + x*S + y carries the planes of point (x, y) as 1.0/0.0,
+    channels past the listed planes are zero."""
     g = gu.load_features("features_playouts_%d.npz" % size)
     n = 37
     batch = BatchedGameState.from_arrays(g["board"][:n], g["age"][:n], g["ko"][:n], g["player"][:n])
     pp = Preprocess(P.DEFAULT_FEATURES)
-    out = pp.to_device(batch, P.LAYOUT_CONV_IN, conv_dtype=dtype, conv_pad=pad, conv_channels=64)
+    out = pp.to_device(batch, P.LAYOUT_CONV_IN, conv_dtype=dtype, conv_channels=channels)
     rows = out.float().cpu().numpy()
-    Sp = size + pad
-    want = np.zeros_like(rows)
     planes = gu.select_planes(g["planes"][:n], P.DEFAULT_FEATURES)            # (n,48,S,S)
-    for b in range(n):
-        blk = np.zeros((Sp, Sp, 64), np.float32)
-        blk[:size, :size, :48] = planes[b].transpose(1, 2, 0)
-        want[128 + b * Sp * Sp:128 + (b + 1) * Sp * Sp] = blk.reshape(Sp * Sp, 64)
-    assert rows.shape[0] % 128 == 0 and rows.shape[0] >= 128 + n * Sp * Sp + 128
-    assert np.array_equal(rows, want)
+    want = np.zeros((n * size * size, channels), np.float32)
+    want[:, :48] = planes.transpose(0, 2, 3, 1).reshape(n * size * size, 48)
+    assert rows.shape[0] % 256 == 0 and rows.shape[0] >= n * size * size and rows.shape[1] == channels
+    assert np.array_equal(rows[:n * size * size], want)
 
 
 def test_state_to_tensor_keeps_reference_signature():

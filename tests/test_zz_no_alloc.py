@@ -26,10 +26,10 @@ def _both(batch, plane_src):
     n, S, F = len(batch), batch.size, len(plane_src)
     src = plane_src.ctypes.data_as(ctypes.c_void_p)
     got = torch.full((n, F, S, S), 7, dtype=torch.uint8, device=batch.device)
-    _cabi.check(L.rag_features_static(_ptr(batch.packed), n, S, src, F, 0, 0, 0, 64, _ptr(got), _stream()))
+    _cabi.check(L.rag_features_static(_ptr(batch.packed), n, S, src, F, 0, 0, 64, _ptr(got), _stream()))
     want = torch.full((n, F, S, S), 9, dtype=torch.uint8, device=batch.device)
     ws = torch.empty(int(L.rag_features_workspace_bytes(n)), dtype=torch.uint8, device=batch.device)
-    _cabi.check(L.rag_features(_ptr(batch.packed), n, S, src, F, 0, 0, 0, 64, _ptr(want), _ptr(ws), ws.numel(), _stream()))
+    _cabi.check(L.rag_features(_ptr(batch.packed), n, S, src, F, 0, 0, 64, _ptr(want), _ptr(ws), ws.numel(), _stream()))
     torch.cuda.synchronize()
     return got.cpu().numpy(), want.cpu().numpy()
 
@@ -57,7 +57,7 @@ def test_static_scratch_refuses_oversized_batches():
     batch = BatchedGameState.random_playouts(n, seed=1)
     src = Preprocess(["board"]).plane_src
     out = torch.zeros((n, 3, 19, 19), dtype=torch.uint8, device="cuda")
-    rc = L.rag_features_static(_ptr(batch.packed), n, 19, src.ctypes.data_as(ctypes.c_void_p), 3, 0, 0, 0, 64,
+    rc = L.rag_features_static(_ptr(batch.packed), n, 19, src.ctypes.data_as(ctypes.c_void_p), 3, 0, 0, 64,
                                _ptr(out), _stream())
     assert rc == -3 and b"at most 256" in L.rag_last_error()
     torch.cuda.synchronize()
