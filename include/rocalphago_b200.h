@@ -95,6 +95,11 @@ size_t rag_features_workspace_bytes(int n);
  * The workspace must stay untouched until the emits that read it have run. */
 int rag_features_analyze(const uint32_t* d_states, int n, int size, int with_ladders,
                          void* d_workspace, size_t workspace_bytes, void* stream);
+/* Tuning/test knob (process-wide): after how many tried moves a ladder search starts handing
+ * replies over to idle warps (default 96; 0 = from the first move; < 0 = never).  Results do not
+ * depend on it.  Returns the previous value. */
+int rag_set_ladder_handover(int moves);
+
 /* Step 1b: the ladder reader over the candidates queued by rag_features_analyze(with_ladders = 2). */
 int rag_features_ladders(const uint32_t* d_states, int n, int size, void* d_workspace,
                          size_t workspace_bytes, void* stream);

@@ -36,15 +36,38 @@ constexpr int kPlaneWords = kNumPlanes * 32;           // 1568 words = 6272 B pe
 constexpr int kCounterBytes = 256;
 constexpr int kMaxPositionsPerLaunch = 1 << 21;        // queue item = pos<<11 | kind<<10 | q
 
+// A reply handed to another warp by a long ladder search (see ladder_kernel).
+struct StealTask {
+    uint32_t H[32], P[32], G[32];    // hunter stones, prey-side stones, prey group: the position the reply is played in
+    int ko, move, is_capture, remaining;
+    int pad[28];
+};
+static_assert(sizeof(StealTask) == 512, "StealTask layout");
+enum { kTaskFree = 0, kTaskPosted = 1, kTaskTaken = 2, kTaskDone0 = 3, kTaskDone1 = 4, kTaskCancelled = 5 };
+enum { kCtlQueued = 0, kCtlTaken = 1, kCtlPosted = 2, kCtlBusy = 4, kCtlAllocCursor = 5 };
+
 struct Workspace {
-    unsigned* counters;      // [0] items queued, [1] items taken
+    unsigned* counters;      // kCtl* slots
     uint32_t* planes;        // [n][50][32]
     uint32_t* queue;         // [n * 2 * S*S]  ladder work items
     size_t queue_cap;
+    StealTask* tasks;        // [task_cap]
+    int* task_status;        // [task_cap]  kTaskFree .. kTaskCancelled, kept apart so that idle warps can scan it cheaply
+    unsigned task_cap;
 };
 
+static unsigned steal_task_cap(int n) {
+    int c = n / 2;
+    return (unsigned)(c < 64 ? 64 : (c > 2048 ? 2048 : c));
+}
+
+static size_t workspace_fixed_bytes(int n) {          // counters + planes + queue, rounded for the task pool's alignment
+    size_t b = (size_t)kCounterBytes + (size_t)n * kPlaneWords * 4 + (size_t)n * 2 * kMaxBoard * kMaxBoard * 4;
+    return (b + 511) / 512 * 512;
+}
+
 static size_t workspace_bytes(int n) {
-    return (size_t)kCounterBytes + (size_t)n * kPlaneWords * 4 + (size_t)n * 2 * kMaxBoard * kMaxBoard * 4;
+    return workspace_fixed_bytes(n) + (size_t)steal_task_cap(n) * (sizeof(StealTask) + 4);
 }
 
 static Workspace carve(void* base, int n) {
@@ -54,6 +77,9 @@ static Workspace carve(void* base, int n) {
     w.planes = (uint32_t*)(p + kCounterBytes);
     w.queue = (uint32_t*)(p + kCounterBytes + (size_t)n * kPlaneWords * 4);
     w.queue_cap = (size_t)n * 2 * kMaxBoard * kMaxBoard;
+    w.task_cap = steal_task_cap(n);
+    w.tasks = (StealTask*)(p + workspace_fixed_bytes(n));
+    w.task_status = (int*)(p + workspace_fixed_bytes(n) + (size_t)w.task_cap * sizeof(StealTask));
     return w;
 }
 
@@ -104,7 +130,7 @@ analyze_kernel(const uint32_t* __restrict__ states, int n, int S, int with_ladde
         const int total = bb_count(cand[0]) + bb_count(cand[1]);
         if (total > 0) {
             unsigned base = 0;
-            if (g.lane == 0) base = atomicAdd(&ws.counters[0], (unsigned)total);
+            if (g.lane == 0) base = atomicAdd(&ws.counters[kCtlQueued], (unsigned)total);
             base = __shfl_sync(kFullMask, base, 0);
             for (int kind = 0; kind < 2; kind++) {
                 BB rem = cand[kind];
@@ -122,33 +148,272 @@ analyze_kernel(const uint32_t* __restrict__ states, int n, int S, int with_ladde
 }
 
 // ---- kernel 2: ladder reader -----------------------------------------------------------------
+//
+// One warp per work item, depth-first (go_bb.cuh).  Most searches try a handful of moves; about one
+// in a thousand -- long chases along the first line of an open board -- tries thousands, and on a
+// single warp that one search used to set the time of the whole batch.  Such a search is a spine
+// with side chases hanging off it, so once a search has tried kStealAfter moves it starts to HAND
+// OVER replies: when it opens a node with several replies it keeps the first and posts the others
+// as tasks (position + move) that any idle warp may take.  The node's value is still "no reply has
+// value 1": a reply of value 1 settles it at once (the handed-over replies are cancelled); otherwise
+// the search takes back what nobody took and waits for the rest.  Warps that run out of work items
+// serve the task ring until nobody is busy.  Nothing here changes a result -- only who computes it.
+
+constexpr int kStealAfterDefault = 96;   // moves tried before a search starts handing over replies
+constexpr int kMaxPosted = 3;            // replies handed over per node
+
+__device__ __forceinline__ int ld_vol(const int* p) { return *(const volatile int*)p; }
+__device__ __forceinline__ unsigned ld_vol(const unsigned* p) { return *(const volatile unsigned*)p; }
+
+struct StealFrames {                     // which tasks each stack frame has out (uniform across lanes)
+    int16_t slot[kLadderDepth][kMaxPosted];
+    uint8_t count[kLadderDepth];
+    uint8_t offered[kLadderDepth];       // a frame hands replies over at most once
+};
+
+// lane 0 decides, the answer is broadcast
+#define LANE0_INT(expr) __shfl_sync(kFullMask, (g.lane == 0) ? (int)(expr) : 0, 0)
+
+__device__ __forceinline__ int steal_post(const Workspace& ws, const Geo& g, BB H, BB P, BB G, int ko, int move,
+                                          bool is_capture, int remaining) {
+    int slot = -1;
+    if (g.lane == 0) {
+        for (int probe = 0; probe < 8 && slot < 0; probe++) {
+            unsigned c = atomicAdd(&ws.counters[kCtlAllocCursor], 1u) % ws.task_cap;
+            if (atomicCAS(&ws.task_status[c], kTaskFree, kTaskTaken) == kTaskFree) slot = (int)c;   // reserved while it is filled
+        }
+    }
+    slot = __shfl_sync(kFullMask, slot, 0);
+    if (slot < 0) return -1;
+    StealTask* t = ws.tasks + slot;
+    t->H[g.lane] = H.w; t->P[g.lane] = P.w; t->G[g.lane] = G.w;
+    if (g.lane == 0) { t->ko = ko; t->move = move; t->is_capture = is_capture ? 1 : 0; t->remaining = remaining; }
+    __threadfence();
+    __syncwarp();
+    if (g.lane == 0) {
+        atomicAdd(&ws.counters[kCtlPosted], 1u);
+        atomicExch(&ws.task_status[slot], kTaskPosted);
+    }
+    return slot;
+}
+
+// A task leaves the "posted" state exactly once (taken, taken back, or cancelled); whoever moves
+// it keeps the count of posted tasks right.
+__device__ __forceinline__ bool steal_claim(const Workspace& ws, int slot, int new_status) {      // lane 0 only
+    if (atomicCAS(&ws.task_status[slot], kTaskPosted, new_status) != kTaskPosted) return false;
+    atomicSub(&ws.counters[kCtlPosted], 1u);
+    return true;
+}
+
+// Cancels a task this warp posted.  Whoever holds it last frees the slot.
+__device__ __forceinline__ void steal_cancel(const Workspace& ws, int slot) {      // lane 0 only
+    int* st = ws.task_status + slot;
+    for (;;) {
+        const int v = ld_vol(st);
+        if (v == kTaskPosted) { if (steal_claim(ws, slot, kTaskFree)) return; }
+        else if (v == kTaskTaken) { if (atomicCAS(st, kTaskTaken, kTaskCancelled) == kTaskTaken) return; }
+        else { atomicExch(st, kTaskFree); return; }                  // done: nobody else will touch it
+    }
+}
+
+struct TaskCancelled {                    // "has the task I am working on been cancelled?"
+    const int* status;                    // null for a search that works on a queue item
+    __device__ __forceinline__ bool operator()() const {
+        int c = 0;
+        if ((threadIdx.x & 31u) == 0u) c = status && ld_vol(status) == kTaskCancelled;
+        return __shfl_sync(kFullMask, c, 0) != 0;
+    }
+};
+
+// ladder_dfs (go_bb.cuh) with hand-over of replies.  `nodes` = moves tried so far by this search.
+__device__ __noinline__ int ladder_dfs_steal(const Workspace& ws, const Geo& g, BB H, BB P, BB G, int ko, BB pending,
+                                             bool frame_is_capture, int remaining_children, int nodes, int steal_after,
+                                             LadderStack& st, StealFrames& sf, const int* own_status, long long t_start)
+{
+    TaskCancelled cancelled{own_status};
+    int d = 0;
+    st.hunter[0] = H; st.prey[0] = P; st.group[0] = G; st.pending[0] = pending; st.ko[0] = (int16_t)ko;
+    sf.count[0] = 0; sf.offered[0] = 0;
+    for (;;) {
+        int v = -1;
+        // Once the search is long, every frame it stands on -- also the old, shallow ones it comes
+        // back to, whose remaining replies are the biggest pieces of work -- offers its extra replies.
+        if (nodes >= steal_after && !sf.offered[d]) {
+            sf.offered[d] = 1;
+            // keep the first reply, post up to kMaxPosted others
+            BB rest = andnot(st.pending[d], bb_single(bb_first(st.pending[d]) >= 0 ? bb_first(st.pending[d]) : 0, g));
+            const bool node_is_capture = frame_is_capture ^ ((d & 1) != 0);
+            while (sf.count[d] < kMaxPosted) {
+                const int m = bb_first(rest);
+                if (m < 0) break;
+                const int slot = steal_post(ws, g, st.hunter[d], st.prey[d], st.group[d], st.ko[d], m, !node_is_capture,
+                                            remaining_children - d);
+                if (slot < 0) break;
+                rest = andnot(rest, bb_single(m, g));
+                st.pending[d] = andnot(st.pending[d], bb_single(m, g));
+                sf.slot[d][sf.count[d]++] = (int16_t)slot;
+            }
+        }
+        const int m = bb_first(st.pending[d]);
+        if (m >= 0) {
+            if ((nodes & 15) == 15 && cancelled()) { v = kLadderAborted; }
+            else {
+                nodes++;
+                st.pending[d] = andnot(st.pending[d], bb_single(m, g));
+                const bool node_is_capture = frame_is_capture ^ ((d & 1) != 0);
+                H = st.hunter[d]; P = st.prey[d]; G = st.group[d]; ko = st.ko[d];
+                const int res = ladder_expand(g, !node_is_capture, H, P, G, ko, m, remaining_children - d, pending);
+                if (res == kLadderPush) {
+                    d++;
+                    st.hunter[d] = H; st.prey[d] = P; st.group[d] = G; st.pending[d] = pending; st.ko[d] = (int16_t)ko;
+                    sf.count[d] = 0; sf.offered[d] = 0;
+                    continue;
+                }
+                if (res == kLadderValue0) continue;                  // this reply does not refute; try the next
+                v = 0;
+            }
+        } else if (sf.count[d] > 0) {
+            // own replies are exhausted (all 0): collect one handed-over reply
+            const int slot = sf.slot[d][sf.count[d] - 1];
+            int* tstat = ws.task_status + slot;
+            const int mv = LANE0_INT(ld_vol(&ws.tasks[slot].move));   // read before the slot can be reused
+            const int took_back = LANE0_INT(steal_claim(ws, slot, kTaskFree));
+            if (took_back) {                                          // nobody wanted it: do it here after all
+                st.pending[d] = st.pending[d] | bb_single(mv, g);
+                sf.count[d]--;
+                continue;
+            }
+            int stt;
+            for (;;) {                                                // somebody is on it: wait for the value
+                stt = LANE0_INT(ld_vol(tstat));
+                if (stt == kTaskDone0 || stt == kTaskDone1) break;
+                if (cancelled()) { stt = -1; break; }
+                __nanosleep(200);
+                if (clock64() - t_start > 20000000000ll) __trap();   // never hang the device
+            }
+            if (stt < 0) v = kLadderAborted;
+            else {
+                if (g.lane == 0) atomicExch(tstat, kTaskFree);
+                sf.count[d]--;
+                if (stt == kTaskDone0) continue;
+                v = 0;                                                // that reply has value 1
+            }
+        } else v = 1;                                                 // every reply failed
+
+        // frame d returns v (0, 1, or kLadderAborted: unwind everything)
+        for (;;) {
+            if (g.lane == 0) for (int i = 0; i < sf.count[d]; i++) steal_cancel(ws, sf.slot[d][i]);
+            sf.count[d] = 0;
+            if (d == 0) return v;
+            d--;
+            if (v == kLadderAborted) continue;
+            if (v == 0) break;                                        // parent keeps looking
+            v = 0;                                                    // a child of value 1 refutes the parent
+        }
+    }
+}
+
+// is_ladder_capture / is_ladder_escape of one move on one prey group, with hand-over.
+__device__ __forceinline__ int ladder_search_steal(const Workspace& ws, const Geo& g, BB H, BB P, BB G, int ko, int move,
+                                                   bool is_capture, int remaining, int nodes, int steal_after, LadderStack& st,
+                                                   StealFrames& sf, const int* own_status, long long t_start) {
+    BB pending = bb_zero();
+    const int res = ladder_expand(g, is_capture, H, P, G, ko, move, remaining, pending);
+    if (res != kLadderPush) return res;
+    return ladder_dfs_steal(ws, g, H, P, G, ko, pending, is_capture, remaining - 1, nodes + 1, steal_after, st, sf, own_status, t_start);
+}
 
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
-ladder_kernel(const uint32_t* __restrict__ states, int S, Workspace ws)
+ladder_kernel(const uint32_t* __restrict__ states, int S, int steal_after, Workspace ws)
 {
     const Geo g = make_geo(S);
     LadderStack st;
-    const unsigned total = min((unsigned)ws.queue_cap, ws.counters[0]);
+    StealFrames sf;
+    const long long t_start = clock64();
+    const unsigned total = min((unsigned)ws.queue_cap, ws.counters[kCtlQueued]);
+
+    // ---- work items
     for (;;) {
         unsigned idx = 0;
-        if (g.lane == 0) idx = atomicAdd(&ws.counters[1], 1u);
+        if (g.lane == 0) idx = atomicAdd(&ws.counters[kCtlTaken], 1u);
         idx = __shfl_sync(kFullMask, idx, 0);
         if (idx >= total) break;
+        if (g.lane == 0) atomicAdd(&ws.counters[kCtlBusy], 1u);
         const uint32_t item = ws.queue[idx];
         const int pos = (int)(item >> 11), kind = (int)((item >> 10) & 1u), q = (int)(item & 1023u);
         const LoadedState s = load_state(states + (size_t)pos * RAG_STATE_WORDS, g);
         const BB own = s.player > 0 ? s.black : s.white;
         const BB opp = s.player > 0 ? s.white : s.black;
+        const int ko = p_to_q(s.ko_p, S);
+        const bool is_escape = kind == 1;
 #ifdef RAG_LADDER_TIMING
         const long long t_item = clock64();
 #endif
-        const int r = ladder_root(g, own, opp, p_to_q(s.ko_p, S), q, kind == 1, -1, st);
+        // top level (go.py:355-361, 422-428): any qualifying neighbour group
+        BB preys[4];
+        const int np = ladder_root_preys(g, own, opp, q, is_escape, preys);
+        int r = kLadderValue0;
+        for (int i = 0; i < np && r == kLadderValue0; i++)
+            r = is_escape ? ladder_search_steal(ws, g, opp, own, preys[i], ko, q, false, kLadderDepth, 0, steal_after, st, sf, nullptr, t_start)
+                          : ladder_search_steal(ws, g, own, opp, preys[i], ko, q, true, kLadderDepth, 0, steal_after, st, sf, nullptr, t_start);
 #ifdef RAG_LADDER_TIMING
         if (g.lane == 0) ws.queue[idx] = (uint32_t)((clock64() - t_item) >> 4);     // tools/ladder_profile.py
 #endif
-        if (r == kLadderValue1 && g.lane == 0)
-            atomicOr(ws.planes + (size_t)pos * kPlaneWords + (kPlaneLadderCapture + kind) * 32 + (q >> 5),
-                     1u << (q & 31));
+        if (g.lane == 0) {
+            if (r == kLadderValue1)
+                atomicOr(ws.planes + (size_t)pos * kPlaneWords + (kPlaneLadderCapture + kind) * 32 + (q >> 5), 1u << (q & 31));
+            __threadfence();
+            atomicSub(&ws.counters[kCtlBusy], 1u);
+        }
+    }
+
+    // ---- out of items: serve handed-over replies until nobody is busy
+    unsigned scan = (blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5)) * 37u;      // every warp starts its scans elsewhere
+    for (;;) {
+        int slot = -1;
+        for (;;) {
+            const unsigned posted = LANE0_INT(ld_vol(&ws.counters[kCtlPosted]));
+            if (posted != 0u) {
+                // one sweep over the status array, 32 entries at a time
+                for (unsigned k = 0; k < ws.task_cap && slot < 0; k += 32) {
+                    const unsigned i = (scan + k + g.lane) % ws.task_cap;
+                    const unsigned hit = __ballot_sync(kFullMask, ld_vol(&ws.task_status[i]) == kTaskPosted);
+                    if (hit) {
+                        const int cand = (int)((scan + k + (unsigned)(__ffs(hit) - 1)) % ws.task_cap);
+                        int ok = 0;
+                        if (g.lane == 0) {
+                            atomicAdd(&ws.counters[kCtlBusy], 1u);                 // before the claim: never "idle" while holding a task
+                            ok = steal_claim(ws, cand, kTaskTaken) ? 1 : 0;
+                            if (!ok) atomicSub(&ws.counters[kCtlBusy], 1u);
+                        }
+                        if (__shfl_sync(kFullMask, ok, 0)) slot = cand;
+                    }
+                }
+                scan += 97u;
+                if (slot >= 0) break;
+            }
+            const int done = LANE0_INT(ld_vol(&ws.counters[kCtlBusy]) == 0u && ld_vol(&ws.counters[kCtlPosted]) == 0u &&
+                                       ld_vol(&ws.counters[kCtlTaken]) >= total);
+            if (done) break;
+            __nanosleep(1000);
+            if (clock64() - t_start > 20000000000ll) __trap();        // never hang the device
+        }
+        if (slot < 0) break;
+        __threadfence();
+        StealTask* t = ws.tasks + slot;
+        int* tstat = ws.task_status + slot;
+        const BB H{__ldcg(&t->H[g.lane])}, P{__ldcg(&t->P[g.lane])}, G{__ldcg(&t->G[g.lane])};
+        const int ko = LANE0_INT(ld_vol(&t->ko)), move = LANE0_INT(ld_vol(&t->move));
+        const int is_capture = LANE0_INT(ld_vol(&t->is_capture)), remaining = LANE0_INT(ld_vol(&t->remaining));
+        const int r = ladder_search_steal(ws, g, H, P, G, ko, move, is_capture != 0, remaining, 0, steal_after, st, sf, tstat, t_start);
+        if (g.lane == 0) {
+            __threadfence();
+            if (r == kLadderAborted) atomicExch(tstat, kTaskFree);
+            else if (atomicCAS(tstat, kTaskTaken, r == kLadderValue1 ? kTaskDone1 : kTaskDone0) != kTaskTaken)
+                atomicExch(tstat, kTaskFree);                         // cancelled while it ran: nobody waits for it
+            atomicSub(&ws.counters[kCtlBusy], 1u);
+        }
+        __syncwarp();
     }
 }
 
@@ -344,7 +609,8 @@ playout_kernel(uint32_t* out, int n_positions, int S, uint64_t seed, int max_ply
 // the library carries these ~2.3 MB until the process exits, and no allocation call is ever needed.
 constexpr int kStaticMaxPositions = 256;
 constexpr size_t kStaticScratchBytes =                              // = workspace_bytes(kStaticMaxPositions)
-    (size_t)kCounterBytes + (size_t)kStaticMaxPositions * (kPlaneWords * 4 + 2 * kMaxBoard * kMaxBoard * 4);
+    ((size_t)kCounterBytes + (size_t)kStaticMaxPositions * (kPlaneWords * 4 + 2 * kMaxBoard * kMaxBoard * 4) + 511) / 512 * 512
+    + (size_t)(kStaticMaxPositions / 2) * (sizeof(StealTask) + 4);
 static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
 
 // In host code `g_static_scratch` is only a handle for the runtime, not an address a kernel could
@@ -365,6 +631,8 @@ static int static_scratch_address(void** out) {
     *out = per_device[dev];
     return RAG_OK;
 }
+
+static int g_steal_after = kStealAfterDefault;      // rag_set_ladder_handover
 
 static int check_size(int size) {
     if (size < 2 || size > kMaxBoard) return fail(RAG_EUNSUPPORTED, "board size %d not in [2, 19]", size);
@@ -459,6 +727,7 @@ int rag_features_analyze(const uint32_t* d_states, int n, int size, int with_lad
     cudaStream_t s = (cudaStream_t)stream;
     Workspace ws = carve(d_workspace, n);
     RAG_CUDA_CHECK(cudaMemsetAsync(ws.counters, 0, kCounterBytes, s));
+    RAG_CUDA_CHECK(cudaMemsetAsync(ws.tasks, 0, (size_t)ws.task_cap * (sizeof(StealTask) + 4), s));     // all tasks free, ring empty
     analyze_kernel<<<(n + kWarpsPerBlock - 1) / kWarpsPerBlock, kWarpsPerBlock * 32, 0, s>>>(d_states, n, size, with_ladders, ws);
     RAG_CUDA_CHECK(cudaGetLastError());
     if (with_ladders == 1) {
@@ -470,7 +739,7 @@ int rag_features_analyze(const uint32_t* d_states, int n, int size, int with_lad
         // and a convolution CTA of another stream (conv.cu) must still fit beside them.
         long long want = ((long long)n * 16 + kWarpsPerBlock - 1) / kWarpsPerBlock;
         int blocks = (int)(want < (long long)sms * 4 ? (want < 1 ? 1 : want) : (long long)sms * 4);
-        ladder_kernel<<<blocks, kWarpsPerBlock * 32, 0, s>>>(d_states, size, ws);
+        ladder_kernel<<<blocks, kWarpsPerBlock * 32, 0, s>>>(d_states, size, g_steal_after, ws);
         RAG_CUDA_CHECK(cudaGetLastError());
     }
     return RAG_OK;
@@ -491,7 +760,7 @@ int rag_features_ladders(const uint32_t* d_states, int n, int size, void* d_work
     RAG_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     long long want = ((long long)n * 16 + kWarpsPerBlock - 1) / kWarpsPerBlock;
     int blocks = (int)(want < (long long)sms * 4 ? (want < 1 ? 1 : want) : (long long)sms * 4);
-    ladder_kernel<<<blocks, kWarpsPerBlock * 32, 0, (cudaStream_t)stream>>>(d_states, size, ws);
+    ladder_kernel<<<blocks, kWarpsPerBlock * 32, 0, (cudaStream_t)stream>>>(d_states, size, g_steal_after, ws);
     RAG_CUDA_CHECK(cudaGetLastError());
     return RAG_OK;
 }
@@ -544,6 +813,8 @@ int rag_features(const uint32_t* d_states, int n, int size, const int32_t* h_pla
     if (int rc = rag_features_analyze(d_states, n, size, with_ladders, d_workspace, workspace_bytes_given, stream)) return rc;
     return rag_features_emit(d_workspace, n, size, h_plane_src, F, layout, conv_dtype, conv_channels, d_out, stream);
 }
+
+int rag_set_ladder_handover(int moves) { int old = g_steal_after; g_steal_after = moves < 0 ? 1 << 30 : moves; return old; }
 
 int rag_features_static_max_positions(void) { return kStaticMaxPositions; }
 

@@ -156,3 +156,26 @@ def test_device_playouts_replay_on_oracle():
     assert checked == n
     stones = (gb != 0).sum(axis=(1, 2))
     assert stones.max() > 200 and stones.min() < 10          # all game phases are covered
+
+
+@pytest.mark.parametrize("handover", [0, 3, 96, -1])
+def test_ladder_planes_do_not_depend_on_reply_handover(handover):
+    """Long ladder searches hand replies over to idle warps after `handover` tried moves
+    (0: from the start, -1: never).  The planes must be the reference's either way."""
+    from rocalphago_b200 import _cabi
+    L = _cabi.lib()
+    g = gu.load_features("features_playouts_19.npz")
+    b, a, ko, pl = go_oracle.random_playouts(4000, size=19, seed=301, max_ply=400, stride=5)
+    want = go_oracle.features(b, a, ko, pl, ["ladder_capture", "ladder_escape"])
+    old = L.rag_set_ladder_handover(handover)
+    try:
+        for rep in range(2):
+            got = _gpu_planes(g["board"], g["age"], g["ko"], g["player"], ["ladder_capture", "ladder_escape"])
+            assert np.array_equal(got, g["planes"][:, 44:46]), _explain(got, g["planes"][:, 44:46])
+            got = _gpu_planes(b, a, ko, pl, ["ladder_capture", "ladder_escape"])
+            assert np.array_equal(got, want), _explain(got, want)
+        small = gu.load_features("features_playouts_7.npz")
+        got = _gpu_planes(small["board"], small["age"], small["ko"], small["player"], ["ladder_escape", "ladder_capture"])
+        assert np.array_equal(got, small["planes"][:, [45, 44]])
+    finally:
+        L.rag_set_ladder_handover(old)
