@@ -187,6 +187,10 @@ def run_gpu(args):
     trace("process group up")
     L = _cabi.lib()
     net = CNNPolicy(DEFAULT_FEATURES, layers=12, filters_per_layer=192, dtype=args.dtype, seed=1234)
+    vnet = None
+    if args.workload == "policy+value":
+        from rocalphago_b200.models import CNNValue
+        vnet = CNNValue(DEFAULT_FEATURES + ["color"], layers=12, filters_per_layer=192, dtype=args.dtype, seed=4321)
     model = net.model
     plane_src = net.preprocessor.plane_src
     h = model._ensure_handle(dev)
@@ -239,7 +243,8 @@ def run_gpu(args):
     if args.no_pipeline:
         print(json.dumps({"serial_ms_per_step": serial_ms, "conv_pair": args.conv_pair}))
         return
-    pipe = EvalPipeline(net, n, device=dev)
+    pipe = EvalPipeline(net, n, device=dev, value_net=vnet)
+    first = (lambda r: r[0]) if vnet is not None else (lambda r: r)
     for i in range(W):
         pipe.submit(batches[i % pool].packed)
     pipe.drain()
@@ -281,8 +286,8 @@ def run_gpu(args):
     for k in range(K):
         t = pipe.submit(host_in[k % pool], to_host=True)
         if k > 0:
-            checksum += float(pipe.result(t - 1)[0, 0])
-    checksum += float(pipe.result(pipe.count - 1)[0, 0])
+            checksum += float(first(pipe.result(t - 1))[0, 0])
+    checksum += float(first(pipe.result(pipe.count - 1))[0, 0])
     f1 = pipe.mark()
     pipe.drain()
     barrier()
@@ -319,7 +324,8 @@ def run_gpu(args):
         k3 = float(np.mean(layer_ms[1:]))                      # the eleven 3x3 192->192 launches
         achieved = FLOP_3X3 * n / (k3 / 1e3) / 1e12
         line = {
-            "metric": METRIC, "value": value, "unit": "positions/s", "n_gpus": world, "steps": K,
+            "metric": METRIC if vnet is None else "positions/sec: 48/49-plane features + policy AND value CNN fwd, 19x19",
+            "value": value, "unit": "positions/s", "n_gpus": world, "steps": K,
             "warmup": W, "ms_per_step": dev_ms / K, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
             "config": {"workload": "48 planes (incl. ladders) + 13x192 policy forward, 19x19, batch %d/GPU, "
@@ -331,9 +337,9 @@ def run_gpu(args):
                              "input batches rotate; the --serial pass writes 256 MiB between steps",
                        "parallelism": "dp%d (independent batches, no collective on the data path)" % world},
             "e2e": {"value": e2e_val, "unit": "positions/s", "h2d_bytes_per_step": int(n * 768),
-                    "d2h_bytes_per_step": int(n * 361 * 4), "ms_per_step": max(e2e_ms, e2e_wall_ms) / K,
+                    "d2h_bytes_per_step": int(n * 361 * 4) + (int(n * 4) if vnet is not None else 0), "ms_per_step": max(e2e_ms, e2e_wall_ms) / K,
                     "checksum": checksum},
-            "gpu_launches": 16 * K,
+            "gpu_launches": (16 if vnet is None else 30) * K,
             "clocks": clocks,
             "roofline": {"bound": "tensor", "kernel": "conv_umma_kernel, 3x3 192->192 layer (11 of 12 conv launches per step)",
                          "achieved": achieved, "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
@@ -439,8 +445,9 @@ def main():
     ap.add_argument("--cpu-sample", type=int, default=512)
     ap.add_argument("--ref-sample", type=int, default=256)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default="policy", choices=["policy", "features"],
-                    help="policy: the flagship (features + 13x192 policy forward); features: BASELINE config 4")
+    ap.add_argument("--workload", default="policy", choices=["policy", "features", "policy+value"],
+                    help="policy: the flagship (features + 13x192 policy forward); features: BASELINE config 4; "
+                         "policy+value: BASELINE config 5 (adds the 49-plane 13x192 value forward to every step)")
     ap.add_argument("--serial", action="store_true", help="also time the single-stream rag_eval_batch step")
     ap.add_argument("--conv-pair", type=int, default=0, help="0: one CTA per tile; 1: CTA pairs (cta_group::2)")
     ap.add_argument("--no-pipeline", action="store_true", help="debug: skip the pipelined passes")

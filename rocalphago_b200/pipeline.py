@@ -18,7 +18,7 @@ from .state import STATE_WORDS, _ptr, _require_cuda
 
 
 class _Slot(object):
-    def __init__(self, L, handle, n, size, device, out_cols):
+    def __init__(self, L, handle, n, size, device, out_cols, value_handle=None):
         rows = int(L.rag_net_input_rows(handle, n))
         ch = int(L.rag_net_input_channels(handle))
         self.packed = torch.empty((n, STATE_WORDS), dtype=torch.int32, device=device)
@@ -26,6 +26,12 @@ class _Slot(object):
         self.fws = torch.empty(int(L.rag_features_workspace_bytes(n)), dtype=torch.uint8, device=device)
         self.out = torch.empty((n, out_cols) if out_cols else (n,), dtype=torch.float32, device=device)
         self.host_out = torch.empty_like(self.out, device="cpu").pin_memory()
+        self.vrows = self.vout = self.host_vout = None
+        if value_handle is not None:
+            self.vrows = torch.empty((int(L.rag_net_input_rows(value_handle, n)), int(L.rag_net_input_channels(value_handle))),
+                                     dtype=torch.float16, device=device)
+            self.vout = torch.empty((n,), dtype=torch.float32, device=device)
+            self.host_vout = torch.empty_like(self.vout, device="cpu").pin_memory()
         self.ana_done = torch.cuda.Event()
         self.feat_done = torch.cuda.Event()
         self.net_done = torch.cuda.Event()
@@ -45,9 +51,12 @@ class EvalPipeline(object):
     result that has not been collected on the device yet.
     """
 
-    def __init__(self, net, batch_size, device=None, size=None):
+    def __init__(self, net, batch_size, device=None, size=None, value_net=None):
+        """`value_net` (optional, a CNNValue): evaluated on the same positions in the same pass --
+        the analysis and the ladder search are shared, each network gets its own planes."""
         _require_cuda()
         self.net, self.model, self.n = net, net.model, int(batch_size)
+        self.value_net = value_net
         self.device = torch.device(device or "cuda", torch.cuda.current_device()) if device is None else torch.device(device)
         self.size = int(size or self.model.board)
         self.L = _cabi.lib()
@@ -56,9 +65,20 @@ class EvalPipeline(object):
         if len(self.plane_src) != self.model.input_dim:
             raise ValueError("feature list gives %d planes, the network takes %d" % (len(self.plane_src), self.model.input_dim))
         cols = self.model.board ** 2 if self.model.head == "policy" else 0
+        self.vhandle = self.vsrc = None
+        if value_net is not None:
+            if value_net.model.board != self.model.board:
+                raise ValueError("policy and value networks must have the same board size")
+            self.vhandle = value_net.model._ensure_handle(self.device)
+            self.vsrc = np.ascontiguousarray(value_net.preprocessor.plane_src, np.int32)
+            self.vchannels = int(self.L.rag_net_input_channels(self.vhandle))
+            self.vdtype_code = 0 if value_net.model.dtype == "bf16" else 1
         with torch.cuda.device(self.device):
-            self.slots = [_Slot(self.L, self.handle, self.n, self.size, self.device, cols) for _ in range(2)]
-            self.nws = torch.empty(int(self.L.rag_net_workspace_bytes(self.handle, self.n)), dtype=torch.uint8, device=self.device)
+            self.slots = [_Slot(self.L, self.handle, self.n, self.size, self.device, cols, self.vhandle) for _ in range(2)]
+            nws = int(self.L.rag_net_workspace_bytes(self.handle, self.n))
+            if self.vhandle is not None:
+                nws = max(nws, int(self.L.rag_net_workspace_bytes(self.vhandle, self.n)))
+            self.nws = torch.empty(nws, dtype=torch.uint8, device=self.device)
             # All four streams have the same priority.  (Giving the convolutions a higher one looked
             # attractive, but with the CTA-pair convolution kernel -- a cluster launch -- and the
             # persistent ladder kernel in flight together, prioritised streams stopped making
@@ -99,6 +119,10 @@ class EvalPipeline(object):
                 _cabi.check(L.rag_features_emit(_ptr(slot.fws), self.n, self.size, src, len(self.plane_src), LAYOUT_CONV_IN,
                                                 self.dtype_code, self.channels, _ptr(slot.rows),
                                                 vp(self.s_feat.cuda_stream)))
+                if self.vhandle is not None:
+                    _cabi.check(L.rag_features_emit(_ptr(slot.fws), self.n, self.size, self.vsrc.ctypes.data_as(vp), len(self.vsrc),
+                                                    LAYOUT_CONV_IN, self.vdtype_code, self.vchannels, _ptr(slot.vrows),
+                                                    vp(self.s_feat.cuda_stream)))
                 slot.feat_done.record(self.s_feat)
             # stage 2: convolutions + head
             with torch.cuda.stream(self.s_net):
@@ -107,11 +131,16 @@ class EvalPipeline(object):
                     self.s_net.wait_event(slot.out_copied)         # the previous result of this slot has been copied out
                 _cabi.check(L.rag_net_forward_rows(self.handle, _ptr(slot.rows), self.n, _ptr(slot.out), _ptr(self.nws),
                                                    self.nws.numel(), vp(self.s_net.cuda_stream)))
+                if self.vhandle is not None:
+                    _cabi.check(L.rag_net_forward_rows(self.vhandle, _ptr(slot.vrows), self.n, _ptr(slot.vout), _ptr(self.nws),
+                                                       self.nws.numel(), vp(self.s_net.cuda_stream)))
                 slot.net_done.record(self.s_net)
             with torch.cuda.stream(self.s_copy):
                 self.s_copy.wait_event(slot.net_done)
                 if to_host:
                     slot.host_out.copy_(slot.out, non_blocking=True)
+                    if self.vhandle is not None:
+                        slot.host_vout.copy_(slot.vout, non_blocking=True)
                 slot.out_copied.record(self.s_copy)
         slot.used = True
         slot.to_host = to_host
@@ -125,7 +154,10 @@ class EvalPipeline(object):
             raise ValueError("ticket %d is no longer (or not yet) in flight" % ticket)
         slot = self.slots[ticket % 2]
         slot.out_copied.synchronize()
-        return slot.host_out if slot.to_host else slot.out
+        out = slot.host_out if slot.to_host else slot.out
+        if self.vhandle is not None:
+            return out, (slot.host_vout if slot.to_host else slot.vout)
+        return out
 
     def mark(self):
         """A CUDA event recorded behind everything submitted so far (for timing)."""

@@ -299,3 +299,22 @@ def test_cta_pair_convolution_kernel_matches_single_cta_kernel():
     finally:
         L.rag_set_conv_pair(old)
     assert np.array_equal(single, pair)
+
+
+def test_pipeline_with_policy_and_value_networks():
+    """BASELINE config 5's shape: one pass gives move probabilities and a value per position; the
+    analysis and the ladder search are shared between the two networks."""
+    from rocalphago_b200.pipeline import EvalPipeline
+    n = 64
+    pol = CNNPolicy(go_oracle.DEFAULT_FEATURES, layers=3, filters_per_layer=64, dtype="fp16", seed=51)
+    val = CNNValue(go_oracle.DEFAULT_FEATURES + ["color"], layers=3, filters_per_layer=64, dtype="fp16", seed=52)
+    batches = [BatchedGameState.random_playouts(n, seed=900 + i, max_ply=350, stride=5) for i in range(3)]
+    pipe = EvalPipeline(pol, n, value_net=val)
+    for i, b in enumerate(batches):
+        t = pipe.submit(b.packed, to_host=(i == 1))
+        probs, values = pipe.result(t)
+        want_p = pol.model.eval_batch_device(b, pol.preprocessor.plane_src).cpu().numpy()
+        want_v = val.model.eval_batch_device(b, val.preprocessor.plane_src).cpu().numpy()
+        assert np.array_equal(probs.cpu().numpy(), want_p)
+        assert np.array_equal(values.cpu().numpy(), want_v)
+    pipe.drain()
