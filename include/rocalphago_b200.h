@@ -142,6 +142,18 @@ int rag_features_static_max_positions(void);
  * (rows past n*S*S are never written nor used). */
 long long rag_conv_rows(int n, int size);
 
+/* ------------------------------------------------------------------ batched players
+ *
+ * GreedyPolicyPlayer.get_move (ai.py:18-45) / ProbabilisticPolicyPlayer.get_moves (ai.py:107-133)
+ * for a batch, on the device: d_probs float [n][S*S] from a policy forward, d_workspace the
+ * analysis of the same n states (its sensibleness plane = get_legal_moves(include_eyes=False)).
+ * The probabilities are restricted to the sensible moves, renormalised, raised to 1/temperature,
+ * and either the most probable move is taken (greedy != 0) or one is drawn (seeded: splitmix64 of
+ * seed and position index; the reference draws from numpy's global generator, so only the
+ * distribution can match).  d_moves[i] = x*S+y, or -1 (pass) when no sensible move exists. */
+int rag_select_moves(const float* d_probs, const void* d_workspace, int n, int size, float temperature,
+                     int greedy, uint64_t seed, int32_t* d_moves, void* stream);
+
 /* ------------------------------------------------------------------ state updates
  *
  * GameState.do_move (go.py:521-581) on packed states, in place, one move per

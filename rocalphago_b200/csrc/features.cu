@@ -632,6 +632,80 @@ static int static_scratch_address(void** out) {
     return RAG_OK;
 }
 
+// ---- move selection for batched players (ai.py:33-45, 84-133) ----------------------------------
+//
+// One warp per position: the network's probabilities restricted to the sensible moves (plane 46 of
+// the analysis: legal and not an own eye -- get_legal_moves(include_eyes=False)), renormalised,
+// raised to beta = 1/temperature (apply_temperature, ai.py:57-66), then either the most probable
+// move (greedy; first in x-major order on ties, as max() over the move list picks) or a draw.
+// -1 = pass, when no sensible move exists.
+__global__ void __launch_bounds__(128)
+select_moves_kernel(const float* __restrict__ probs, const uint32_t* __restrict__ planes, int n, int S, float beta,
+                    int greedy, unsigned long long seed, int32_t* __restrict__ moves)
+{
+    const int pos = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (pos >= n) return;
+    const int P = S * S;
+    const uint32_t* sens = planes + (size_t)pos * kPlaneWords + kPlaneSensibleness * 32;
+    const float* pr = probs + (size_t)pos * P;
+    // log-space weights of my points (12 per lane cover 19x19)
+    float lw[12];
+    float mx = -INFINITY;
+    #pragma unroll
+    for (int j = 0; j < 12; j++) {
+        const int i = lane + 32 * j;
+        lw[j] = -INFINITY;
+        if (i < P) {
+            const int x = i / S, y = i - x * S;
+            if ((__ldg(sens + x) >> y) & 1u) lw[j] = beta * logf(fmaxf(pr[i], 1e-37f));
+        }
+        mx = fmaxf(mx, lw[j]);
+    }
+    for (int o = 16; o; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if (mx == -INFINITY) { if (lane == 0) moves[pos] = -1; return; }          // nothing sensible: pass
+    if (greedy) {
+        int best = 1 << 30;
+        #pragma unroll
+        for (int j = 0; j < 12; j++) if (lw[j] == mx) best = min(best, lane + 32 * j);
+        for (int o = 16; o; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+        if (lane == 0) moves[pos] = best;
+        return;
+    }
+    float w[12], mine = 0.f;
+    #pragma unroll
+    for (int j = 0; j < 12; j++) { w[j] = lw[j] == -INFINITY ? 0.f : expf(lw[j] - mx); mine += w[j]; }
+    float incl = mine;                                                         // inclusive scan over lanes
+    for (int o = 1; o < 32; o <<= 1) { float t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+    const float total = __shfl_sync(0xffffffffu, incl, 31);
+    // one uniform number per (seed, position): splitmix64
+    unsigned long long z = seed + 0x9E3779B97F4A7C15ull * (unsigned long long)(pos + 1);
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull; z = (z ^ (z >> 27)) * 0x94D049BB133111EBull; z ^= z >> 31;
+    const float u = (float)((z >> 40) + 0.5) * (1.0f / 16777216.0f) * total;   // in (0, total)
+    // the points are ordered lane-major here (lane 0 owns 0, 32, 64 ...), which is a fixed
+    // permutation of the move list: the draw is exact for the distribution either way
+    const float before = incl - mine;
+    const bool in_me = u >= before && u < incl;
+    const unsigned who = __ballot_sync(0xffffffffu, in_me);
+    int chosen = -1;
+    const int src_lane = who ? __ffs(who) - 1 : -1;
+    if (lane == src_lane) {
+        float acc = before;
+        #pragma unroll
+        for (int j = 0; j < 12; j++) { if (w[j] > 0.f) { chosen = lane + 32 * j; acc += w[j]; if (u < acc) break; } }
+    }
+    if (src_lane < 0) {                                                        // rounding at the very end: last sensible point
+        int last = -1;
+        #pragma unroll
+        for (int j = 0; j < 12; j++) if (w[j] > 0.f) last = max(last, lane + 32 * j);
+        for (int o = 16; o; o >>= 1) last = max(last, __shfl_xor_sync(0xffffffffu, last, o));
+        chosen = last;
+        if (lane == 0) moves[pos] = chosen;
+        return;
+    }
+    chosen = __shfl_sync(0xffffffffu, chosen, src_lane);
+    if (lane == 0) moves[pos] = chosen;
+}
+
 static int g_steal_after = kStealAfterDefault;      // rag_set_ladder_handover
 
 static int check_size(int size) {
@@ -837,6 +911,20 @@ int rag_features_static(const uint32_t* d_states, int n, int size, const int32_t
 }
 
 long long rag_conv_rows(int n, int size) { return conv_rows(n, size); }
+
+int rag_select_moves(const float* d_probs, const void* d_workspace, int n, int size, float temperature, int greedy,
+                     uint64_t seed, int32_t* d_moves, void* stream)
+{
+    if (n < 0 || (n > 0 && (!d_probs || !d_workspace || !d_moves))) return fail(RAG_EINVAL, "null argument");
+    if (int rc = check_size(size)) return rc;
+    if (!(temperature > 0.f)) return fail(RAG_EINVAL, "temperature must be positive (got %g)", (double)temperature);
+    if (n == 0) return RAG_OK;
+    const uint32_t* planes = (const uint32_t*)((const char*)d_workspace + kCounterBytes);
+    select_moves_kernel<<<(n + 3) / 4, 128, 0, (cudaStream_t)stream>>>(d_probs, planes, n, size, 1.0f / temperature, greedy,
+                                                                    (unsigned long long)seed, d_moves);
+    RAG_CUDA_CHECK(cudaGetLastError());
+    return RAG_OK;
+}
 
 int rag_do_move(uint32_t* d_states, int n, int size, const int32_t* d_moves, int32_t* d_status, void* stream)
 {
