@@ -367,8 +367,12 @@ ladder_kernel(const uint32_t* __restrict__ states, int S, int steal_after, Works
         }
     }
 
-    // ---- out of items: serve handed-over replies until nobody is busy
-    unsigned scan = (blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5)) * 37u;      // every warp starts its scans elsewhere
+    // ---- out of items: serve handed-over replies until nobody is busy.  One warp per CTA stays for
+    // that (there are never more than a few dozen tasks in flight); idle warps sleep between looks,
+    // longer each time, so that they take neither issue slots nor L2 bandwidth from the searches.
+    if (steal_after >= (1 << 29) || (threadIdx.x >> 5) != 0) return;
+    unsigned scan = blockIdx.x * 37u;                                              // every warp starts its scans elsewhere
+    unsigned nap = 500;
     for (;;) {
         int slot = -1;
         for (;;) {
@@ -395,10 +399,12 @@ ladder_kernel(const uint32_t* __restrict__ states, int S, int steal_after, Works
             const int done = LANE0_INT(ld_vol(&ws.counters[kCtlBusy]) == 0u && ld_vol(&ws.counters[kCtlPosted]) == 0u &&
                                        ld_vol(&ws.counters[kCtlTaken]) >= total);
             if (done) break;
-            __nanosleep(1000);
+            __nanosleep(nap);
+            if (nap < 8000) nap += nap / 2;
             if (clock64() - t_start > 20000000000ll) __trap();        // never hang the device
         }
         if (slot < 0) break;
+        nap = 500;
         __threadfence();
         StealTask* t = ws.tasks + slot;
         int* tstat = ws.task_status + slot;

@@ -73,6 +73,10 @@ RAG_FN BB andnot(BB a, BB b) { return BB{a.w & ~b.w}; }             // a & ~b
 RAG_FN bool bb_any(BB a) { return __any_sync(kFullMask, a.w != 0u) != 0; }
 RAG_FN bool bb_equal(BB a, BB b) { return __all_sync(kFullMask, a.w == b.w) != 0; }
 RAG_FN int bb_count(BB a) { return (int)__reduce_add_sync(kFullMask, (unsigned)__popc(a.w)); }
+// several "is this set non-empty?" questions answered by ONE warp reduction: bit i of the result is bb_any(x_i)
+RAG_FN unsigned bb_any4(BB a, BB b, BB c, BB d) {
+    return __reduce_or_sync(kFullMask, (a.w ? 1u : 0u) | (b.w ? 2u : 0u) | (c.w ? 4u : 0u) | (d.w ? 8u : 0u));
+}
 RAG_FN BB bb_single(int q, const Geo& g) { return BB{(g.lane == (uint32_t)(q >> 5)) ? (1u << (q & 31)) : 0u}; }
 RAG_FN bool bb_test(BB a, int q) { return ((__shfl_sync(kFullMask, a.w, q >> 5) >> (q & 31)) & 1u) != 0u; }
 // lowest point in x-major order, or -1
@@ -131,6 +135,9 @@ RAG_FN void bb_store(uint32_t* rows32, BB a, const Geo& g) { rows32[g.lane] = a.
 
 struct BB { uint32_t w[32]; };
 struct Geo { int S; uint32_t rowmask; };
+// host-only operation counters (tools/ladder_study.py): how many warp collectives would the device issue?
+struct OpCounts { long long nbrs, any, count, first, test, flood_calls, flood_iters, from_dir; };
+static OpCounts g_ops = {0, 0, 0, 0, 0, 0, 0, 0};
 
 RAG_FN Geo make_geo(int S) { Geo g; g.S = S; g.rowmask = (1u << S) - 1u; return g; }
 RAG_FN uint32_t rm(const Geo& g, int r) { return r < g.S ? g.rowmask : 0u; }
@@ -140,12 +147,16 @@ RAG_FN BB operator&(BB a, BB b) { for (int i = 0; i < 32; i++) a.w[i] &= b.w[i];
 RAG_FN BB operator|(BB a, BB b) { for (int i = 0; i < 32; i++) a.w[i] |= b.w[i]; return a; }
 RAG_FN BB operator^(BB a, BB b) { for (int i = 0; i < 32; i++) a.w[i] ^= b.w[i]; return a; }
 RAG_FN BB andnot(BB a, BB b) { for (int i = 0; i < 32; i++) a.w[i] &= ~b.w[i]; return a; }
-RAG_FN bool bb_any(BB a) { for (int i = 0; i < 32; i++) if (a.w[i]) return true; return false; }
-RAG_FN bool bb_equal(BB a, BB b) { for (int i = 0; i < 32; i++) if (a.w[i] != b.w[i]) return false; return true; }
-RAG_FN int bb_count(BB a) { int c = 0; for (int i = 0; i < 32; i++) c += __builtin_popcount(a.w[i]); return c; }
+RAG_FN bool bb_any(BB a) { g_ops.any++; for (int i = 0; i < 32; i++) if (a.w[i]) return true; return false; }
+RAG_FN bool bb_equal(BB a, BB b) { g_ops.any++; for (int i = 0; i < 32; i++) if (a.w[i] != b.w[i]) return false; return true; }
+RAG_FN int bb_count(BB a) { g_ops.count++; int c = 0; for (int i = 0; i < 32; i++) c += __builtin_popcount(a.w[i]); return c; }
+RAG_FN unsigned bb_any4(BB a, BB b, BB c, BB d) {
+    return (bb_any(a) ? 1u : 0u) | (bb_any(b) ? 2u : 0u) | (bb_any(c) ? 4u : 0u) | (bb_any(d) ? 8u : 0u);
+}
 RAG_FN BB bb_single(int q, const Geo&) { BB r = bb_zero(); r.w[q >> 5] = 1u << (q & 31); return r; }
-RAG_FN bool bb_test(BB a, int q) { return (a.w[q >> 5] >> (q & 31)) & 1u; }
+RAG_FN bool bb_test(BB a, int q) { g_ops.test++; return (a.w[q >> 5] >> (q & 31)) & 1u; }
 RAG_FN int bb_first(BB a) {
+    g_ops.first++;
     for (int i = 0; i < 32; i++) if (a.w[i]) return (i << 5) | __builtin_ctz(a.w[i]);
     return -1;
 }
@@ -159,6 +170,7 @@ RAG_FN int bb_select(BB a, int r) {
 }
 RAG_FN BB bb_nbrs(BB a, const Geo& g) {
     BB r;
+    g_ops.nbrs++;
     for (int i = 0; i < 32; i++) {
         uint32_t up = i > 0 ? a.w[i - 1] : 0u, dn = i < 31 ? a.w[i + 1] : 0u;
         r.w[i] = (up | dn | (a.w[i] << 1) | (a.w[i] >> 1)) & rm(g, i);
@@ -166,6 +178,7 @@ RAG_FN BB bb_nbrs(BB a, const Geo& g) {
     return r;
 }
 RAG_FN BB bb_from_north(BB a, const Geo& g, bool fill) {
+    g_ops.from_dir++;
     BB r; for (int i = 0; i < 32; i++) r.w[i] = (i > 0 ? a.w[i - 1] : (fill ? kFullMask : 0u)) & rm(g, i); return r;
 }
 RAG_FN BB bb_from_south(BB a, const Geo& g, bool fill) {
@@ -191,7 +204,13 @@ RAG_FN void bb_store(uint32_t* rows32, BB a, const Geo&) { for (int i = 0; i < 3
 // Device-side twin of group_sets[x][y] (go.py:49,125-157): a fixed point of dilation.
 RAG_FN BB bb_flood(BB seed, BB mask, const Geo& g) {
     BB cur = seed;
+#if !RAG_DEVICE_BUILD
+    g_ops.flood_calls++;
+#endif
     for (;;) {
+#if !RAG_DEVICE_BUILD
+        g_ops.flood_iters++;
+#endif
         BB nx = (cur | bb_nbrs(cur, g)) & mask;
         nx = (nx | bb_nbrs(nx, g)) & mask;
         if (bb_equal(nx, cur)) return cur;
@@ -222,19 +241,22 @@ RAG_FN int q_diagonal(int q, int i, int S) {
 // legal by go.py:267-285 (occupied, ko, suicide; superko is not enforced on this path).
 // Captures are resolved in the reference's neighbour order so that the ko point, including
 // the "stale ko" of SURVEY H3, comes out the same (go.py:542-561).
-RAG_FN bool bb_play(const Geo& g, BB& M, BB& O, int& ko, int q, int* captured) {
+RAG_FN bool bb_play_ex(const Geo& g, BB& M, BB& O, int& ko, int q, int* captured, BB& ptn_out) {
     if (q == ko) return false;
     const BB pt = bb_single(q, g);
-    if (bb_any((M | O) & pt)) return false;
     const BB M2 = M | pt;
     BB O2 = O;
     int newko = -1, ncap = 0;
     const BB ptn = bb_nbrs(pt, g);
+    ptn_out = ptn;
     const BB empty2 = andnot(bb_board(g), M2 | O);
     // Only an enemy neighbour with no empty point next to that very stone can be captured;
     // most moves have none, and then no group needs to be traced at all.
     const BB maybe = andnot(ptn & O, bb_nbrs(empty2, g));
-    if (bb_any(maybe)) {
+    // occupied? / capture candidates? / an empty neighbour? / a friendly neighbour?  -- one reduction
+    const unsigned f = bb_any4((M | O) & pt, maybe, ptn & empty2, ptn & M);
+    if (f & 1u) return false;
+    if (f & 2u) {
         for (int d = 0; d < 4; d++) {
             int nq = q_neighbor(q, d, g.S);
             if (nq < 0 || !bb_test(maybe & O2, nq)) continue;
@@ -247,21 +269,25 @@ RAG_FN bool bb_play(const Geo& g, BB& M, BB& O, int& ko, int q, int* captured) {
             if (sz == 1) {                                          // go.py:553-561
                 // recapture would take exactly the played stone: it is alone and its only
                 // liberty is the point just emptied
-                bool alone = !bb_any(ptn & M);
                 BB e2 = andnot(bb_board(g), M2 | O2);
-                if (alone && bb_count(ptn & e2) == 1) newko = nq;
+                if (!(f & 8u) && bb_count(ptn & e2) == 1) newko = nq;
             }
         }
     }
     // suicide (go.py:219-240): a capture or an empty neighbour leaves the stone a liberty;
     // otherwise the group it joined must have one somewhere
-    if (ncap == 0 && !bb_any(ptn & empty2)) {
+    if (ncap == 0 && !(f & 4u)) {
         BB me = bb_flood(pt, M2, g);
         if (!bb_any(bb_nbrs(me, g) & empty2)) return false;
     }
     M = M2; O = O2; ko = newko;
     if (captured) *captured = ncap;
     return true;
+}
+
+RAG_FN bool bb_play(const Geo& g, BB& M, BB& O, int& ko, int q, int* captured) {
+    BB ptn;
+    return bb_play_ex(g, M, O, ko, q, captured, ptn);
 }
 
 // ------------------------------------------------------------------ eyes  (go.py:287-327)
@@ -522,7 +548,8 @@ RAG_FN int ladder_expand(const Geo& g, bool is_capture, BB& H, BB& P, BB& G, int
 #if !RAG_DEVICE_BUILD
     if (g_ladder_node_hook) g_ladder_node_hook(H.w, P.w, ko, is_capture ? 1 : 0, mv);
 #endif
-    bool ok = is_capture ? bb_play(g, H, P, ko, mv, nullptr) : bb_play(g, P, H, ko, mv, nullptr);
+    BB ptn;
+    bool ok = is_capture ? bb_play_ex(g, H, P, ko, mv, nullptr, ptn) : bb_play_ex(g, P, H, ko, mv, nullptr, ptn);
     if (!ok) return kLadderValue0;
     if (remaining <= 0) return is_capture ? kLadderValue1 : kLadderValue0;
     const BB empty = andnot(bb_board(g), H | P);
@@ -530,11 +557,11 @@ RAG_FN int ladder_expand(const Geo& g, bool is_capture, BB& H, BB& P, BB& G, int
         // The prey side moved.  Its group G grows only if the new stone touches it (a reply can
         // also be a capture elsewhere); other groups of its colour the stone touches join too.
         // A hunter move never changes G: the group keeps a liberty, so it is not what is captured.
-        const BB pt = bb_single(mv, g), ptn = bb_nbrs(pt, g);
-        if (bb_any(ptn & G)) {
-            const BB extra = andnot(ptn & P, G);
-            G = G | pt;
-            if (bb_any(extra)) G = G | bb_flood(extra, P, g);
+        const BB extra = andnot(ptn & P, G);
+        const unsigned f = bb_any4(ptn & G, extra, bb_zero(), bb_zero());
+        if (f & 1u) {
+            G = G | bb_single(mv, g);
+            if (f & 2u) G = G | bb_flood(extra, P, g);
         }
     }
     const BB gn = bb_nbrs(G, g);

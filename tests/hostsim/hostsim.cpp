@@ -11,6 +11,8 @@
 #include <stdlib.h>
 
 using namespace rag;
+static int g_skip_ladders = 0;
+extern "C" void hostsim_skip_ladders(int v) { g_skip_ladders = v; }
 
 extern "C" int hostsim_features(int n, int S, const int8_t* board, const int16_t* age, const int32_t* ko,
                                 const int32_t* player, uint8_t* out, int64_t* stats, int64_t* item_nodes, int64_t item_cap)
@@ -40,7 +42,7 @@ extern "C" int hostsim_features(int n, int S, const int8_t* board, const int16_t
         BB cand_cap = A.legal & bb_nbrs(A.opp_lib2, g);
         BB cand_esc = A.legal & bb_nbrs(A.own_atari, g);
         if (stats) { stats[0] += bb_count(cand_cap); stats[1] += bb_count(cand_esc); }
-        for (int kind = 0; kind < 2; kind++) {
+        for (int kind = 0; kind < 2 && !g_skip_ladders; kind++) {
             BB rem = kind ? cand_esc : cand_cap;
             for (;;) {
                 int q = bb_first(rem);
@@ -118,4 +120,11 @@ extern "C" long long hostsim_ladder_distinct(int S, const int8_t* board, int ko,
     if (per_depth) for (int i = 0; i < 96; i++) per_depth[i] = g_ladder_stats.per_depth[i];
     g_ladder_node_hook = nullptr; free(lst);
     return (long long)seen.size();
+}
+
+extern "C" void hostsim_opcounts(long long* out, int reset)
+{
+    out[0] = g_ops.nbrs; out[1] = g_ops.any; out[2] = g_ops.count; out[3] = g_ops.first; out[4] = g_ops.test;
+    out[5] = g_ops.flood_calls; out[6] = g_ops.flood_iters; out[7] = g_ops.from_dir; out[8] = g_ladder_stats.nodes;
+    if (reset) { g_ops = OpCounts{0, 0, 0, 0, 0, 0, 0, 0}; }
 }

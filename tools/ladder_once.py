@@ -1,0 +1,13 @@
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from rocalphago_b200 import BatchedGameState, Preprocess, _cabi
+from rocalphago_b200.state import _ptr, _stream
+L = _cabi.lib(); pp = Preprocess()
+n = 4096; L.rag_set_ladder_handover(-1)
+b = BatchedGameState.random_playouts(n, seed=7)
+ws = pp._ws.get(n, b.device)
+for _ in range(3):
+    _cabi.check(L.rag_features_analyze(_ptr(b.packed), n, 19, 1, _ptr(ws), ws.numel(), _stream()))
+torch.cuda.synchronize()
+print("ok")
