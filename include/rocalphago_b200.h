@@ -121,7 +121,7 @@ int rag_features(const uint32_t* d_states, int n, int size, const int32_t* h_pla
  * framework's memory pool, or a latency-critical loop (a GTP engine answering under a clock)
  * that cannot afford the device-wide synchronisation an allocation may imply.  For them the
  * scratch of the analysis and ladder kernels lives in the library itself: a fixed array in device
- * memory, about 2.3 MB on every GPU that loads the library, kept until the process exits.
+ * memory, about 2.4 MB on every GPU that loads the library, kept until the process exits.
  *
  *   - at most rag_features_static_max_positions() (= 256) positions per call; more is refused
  *     with RAG_ENOMEM and a message -- split the batch or use rag_features
@@ -198,6 +198,10 @@ typedef struct rag_net_desc {
     int dtype;                       /* RAG_DTYPE_BF16 / RAG_DTYPE_FP16 operands */
     int kernel_flip;                 /* 1: Theano semantics (true convolution, the reference's
                                         pinned backend); 0: cross-correlation (TensorFlow) */
+    int resnet;                      /* 1: ResnetPolicy (policy.py:141-271): convolution 1 is linear, every
+                                        later one is BatchNormalization -> ReLU -> convolution, units are
+                                        closed by adding the unit's input, a last ReLU precedes the 1x1 */
+    int unit_end[RAG_MAX_LAYERS];    /* resnet: 1 where convolution K closes a unit (n_skip_K, policy.py:220) */
 } rag_net_desc;
 
 typedef struct rag_net rag_net;
@@ -208,6 +212,8 @@ int rag_net_destroy(rag_net* net);
 /* Keras model.get_weights() order and layouts: per conv layer W (out, in, kh, kw) and b (out,);
  * the 1x1 conv's W (1, in, 1, 1) and b (1,); then policy: Bias W (S*S,)  (nn_util.py:128-133);
  * value: Dense W (S*S, units), b (units,), Dense W (units, 1), b (1,)  (value.py:27-28).
+ * Residual networks: every convolution after the first is preceded by its BatchNormalization's
+ * gamma, beta, running_mean, running_std, each (S,) (Keras-1 default axis -1).
  * Host float arrays; copies them to the device (synchronous). */
 int rag_net_num_weight_arrays(const rag_net* net);
 int rag_net_load_weights(rag_net* net, const float* const* h_arrays, int n_arrays);

@@ -75,3 +75,37 @@ def forward(weights, x, specs, head="policy", kernel_flip=True, threads=None, re
         d1 = flat @ torch.from_numpy(np.asarray(weights[i], np.float32)) + torch.from_numpy(np.asarray(weights[i + 1], np.float32))
         d2 = d1 @ torch.from_numpy(np.asarray(weights[i + 2], np.float32)) + torch.from_numpy(np.asarray(weights[i + 3], np.float32))
         return torch.tanh(d2).reshape(-1).numpy()
+
+
+def forward_resnet(weights, x, specs, unit_end, kernel_flip=True, threads=None, eps=1e-3):
+    """ResnetPolicy.create_network (policy.py:141-271) at inference.  specs = [(filters, width)] of
+    every convolution (the first one included), unit_end[i] = 1 where convolution i closes a
+    residual unit.  weights in Keras get_weights() order: conv1 W, b; then per convolution
+    BatchNormalization gamma, beta, running_mean, running_std -- each of shape (S,), because
+    BatchNormalization() defaults to axis=-1 in Keras 1.2.0, the y coordinate under 'th'
+    ordering -- and W, b; then the 1x1 W, b and the Bias vector."""
+    if threads:
+        torch.set_num_threads(int(threads))
+    t = lambda a: torch.from_numpy(np.asarray(a, np.float32))  # noqa: E731
+    with torch.no_grad():
+        h = torch.as_tensor(np.asarray(x, dtype=np.float32))
+        W, b = t(weights[0]), t(weights[1])
+        k = specs[0][1]
+        path = F.conv2d(h, W.flip(2, 3) if kernel_flip else W, b, padding=k // 2)          # linear
+        block_input = path
+        i = 2
+        for c in range(1, len(specs)):
+            gamma, beta, mean, var = (t(weights[i + j]) for j in range(4))
+            path = (path - mean) * (gamma / torch.sqrt(var + eps)) + beta                   # broadcast over the last axis
+            path = F.relu(path)
+            W, b = t(weights[i + 4]), t(weights[i + 5])
+            k = specs[c][1]
+            path = F.conv2d(path, W.flip(2, 3) if kernel_flip else W, b, padding=k // 2)
+            i += 6
+            if unit_end[c]:
+                path = block_input + path
+                block_input = path
+        path = F.relu(path)
+        path = F.conv2d(path, t(weights[i]), t(weights[i + 1]))
+        logits = path.reshape(path.shape[0], -1) + t(weights[i + 2])
+        return torch.softmax(logits, dim=1).numpy()

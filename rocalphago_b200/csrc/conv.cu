@@ -45,13 +45,20 @@ constexpr int kATileBytes = kTileM * kChunkK * 2;     // 16 KiB
 struct ConvParams {
     int tiles, width, kchunks, N, stages, dtype;
     int S, n;                 // board size, boards
-    int mode;                 // 0: write 16-bit pixel rows; 1: fused 1x1 head -> fp32 logits
+    int mode;                 // 0: write 16-bit pixel rows; 1: fused 1x1 head -> fp32 logits;
+                              // 2 / 3: the same for a residual network (see the epilogue)
     int relu;
     long long rows;           // n * S * S
     const float* bias;        // [N]
     const float* head_w;      // [N]   (mode 1)
     float head_b;
     void* out;
+    // residual networks (policy.py:141-271): L = conv + bias (+ residual); `linear_out` keeps L when it
+    // is a unit's output; what the next convolution reads is relu(L * bn_scale[y] + bn_shift[y])
+    const uint16_t* residual;     // [rows][N] or null
+    uint16_t* linear_out;         // [rows][N] or null
+    const float* bn_scale;        // [S] (indexed by y, the reference's BatchNormalization axis) or null
+    const float* bn_shift;
 };
 
 // ---- PTX wrappers ----------------------------------------------------------------------------
@@ -219,7 +226,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
     for (int i = threadIdx.x; i < p.N; i += blockDim.x) {
         s_bias[i] = p.bias[i];
-        s_head[i] = p.mode == 1 ? p.head_w[i] : 0.f;
+        s_head[i] = (p.mode == 1 || p.mode == 3) ? p.head_w[i] : 0.f;
     }
     tc_fence_before();
     __syncthreads();
@@ -329,7 +336,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                             dst[j] = make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
                     }
                 }
-            } else {
+            } else if (p.mode == 1) {
                 float acc = 0.f;
                 for (int c0 = 0; c0 < p.N; c0 += 32) {
                     uint32_t v[32];
@@ -343,6 +350,61 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     }
                 }
                 if (real) reinterpret_cast<float*>(p.out)[row] = acc + p.head_b;      // Flatten: index b*S*S + x*S + y
+            }
+            if (p.mode >= 2) {
+                // residual network layer: same accumulator walk with the extra terms
+                float sc = 1.f, sh = 0.f;
+                if (p.bn_scale) { const int y = (int)(row % p.S); sc = p.bn_scale[y]; sh = p.bn_shift[y]; }
+                const bool fp16 = p.dtype != RAG_DTYPE_BF16;
+                const uint16_t* rrow = p.residual ? p.residual + row * p.N : nullptr;
+                uint16_t* lrow = p.linear_out ? p.linear_out + row * p.N : nullptr;
+                uint16_t* orow = reinterpret_cast<uint16_t*>(p.out) + row * p.N;
+                float acc = 0.f;
+                for (int c0 = 0; c0 < p.N; c0 += 32) {
+                    uint32_t v[32];
+                    tc_ld32(taddr + (uint32_t)c0, v);
+                    tc_wait_ld();
+                    uint32_t res[16];
+                    #pragma unroll
+                    for (int j = 0; j < 16; j++) res[j] = 0u;
+                    if (rrow && real) {
+                        const uint4* src = reinterpret_cast<const uint4*>(rrow + c0);
+                        #pragma unroll
+                        for (int j = 0; j < 4; j++) { uint4 t = src[j]; res[4 * j] = t.x; res[4 * j + 1] = t.y; res[4 * j + 2] = t.z; res[4 * j + 3] = t.w; }
+                    }
+                    uint32_t lin[16], act[16];
+                    #pragma unroll
+                    for (int j = 0; j < 16; j++) {
+                        float r0, r1;
+                        if (fp16) { float2 t = __half22float2(*reinterpret_cast<__half2*>(&res[j])); r0 = t.x; r1 = t.y; }
+                        else { float2 t = __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&res[j])); r0 = t.x; r1 = t.y; }
+                        const float l0 = __uint_as_float(v[2 * j]) + s_bias[c0 + 2 * j] + r0;
+                        const float l1 = __uint_as_float(v[2 * j + 1]) + s_bias[c0 + 2 * j + 1] + r1;
+                        const float a0 = fmaxf(fmaf(l0, sc, sh), 0.f), a1 = fmaxf(fmaf(l1, sc, sh), 0.f);
+                        if (fp16) {
+                            __half2 h = __floats2half2_rn(l0, l1); lin[j] = *reinterpret_cast<uint32_t*>(&h);
+                            __half2 k = __floats2half2_rn(a0, a1); act[j] = *reinterpret_cast<uint32_t*>(&k);
+                        } else {
+                            __nv_bfloat162 h = __floats2bfloat162_rn(l0, l1); lin[j] = *reinterpret_cast<uint32_t*>(&h);
+                            __nv_bfloat162 k = __floats2bfloat162_rn(a0, a1); act[j] = *reinterpret_cast<uint32_t*>(&k);
+                        }
+                        acc = fmaf(a0, s_head[c0 + 2 * j], acc);
+                        acc = fmaf(a1, s_head[c0 + 2 * j + 1], acc);
+                    }
+                    if (real) {
+                        if (lrow) {
+                            uint4* dst = reinterpret_cast<uint4*>(lrow + c0);
+                            #pragma unroll
+                            for (int j = 0; j < 4; j++) dst[j] = make_uint4(lin[4 * j], lin[4 * j + 1], lin[4 * j + 2], lin[4 * j + 3]);
+                        }
+                        if (p.mode == 2) {
+                            uint4* dst = reinterpret_cast<uint4*>(orow + c0);
+                            #pragma unroll
+                            for (int j = 0; j < 4; j++) dst[j] = make_uint4(act[4 * j], act[4 * j + 1], act[4 * j + 2], act[4 * j + 3]);
+                        }
+                    }
+                }
+                if (p.mode == 3 && real) reinterpret_cast<float*>(p.out)[row] = acc + p.head_b;
             }
             tc_fence_before();
             __syncwarp();
@@ -490,6 +552,8 @@ struct Layer {
     int width, cin, cout, cin_pad, n_pad, taps;
     uint16_t* d_w = nullptr;      // [taps][n_pad][cin_pad]
     float* d_bias = nullptr;      // [n_pad]
+    float* d_bn_scale = nullptr;  // residual nets: BatchNormalization applied to this layer's INPUT, [S] each
+    float* d_bn_shift = nullptr;
 };
 
 }  // namespace rag
@@ -533,6 +597,7 @@ static int pick_stages(int N) {
 }
 
 struct NetBuffers {
+    uint16_t* lin[2];        // residual nets: unit outputs (the skip path)
     uint16_t* act[2];
     float* logits;
     uint16_t* in_rows;       // only for the NCHW entry
@@ -557,12 +622,20 @@ static NetBuffers carve_net(const rag_net* net, int n, void* ws, bool with_input
     b.act[1] = (uint16_t*)p; p += b.act_bytes;
     b.logits = (float*)p; p += logits_bytes;
     b.in_rows = (uint16_t*)p; p += b.in_bytes;
-    b.total = 2 * b.act_bytes + logits_bytes + b.in_bytes;
+    b.lin[0] = b.lin[1] = nullptr;
+    size_t lin_bytes = 0;
+    if (net->desc.resnet) {
+        b.lin[0] = (uint16_t*)p; p += b.act_bytes;
+        b.lin[1] = (uint16_t*)p; p += b.act_bytes;
+        lin_bytes = 2 * b.act_bytes;
+    }
+    b.total = 2 * b.act_bytes + logits_bytes + b.in_bytes + lin_bytes;
     return b;
 }
 
 static int run_layers(rag_net* net, const uint16_t* d_in, int n, float* d_out, const NetBuffers& b, cudaStream_t s) {
     const int S = net->desc.board, L = (int)net->layers.size();
+    int lin_cur = 0;
     const uint16_t* cur = d_in;
     for (int l = 0; l < L; l++) {
         const Layer& ly = net->layers[l];
@@ -579,6 +652,14 @@ static int run_layers(rag_net* net, const uint16_t* d_in, int n, float* d_out, c
         p.mode = last ? 1 : 0; p.relu = 1;
         p.bias = ly.d_bias; p.head_w = net->d_head_w; p.head_b = net->head_b;
         p.out = last ? (void*)b.logits : (void*)dst;
+        if (net->desc.resnet) {
+            // conv l ends a unit (or is the first convolution): its linear output is the next skip path
+            p.mode = last ? 3 : 2;
+            const bool unit_end = net->desc.unit_end[l] != 0;
+            if (l > 0 && unit_end) p.residual = b.lin[lin_cur];
+            if (unit_end && !last) { p.linear_out = b.lin[l == 0 ? lin_cur : 1 - lin_cur]; if (l > 0) lin_cur = 1 - lin_cur; }
+            if (!last) { p.bn_scale = net->layers[l + 1].d_bn_scale; p.bn_shift = net->layers[l + 1].d_bn_shift; }
+        }
 
         // a CTA pair (cta_group::2) needs an even split of the weight tile into 8-row groups
         const bool pair = g_conv_pair && (ly.n_pad % 32 == 0) && net->sms >= 2;
@@ -649,6 +730,12 @@ int rag_net_create(const rag_net_desc* desc, rag_net** out)
     if (desc->head != RAG_HEAD_POLICY && desc->head != RAG_HEAD_VALUE) return fail(RAG_EINVAL, "head %d", desc->head);
     if (desc->dtype != RAG_DTYPE_BF16 && desc->dtype != RAG_DTYPE_FP16) return fail(RAG_EINVAL, "dtype %d", desc->dtype);
     if (desc->head == RAG_HEAD_VALUE && (desc->dense_units < 1 || desc->dense_units > 4096)) return fail(RAG_EINVAL, "dense_units %d", desc->dense_units);
+    if (desc->resnet) {
+        if (desc->head != RAG_HEAD_POLICY) return fail(RAG_EUNSUPPORTED, "residual networks are policy networks (policy.py:141)");
+        for (int l = 1; l < desc->layers; l++)
+            if (desc->filters[l] != desc->filters[0]) return fail(RAG_EINVAL, "a residual network needs the same filter count in every layer");
+        if (!desc->unit_end[desc->layers - 1]) return fail(RAG_EINVAL, "the last convolution must close a residual unit");
+    }
     rag_net* net = new rag_net();
     net->desc = *desc;
     int cin = desc->in_planes;
@@ -677,7 +764,7 @@ int rag_net_create(const rag_net_desc* desc, rag_net** out)
 int rag_net_destroy(rag_net* net)
 {
     if (!net) return RAG_OK;
-    for (auto& ly : net->layers) { cudaFree(ly.d_w); cudaFree(ly.d_bias); }
+    for (auto& ly : net->layers) { cudaFree(ly.d_w); cudaFree(ly.d_bias); cudaFree(ly.d_bn_scale); cudaFree(ly.d_bn_shift); }
     for (auto& e : net->events) cudaEventDestroy(e);
     cudaFree(net->d_head_w); cudaFree(net->d_pos_bias);
     cudaFree(net->d_dense1_w); cudaFree(net->d_dense1_b); cudaFree(net->d_dense2_w); cudaFree(net->d_dense2_b);
@@ -688,7 +775,8 @@ int rag_net_destroy(rag_net* net)
 int rag_net_num_weight_arrays(const rag_net* net)
 {
     if (!net) return 0;
-    return 2 * (int)net->layers.size() + 2 + (net->desc.head == RAG_HEAD_POLICY ? 1 : 4);
+    const int L = (int)net->layers.size();
+    return 2 * L + (net->desc.resnet ? 4 * (L - 1) : 0) + 2 + (net->desc.head == RAG_HEAD_POLICY ? 1 : 4);
 }
 
 int rag_net_load_weights(rag_net* net, const float* const* h_arrays, int n_arrays)
@@ -701,6 +789,18 @@ int rag_net_load_weights(rag_net* net, const float* const* h_arrays, int n_array
     int ai = 0;
     for (int l = 0; l < L; l++) {
         Layer& ly = net->layers[l];
+        if (net->desc.resnet && l > 0) {
+            // BatchNormalization() in front of this convolution (policy.py:226-228), Keras-1 defaults:
+            // mode 0, axis -1 (= the y coordinate in 'th' ordering), epsilon 1e-3; at inference
+            // x -> gamma * (x - running_mean) / sqrt(running_std + eps) + beta  (running_std holds the variance)
+            const float* gamma = h_arrays[ai++]; const float* beta = h_arrays[ai++];
+            const float* mean = h_arrays[ai++];  const float* var = h_arrays[ai++];
+            const int S = net->desc.board;
+            std::vector<float> sc(S), sh(S);
+            for (int y = 0; y < S; y++) { sc[y] = gamma[y] / sqrtf(var[y] + 1e-3f); sh[y] = beta[y] - mean[y] * sc[y]; }
+            if (int rc = upload(&ly.d_bn_scale, sc)) return rc;
+            if (int rc = upload(&ly.d_bn_shift, sh)) return rc;
+        }
         const float* W = h_arrays[ai++];      // (cout, cin, kh, kw)  Keras 'th' kernel layout
         const float* bsrc = h_arrays[ai++];   // (cout,)
         const int k = ly.width;

@@ -612,7 +612,7 @@ playout_kernel(uint32_t* out, int n_positions, int S, uint64_t seed, int max_ply
 //
 // Same layout as the caller-provided workspace (counters, bit-planes, ladder queue), sized for
 // kStaticMaxPositions positions, but living in the library's own device image: every GPU that loads
-// the library carries these ~2.3 MB until the process exits, and no allocation call is ever needed.
+// the library carries these ~2.4 MB until the process exits, and no allocation call is ever needed.
 constexpr int kStaticMaxPositions = 256;
 constexpr size_t kStaticScratchBytes =                              // = workspace_bytes(kStaticMaxPositions)
     ((size_t)kCounterBytes + (size_t)kStaticMaxPositions * (kPlaneWords * 4 + 2 * kMaxBoard * kMaxBoard * 4) + 511) / 512 * 512

@@ -23,7 +23,7 @@ class _NetDesc(ctypes.Structure):
     _fields_ = [("board", ctypes.c_int), ("in_planes", ctypes.c_int), ("layers", ctypes.c_int),
                 ("filters", ctypes.c_int * MAX_LAYERS), ("widths", ctypes.c_int * MAX_LAYERS),
                 ("head", ctypes.c_int), ("dense_units", ctypes.c_int), ("dtype", ctypes.c_int),
-                ("kernel_flip", ctypes.c_int)]
+                ("kernel_flip", ctypes.c_int), ("resnet", ctypes.c_int), ("unit_end", ctypes.c_int * MAX_LAYERS)]
 
 
 class Bias(object):
@@ -41,9 +41,15 @@ class Network(object):
     """
 
     def __init__(self, board, input_dim, specs, head="policy", dense_units=256, dtype="bf16",
-                 kernel_flip=True, seed=None):
+                 kernel_flip=True, seed=None, unit_end=None):
+        """unit_end (residual networks only, policy.py:141-271): one flag per convolution, 1 where it
+        closes a residual unit (the first convolution counts as closing one: its output is the
+        first skip path).  None = a plain Sequential stack."""
         self.board, self.input_dim = int(board), int(input_dim)
         self.specs = [(int(f), int(w)) for f, w in specs]
+        self.unit_end = None if unit_end is None else [int(bool(u)) for u in unit_end]
+        if self.unit_end is not None and (len(self.unit_end) != len(self.specs) or not self.unit_end[0] or not self.unit_end[-1]):
+            raise ValueError("unit_end needs one flag per convolution, set on the first and the last")
         self.head, self.dense_units = head, int(dense_units)
         self.dtype, self.kernel_flip = dtype, bool(kernel_flip)
         self.input_shape = (None, self.input_dim, self.board, self.board)      # read by trainers
@@ -58,7 +64,9 @@ class Network(object):
     # -- weights ---------------------------------------------------------------------------
     def _shapes(self):
         shapes, cin = [], self.input_dim
-        for nb, k in self.specs:
+        for i, (nb, k) in enumerate(self.specs):
+            if self.unit_end is not None and i > 0:
+                shapes += [(self.board,)] * 4       # BatchNormalization: gamma, beta, running_mean, running_std (axis -1)
             shapes += [(nb, cin, k, k), (nb,)]
             cin = nb
         shapes += [(1, cin, 1, 1), (1,)]
@@ -72,8 +80,15 @@ class Network(object):
     def _init_uniform(self, seed):
         """init='uniform' (Keras 1.2.0: U(-0.05, 0.05)); biases and Bias start at zero."""
         rng = np.random.RandomState(seed)
-        return [rng.uniform(-0.05, 0.05, size=s).astype(np.float32) if len(s) > 1 else np.zeros(s, np.float32)
-                for s in self._shapes()]
+        out = [rng.uniform(-0.05, 0.05, size=s).astype(np.float32) if len(s) > 1 else np.zeros(s, np.float32)
+               for s in self._shapes()]
+        if self.unit_end is not None:               # BatchNormalization starts as gamma = 1, beta = 0, mean 0, variance 1
+            i = 2
+            for _ in self.specs[1:]:
+                out[i] = np.ones(self.board, np.float32)
+                out[i + 3] = np.ones(self.board, np.float32)
+                i += 6
+        return out
 
     def get_weights(self):
         return [w.copy() for w in self._weights]
@@ -102,6 +117,10 @@ class Network(object):
 
     # -- (de)serialisation in Keras-1 Sequential JSON -------------------------------------------
     def to_json(self):
+        if self.unit_end is not None:
+            return json.dumps({"class_name": "Model", "keras_version": "1.2.0", "rocalphago_b200": {
+                "arch": "resnet", "board": self.board, "input_dim": self.input_dim, "specs": self.specs,
+                "unit_end": self.unit_end, "dtype": self.dtype, "kernel_flip": self.kernel_flip}})
         layers = []
         for i, (nb, k) in enumerate(self.specs):
             cfg = {"name": "convolution2d_%d" % (i + 1), "nb_filter": nb, "nb_row": k, "nb_col": k,
@@ -131,6 +150,11 @@ class Network(object):
         """Reads the Sequential JSON Keras 1.x writes for these architectures
         (e.g. the reference's tests/test_data/minimodel.json)."""
         km = json.loads(text)
+        ext = km.get("rocalphago_b200", {})
+        if ext.get("arch") == "resnet":
+            return Network(ext["board"], ext["input_dim"], [tuple(x) for x in ext["specs"]], head="policy",
+                           dtype=ext.get("dtype", "bf16"), kernel_flip=ext.get("kernel_flip", True),
+                           unit_end=ext["unit_end"])
         if km.get("class_name") != "Sequential":
             raise ValueError("only Sequential models are supported on this path (got %s)" % km.get("class_name"))
         convs, head, dense, board, input_dim = [], None, [], None, None
@@ -182,6 +206,9 @@ class Network(object):
             d.dense_units = self.dense_units
             d.dtype = DTYPE_BF16 if self.dtype == "bf16" else DTYPE_FP16
             d.kernel_flip = int(self.kernel_flip)
+            d.resnet = int(self.unit_end is not None)
+            for i, u in enumerate(self.unit_end or []):
+                d.unit_end[i] = u
             h = ctypes.c_void_p()
             with torch.cuda.device(device):
                 _cabi.check(L.rag_net_create(ctypes.byref(d), ctypes.byref(h)))

@@ -84,6 +84,35 @@ class CNNPolicy(NeuralNetBase):
                        seed=params.get("seed"))
 
 
+@neuralnet
+class ResnetPolicy(CNNPolicy):
+    """Residual network architecture as per He at al. 2015 (policy.py:141-271)"""
+
+    @staticmethod
+    def create_network(**kwargs):
+        """Same keyword arguments as the reference: input_dim, board (19), filters_per_layer (128),
+        layers (20), filter_width_K (3; filter_width_1 = 5), n_skip_K (1): the first convolution is
+        linear; then units of n_skip_K x [BatchNormalization -> ReLU -> convolution] whose output is
+        added to the unit's input; a last ReLU, the 1x1 convolution, Flatten, Bias, softmax.
+        Faithful to two quirks of the reference: filter_width_K inside the units is looked up with
+        the unit's own layer index, so the first unit's first convolution is again filter_width_1
+        wide (policy.py:229-231 with K = 1); BatchNormalization() is built with Keras-1 defaults,
+        i.e. it normalises over the LAST axis (the y coordinate), not over channels."""
+        params = {"board": 19, "filters_per_layer": 128, "layers": 20, "filter_width_1": 5}
+        params.update(kwargs)
+        specs = [(params["filters_per_layer"], params["filter_width_1"])]
+        unit_end = [1]
+        layer = 1
+        while layer < params["layers"]:
+            n_skip = params.get("n_skip_%d" % layer, 1)
+            for i in range(n_skip):
+                specs.append((params["filters_per_layer"], params.get("filter_width_%d" % (layer + i), 3)))
+                unit_end.append(1 if i == n_skip - 1 else 0)
+            layer += n_skip
+        return Network(params["board"], params["input_dim"], specs, head="policy", dtype=params.get("dtype", "bf16"),
+                       kernel_flip=params.get("kernel_flip", True), seed=params.get("seed"), unit_end=unit_end)
+
+
 def _smoke(batch, board, age, ko, player):
     """Used by __graft_entry__.smoke(): a 3-layer policy on the smoke batch vs the CPU oracle."""
     from oracle import cnn_oracle, go_oracle

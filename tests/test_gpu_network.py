@@ -318,3 +318,50 @@ def test_pipeline_with_policy_and_value_networks():
         assert np.array_equal(probs.cpu().numpy(), want_p)
         assert np.array_equal(values.cpu().numpy(), want_v)
     pipe.drain()
+
+
+@pytest.mark.parametrize("arch", [dict(layers=5, filters_per_layer=64), dict(layers=7, filters_per_layer=64, n_skip_1=2, n_skip_3=3),
+                                  dict(layers=20, filters_per_layer=128)])
+def test_resnet_policy(arch):
+    """ResnetPolicy (policy.py:141-271): BatchNormalization -> ReLU -> convolution units with skip
+    connections, against the torch restatement; BN statistics are randomised so that the affine part matters."""
+    from rocalphago_b200.models import ResnetPolicy
+    feats = go_oracle.DEFAULT_FEATURES
+    n = 24
+    b, a, ko, pl = _positions(n, seed=61)
+    planes = go_oracle.features(b, a, ko, pl, feats)
+    net = ResnetPolicy(feats, dtype="fp16", seed=5, **arch)
+    m = net.model
+    assert len(m.specs) == arch["layers"] and m.specs[0][1] == 5 and m.specs[1][1] == 5      # the filter_width_1 quirk
+    w = m.get_weights()
+    rng = np.random.RandomState(3)
+    i = 2
+    for _ in m.specs[1:]:
+        w[i] = rng.uniform(0.5, 1.5, 19).astype(np.float32)        # gamma
+        w[i + 1] = rng.uniform(-0.02, 0.02, 19).astype(np.float32)  # beta
+        w[i + 2] = rng.uniform(-0.01, 0.01, 19).astype(np.float32)  # running mean
+        w[i + 3] = rng.uniform(0.5, 2.0, 19).astype(np.float32)     # running variance
+        i += 6
+    w[-1] = rng.normal(0, 0.5, 361).astype(np.float32)
+    m.set_weights(w)
+    want = cnn_oracle.forward_resnet(w, planes, m.specs, m.unit_end, threads=os.cpu_count())
+    got = net.forward(planes)
+    st = _policy_stats(got, want)
+    assert got.shape == (n, 361) and np.allclose(got.sum(1), 1.0, atol=1e-5)
+    assert st["max_abs"] <= PROB_TOL and st["logit_rel"] <= 0.03, st
+    batch = BatchedGameState.from_arrays(b, a, ko, pl)
+    fused = m.eval_batch_device(batch, net.preprocessor.plane_src).cpu().numpy()
+    assert np.array_equal(fused, got)
+    res = net.batch_eval_state(batch)
+    assert len(res) == n and abs(sum(p for _, p in res[0]) - 1.0) < 1e-5
+
+
+def test_resnet_save_load(tmp_path):
+    from rocalphago_b200.models import ResnetPolicy
+    net = ResnetPolicy(["board", "ones"], layers=4, filters_per_layer=64, n_skip_1=2, seed=1)
+    mj, wf = str(tmp_path / "r.json"), str(tmp_path / "r.npz")
+    net.save_model(mj, wf)
+    copy = NeuralNetBase.load_model(mj)
+    assert isinstance(copy, ResnetPolicy) and copy.model.unit_end == net.model.unit_end and copy.model.specs == net.model.specs
+    for w1, w2 in zip(net.model.get_weights(), copy.model.get_weights()):
+        assert np.array_equal(w1, w2)
