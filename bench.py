@@ -187,6 +187,10 @@ def run_gpu(args):
     trace("process group up")
     L = _cabi.lib()
     net = CNNPolicy(DEFAULT_FEATURES, layers=12, filters_per_layer=192, dtype=args.dtype, seed=1234)
+    if args.workload == "value":
+        # BASELINE config 3: value net, 49 planes (48 + colour), 12 conv + 1x1 + Dense 256 + tanh
+        from rocalphago_b200.models import CNNValue
+        net = CNNValue(DEFAULT_FEATURES + ["color"], layers=12, filters_per_layer=192, dtype=args.dtype, seed=4321)
     vnet = None
     if args.workload == "policy+value":
         from rocalphago_b200.models import CNNValue
@@ -245,6 +249,7 @@ def run_gpu(args):
         return
     pipe = EvalPipeline(net, n, device=dev, value_net=vnet)
     first = (lambda r: r[0]) if vnet is not None else (lambda r: r)
+    one = (lambda t: float(t.reshape(-1)[0]))
     for i in range(W):
         pipe.submit(batches[i % pool].packed)
     pipe.drain()
@@ -286,8 +291,8 @@ def run_gpu(args):
     for k in range(K):
         t = pipe.submit(host_in[k % pool], to_host=True)
         if k > 0:
-            checksum += float(first(pipe.result(t - 1))[0, 0])
-    checksum += float(first(pipe.result(pipe.count - 1))[0, 0])
+            checksum += one(first(pipe.result(t - 1)))
+    checksum += one(first(pipe.result(pipe.count - 1)))
     f1 = pipe.mark()
     pipe.drain()
     barrier()
@@ -308,7 +313,7 @@ def run_gpu(args):
         full = D.gather_results(local, n * world)
         g1.record()
         torch.cuda.synchronize()
-        assert tuple(full.shape) == (n * world, 361)
+        assert full.shape[0] == n * world
         gather_ms = g0.elapsed_time(g1)
 
     t = torch.tensor([dev_ms, e2e_ms, e2e_wall_ms], dtype=torch.float64, device=dev)
@@ -324,7 +329,8 @@ def run_gpu(args):
         k3 = float(np.mean(layer_ms[1:]))                      # the eleven 3x3 192->192 launches
         achieved = FLOP_3X3 * n / (k3 / 1e3) / 1e12
         line = {
-            "metric": METRIC if vnet is None else "positions/sec: 48/49-plane features + policy AND value CNN fwd, 19x19",
+            "metric": ("positions/sec: 49-plane features + value CNN fwd, 19x19" if args.workload == "value" else METRIC)
+                      if vnet is None else "positions/sec: 48/49-plane features + policy AND value CNN fwd, 19x19",
             "value": value, "unit": "positions/s", "n_gpus": world, "steps": K,
             "warmup": W, "ms_per_step": dev_ms / K, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
@@ -445,7 +451,7 @@ def main():
     ap.add_argument("--cpu-sample", type=int, default=512)
     ap.add_argument("--ref-sample", type=int, default=256)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default="policy", choices=["policy", "features", "policy+value"],
+    ap.add_argument("--workload", default="policy", choices=["policy", "features", "policy+value", "value"],
                     help="policy: the flagship (features + 13x192 policy forward); features: BASELINE config 4; "
                          "policy+value: BASELINE config 5 (adds the 49-plane 13x192 value forward to every step)")
     ap.add_argument("--serial", action="store_true", help="also time the single-stream rag_eval_batch step")
@@ -458,6 +464,10 @@ def main():
         if args.batch == 4096:
             args.batch = 32768
         run_features(args)
+    elif args.workload == "value":
+        if args.batch == 4096:
+            args.batch = 1024
+        run_gpu(args)
     else:
         run_gpu(args)
 
