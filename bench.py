@@ -352,9 +352,9 @@ def run_gpu(args):
                          "frac": achieved / peaks["tf_sustained"], "peak_source": peaks["src"] + " (sustained)",
                          "ms_per_launch": k3,
                          # dram__bytes_read.sum + dram__bytes_write.sum per launch from the ncu --set full capture
-                         # of this kernel at batch 4096 (profiles/r1_conv_ncu_summary.md); scales with the batch
-                         "traffic": {"bytes": int(1.2113e9 * n / 4096), "algorithmic_bytes": int(n * 400 * 192 * 2 * 2),
-                                     "source": "profiles/r1_conv_ncu_summary.md"},
+                         # of this kernel at batch 4096 (profiles/r1_final_ncu_summary.md); scales with the batch
+                         "traffic": {"bytes": int(1.0892e9 * n / 4096), "algorithmic_bytes": int(n * 361 * 192 * 2 * 2),
+                                     "source": "profiles/r1_final_ncu_summary.md"},
                          "note": "CUDA events recorded by the library on the launching stream, sampled %d time(s) inside "
                                  "the timed region while the next batch's feature kernels share the SMs" % samples},
             "stage_ms": {"conv_layer1": float(layer_ms[0]), "conv_3x3_mean": k3, "conv_all": float(layer_ms.sum()),
