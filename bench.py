@@ -247,7 +247,7 @@ def run_gpu(args):
     if args.no_pipeline:
         print(json.dumps({"serial_ms_per_step": serial_ms, "conv_pair": args.conv_pair}))
         return
-    pipe = EvalPipeline(net, n, device=dev, value_net=vnet)
+    pipe = EvalPipeline(net, n, device=dev, value_net=vnet, slots=args.slots)
     first = (lambda r: r[0]) if vnet is not None else (lambda r: r)
     one = (lambda t: float(t.reshape(-1)[0]))
     for i in range(W):
@@ -305,7 +305,7 @@ def run_gpu(args):
     gather_ms = None
     if world > 1:
         from rocalphago_b200 import distributed as D
-        local = pipe.slots[(pipe.count - 1) % 2].out
+        local = pipe.slots[(pipe.count - 1) % pipe.nslots].out
         D.gather_results(local, n * world)
         barrier()
         g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -337,8 +337,9 @@ def run_gpu(args):
             "config": {"workload": "48 planes (incl. ladders) + 13x192 policy forward, 19x19, batch %d/GPU, "
                                    "device-generated random-playout positions, random-init weights" % n,
                        "batch_per_gpu": n,
-                       "schedule": "two-stage pipeline: feature kernels of batch k+1 on one stream overlap the "
-                                   "convolutions of batch k on another (rocalphago_b200/pipeline.py)",
+                       "schedule": "two-stage pipeline, %d batches in flight: the feature kernels of the next batches run "
+                                   "on their own streams underneath the convolutions of the current one "
+                                   "(rocalphago_b200/pipeline.py)" % pipe.nslots,
                        "l2": "no flush needed: each step streams 1.6 GB of activations (13x the 126 MB L2) and the "
                              "input batches rotate; the --serial pass writes 256 MiB between steps",
                        "parallelism": "dp%d (independent batches, no collective on the data path)" % world},
@@ -457,6 +458,7 @@ def main():
     ap.add_argument("--serial", action="store_true", help="also time the single-stream rag_eval_batch step")
     ap.add_argument("--conv-pair", type=int, default=0, help="0: one CTA per tile; 1: CTA pairs (cta_group::2)")
     ap.add_argument("--no-pipeline", action="store_true", help="debug: skip the pipelined passes")
+    ap.add_argument("--slots", type=int, default=None, help="batches in flight in the pipeline (default: 2, or 4 below 2048 positions)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

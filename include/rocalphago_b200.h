@@ -99,6 +99,10 @@ int rag_features_analyze(const uint32_t* d_states, int n, int size, int with_lad
  * replies over to idle warps (default 96; 0 = from the first move; < 0 = never).  Results do not
  * depend on it.  Returns the previous value. */
 int rag_set_ladder_handover(int moves);
+/* Tuning knob (process-wide): how many CTAs of the ladder kernel keep one warp waiting for handed-over
+ * replies once the queue is empty (< 0 = all of them).  Results do not depend on it.  Returns the
+ * previous value. */
+int rag_set_ladder_helpers(int ctas);
 
 /* Step 1b: the ladder reader over the candidates queued by rag_features_analyze(with_ladders = 2). */
 int rag_features_ladders(const uint32_t* d_states, int n, int size, void* d_workspace,

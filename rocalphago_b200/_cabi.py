@@ -46,6 +46,7 @@ def lib():
         "rag_features_workspace_bytes": (sz, [i32]),
         "rag_features_analyze": (i32, [vp, i32, i32, i32, vp, sz, vp]),
         "rag_set_ladder_handover": (i32, [i32]),
+        "rag_set_ladder_helpers": (i32, [i32]),
         "rag_features_ladders": (i32, [vp, i32, i32, vp, sz, vp]),
         "rag_features_emit": (i32, [vp, i32, i32, vp, i32, i32, i32, i32, vp, vp]),
         "rag_features": (i32, [vp, i32, i32, vp, i32, i32, i32, i32, vp, vp, sz, vp]),

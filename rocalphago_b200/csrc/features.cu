@@ -23,6 +23,7 @@
 #include <cuda_fp16.h>
 #include <string.h>
 #include <mutex>
+#include <stdlib.h>
 
 namespace rag {
 
@@ -324,7 +325,7 @@ __device__ __forceinline__ int ladder_search_steal(const Workspace& ws, const Ge
 }
 
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
-ladder_kernel(const uint32_t* __restrict__ states, int S, int steal_after, Workspace ws)
+ladder_kernel(const uint32_t* __restrict__ states, int S, int steal_after, int helper_ctas, Workspace ws)
 {
     const Geo g = make_geo(S);
     LadderStack st;
@@ -367,10 +368,12 @@ ladder_kernel(const uint32_t* __restrict__ states, int S, int steal_after, Works
         }
     }
 
-    // ---- out of items: serve handed-over replies until nobody is busy.  One warp per CTA stays for
-    // that (there are never more than a few dozen tasks in flight); idle warps sleep between looks,
-    // longer each time, so that they take neither issue slots nor L2 bandwidth from the searches.
-    if (steal_after >= (1 << 29) || (threadIdx.x >> 5) != 0) return;
+    // ---- out of items: serve handed-over replies until nobody is busy.  One warp of each of the
+    // first `helper_ctas` CTAs stays for that (there are never more than a few dozen tasks in
+    // flight); every other CTA exits and gives its registers back, so that the kernels of the next
+    // batch can start underneath a long search.  Idle warps sleep between looks, longer each time,
+    // so that they take neither issue slots nor L2 bandwidth from the searches.
+    if (steal_after >= (1 << 29) || (threadIdx.x >> 5) != 0 || (int)blockIdx.x >= helper_ctas) return;
     unsigned scan = blockIdx.x * 37u;                                              // every warp starts its scans elsewhere
     unsigned nap = 500;
     for (;;) {
@@ -619,6 +622,31 @@ constexpr size_t kStaticScratchBytes =                              // = workspa
     + (size_t)(kStaticMaxPositions / 2) * (sizeof(StealTask) + 4);
 static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
 
+// The kernels that run next to the convolutions in a pipeline (analysis, ladder reader, conv-layout
+// emit) ask for the same shared-memory / L1 split as the convolution kernel uses (all of it shared
+// memory).  An SM has one split at a time and changes it only when it is empty: with different
+// preferences, a convolution CTA could not start on an SM where a ladder warp was still searching,
+// and -- the tiles of a layer being dealt out statically -- every layer then waited for a second
+// round of CTAs.  (Measured at batch 256: forward 0.70 ms alone, 1.07 ms beside the ladder kernels.)
+static int match_conv_carveout() {
+    static std::mutex mu;
+    static bool done[64] = {false};
+    int dev = -1;
+    RAG_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return fail(RAG_EUNSUPPORTED, "device ordinal %d not supported", dev);
+    std::lock_guard<std::mutex> lock(mu);
+    if (done[dev]) return RAG_OK;
+    const char* e = getenv("RAG_CARVEOUT");
+    const int pct = e ? atoi(e) : (int)cudaSharedmemCarveoutMaxShared;
+    if (pct >= 0) {
+        RAG_CUDA_CHECK(cudaFuncSetAttribute(analyze_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+        RAG_CUDA_CHECK(cudaFuncSetAttribute(ladder_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+        RAG_CUDA_CHECK(cudaFuncSetAttribute(emit_conv_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+    }
+    done[dev] = true;
+    return RAG_OK;
+}
+
 // In host code `g_static_scratch` is only a handle for the runtime, not an address a kernel could
 // use; the device address has to be asked for, per device, with that device current.
 static int static_scratch_address(void** out) {
@@ -713,6 +741,7 @@ select_moves_kernel(const float* __restrict__ probs, const uint32_t* __restrict_
 }
 
 static int g_steal_after = kStealAfterDefault;      // rag_set_ladder_handover
+static int g_helper_ctas = 1 << 30;                 // rag_set_ladder_helpers
 
 static int check_size(int size) {
     if (size < 2 || size > kMaxBoard) return fail(RAG_EUNSUPPORTED, "board size %d not in [2, 19]", size);
@@ -805,6 +834,7 @@ int rag_features_analyze(const uint32_t* d_states, int n, int size, int with_lad
         return fail(RAG_ENOMEM, "workspace has %zu bytes, %zu needed for n = %d", workspace_bytes_given, workspace_bytes(n), n);
     if (n == 0) return RAG_OK;
     cudaStream_t s = (cudaStream_t)stream;
+    if (int rc = match_conv_carveout()) return rc;
     Workspace ws = carve(d_workspace, n);
     RAG_CUDA_CHECK(cudaMemsetAsync(ws.counters, 0, kCounterBytes, s));
     RAG_CUDA_CHECK(cudaMemsetAsync(ws.tasks, 0, (size_t)ws.task_cap * (sizeof(StealTask) + 4), s));     // all tasks free, ring empty
@@ -819,7 +849,7 @@ int rag_features_analyze(const uint32_t* d_states, int n, int size, int with_lad
         // and a convolution CTA of another stream (conv.cu) must still fit beside them.
         long long want = ((long long)n * 16 + kWarpsPerBlock - 1) / kWarpsPerBlock;
         int blocks = (int)(want < (long long)sms * 4 ? (want < 1 ? 1 : want) : (long long)sms * 4);
-        ladder_kernel<<<blocks, kWarpsPerBlock * 32, 0, s>>>(d_states, size, g_steal_after, ws);
+        ladder_kernel<<<blocks, kWarpsPerBlock * 32, 0, s>>>(d_states, size, g_steal_after, g_helper_ctas, ws);
         RAG_CUDA_CHECK(cudaGetLastError());
     }
     return RAG_OK;
@@ -834,13 +864,15 @@ int rag_features_ladders(const uint32_t* d_states, int n, int size, void* d_work
     if (workspace_bytes_given < workspace_bytes(n))
         return fail(RAG_ENOMEM, "workspace has %zu bytes, %zu needed for n = %d", workspace_bytes_given, workspace_bytes(n), n);
     if (n == 0) return RAG_OK;
+    if (int rc = match_conv_carveout()) return rc;
     Workspace ws = carve(d_workspace, n);
     int dev = 0, sms = 148;
     RAG_CUDA_CHECK(cudaGetDevice(&dev));
     RAG_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    long long want = ((long long)n * 16 + kWarpsPerBlock - 1) / kWarpsPerBlock;
+    static int wpp = getenv("RAG_LADDER_WPP") ? atoi(getenv("RAG_LADDER_WPP")) : 16;
+    long long want = ((long long)n * wpp + kWarpsPerBlock - 1) / kWarpsPerBlock;
     int blocks = (int)(want < (long long)sms * 4 ? (want < 1 ? 1 : want) : (long long)sms * 4);
-    ladder_kernel<<<blocks, kWarpsPerBlock * 32, 0, (cudaStream_t)stream>>>(d_states, size, g_steal_after, ws);
+    ladder_kernel<<<blocks, kWarpsPerBlock * 32, 0, (cudaStream_t)stream>>>(d_states, size, g_steal_after, g_helper_ctas, ws);
     RAG_CUDA_CHECK(cudaGetLastError());
     return RAG_OK;
 }
@@ -894,6 +926,7 @@ int rag_features(const uint32_t* d_states, int n, int size, const int32_t* h_pla
     return rag_features_emit(d_workspace, n, size, h_plane_src, F, layout, conv_dtype, conv_channels, d_out, stream);
 }
 
+int rag_set_ladder_helpers(int ctas) { int old = g_helper_ctas; g_helper_ctas = ctas < 0 ? 1 << 30 : ctas; return old; }
 int rag_set_ladder_handover(int moves) { int old = g_steal_after; g_steal_after = moves < 0 ? 1 << 30 : moves; return old; }
 
 int rag_features_static_max_positions(void) { return kStaticMaxPositions; }

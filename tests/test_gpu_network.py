@@ -279,7 +279,7 @@ def test_two_stream_pipeline_gives_the_same_results():
     for i in range(5):
         assert np.array_equal(got[i], want[i]), i
     with pytest.raises(ValueError):
-        pipe.result(0)                                          # long gone
+        pipe.result(0)                                          # long gone (5 batches through 4 slots)
     with pytest.raises(ValueError):
         pipe.submit(batches[0].packed[:10])
 
@@ -365,3 +365,19 @@ def test_resnet_save_load(tmp_path):
     assert isinstance(copy, ResnetPolicy) and copy.model.unit_end == net.model.unit_end and copy.model.specs == net.model.specs
     for w1, w2 in zip(net.model.get_weights(), copy.model.get_weights()):
         assert np.array_equal(w1, w2)
+
+
+def test_pipeline_with_cuda_graphs_gives_the_same_results():
+    """graphs=True replays every stage of a slot as a CUDA graph from the slot's second use on."""
+    from rocalphago_b200.pipeline import EvalPipeline
+    n = 80
+    net = CNNPolicy(go_oracle.DEFAULT_FEATURES, layers=3, filters_per_layer=64, dtype="fp16", seed=61)
+    batches = [BatchedGameState.random_playouts(n, seed=700 + i, max_ply=350, stride=5) for i in range(7)]
+    want = [net.model.eval_batch_device(b, net.preprocessor.plane_src).cpu().numpy() for b in batches]
+    pipe = EvalPipeline(net, n, graphs=True)
+    for i, b in enumerate(batches):
+        src = b.packed if i % 3 else b.packed.cpu().pin_memory()
+        t = pipe.submit(src, to_host=(i % 2 == 0))
+        assert np.array_equal(pipe.result(t).cpu().numpy(), want[i]), i
+    assert all(len(s.graphs) == 3 for s in pipe.slots[:3])      # 7 batches over 4 slots: slots 0-2 were used twice
+    pipe.drain()

@@ -1,42 +1,31 @@
-"""Timeline of the two-stage pipeline: when does each stage of each batch start/finish on the GPU?"""
+"""Timeline of the pipeline: when does each stage of each batch start/finish on the GPU?
+usage: pipeline_timeline.py [batch] [slots] [helper CTAs]"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
-from rocalphago_b200 import BatchedGameState
+from rocalphago_b200 import BatchedGameState, _cabi
 from rocalphago_b200.models import CNNPolicy
 from rocalphago_b200.pipeline import EvalPipeline
 from rocalphago_b200.preprocessing import DEFAULT_FEATURES
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
+if len(sys.argv) > 3:
+    _cabi.lib().rag_set_ladder_helpers(int(sys.argv[3]))
 net = CNNPolicy(DEFAULT_FEATURES, layers=12, filters_per_layer=192, dtype="fp16", seed=1)
-batches = [BatchedGameState.random_playouts(n, seed=20261106 + 7919 * i) for i in range(4)]
-pipe = EvalPipeline(net, n)
-for i in range(4):
+batches = [BatchedGameState.random_playouts(n, seed=5 + i) for i in range(4)]
+pipe = EvalPipeline(net, n, slots=int(sys.argv[2]) if len(sys.argv) > 2 else None)
+for i in range(8):
     pipe.submit(batches[i % 4].packed)
 pipe.drain()
-# instrument: wrap the events with timing-enabled twins
-K = 8
-marks = []
-E = lambda: torch.cuda.Event(enable_timing=True)
-t0 = E(); t0.record(); torch.cuda.synchronize()
-orig_submit = pipe.submit
-for k in range(K):
-    slot = pipe.slots[pipe.count % 2]
-    a0, a1, f1, n0, n1 = E(), E(), E(), E(), E()
-    # start markers: recorded on the stage's stream after its waits would be ideal; approximate by recording
-    # "done" events right after the stage (the pipeline's own events) and "start" right before enqueue
-    with torch.cuda.stream(pipe.s_ana):
-        if slot.used:
-            pipe.s_ana.wait_event(slot.net_done)
-        a0.record(pipe.s_ana)
-    t = pipe.submit(batches[k % 4].packed)
-    a1.record(pipe.s_ana); f1.record(pipe.s_feat); n1.record(pipe.s_net)
-    marks.append((a0, a1, f1, n1))
+t0 = torch.cuda.Event(enable_timing=True); t0.record(); torch.cuda.synchronize()
+pipe.trace = []
+for k in range(16):
+    pipe.submit(batches[k % 4].packed)
 pipe.drain(); torch.cuda.synchronize()
-print("batch | analysis start..end | ladder+emit end | net end   (ms since t0)")
-prev_n = None
-for k, (a0, a1, f1, n1) in enumerate(marks):
-    print("%5d | %7.2f .. %7.2f | %7.2f | %7.2f   (step %.2f)" % (
-        k, t0.elapsed_time(a0), t0.elapsed_time(a1), t0.elapsed_time(f1), t0.elapsed_time(n1),
-        (t0.elapsed_time(n1) - prev_n) if prev_n else 0))
-    prev_n = t0.elapsed_time(n1)
+print("batch | features start | analysis end | ladders+emit end | forward start .. end   (ms since t0)")
+prev = None
+for k, tr in enumerate(pipe.trace):
+    t = [t0.elapsed_time(e) for e in tr]
+    print("%5d | %7.2f | %7.2f | %7.2f | %7.2f .. %7.2f  (forward %.2f, step %.2f)" % (
+        k, t[0], t[1], t[2], t[3], t[4], t[4] - t[3], (t[4] - prev) if prev else 0))
+    prev = t[4]
