@@ -100,7 +100,7 @@ int rag_features_analyze(const uint32_t* d_states, int n, int size, int with_lad
  * depend on it.  Returns the previous value. */
 int rag_set_ladder_handover(int moves);
 /* Tuning knob (process-wide): how many CTAs of the ladder kernel keep one warp waiting for handed-over
- * replies once the queue is empty (< 0 = all of them).  Results do not depend on it.  Returns the
+ * replies once the queue is empty (default 32; < 0 = all of them).  Results do not depend on it.  Returns the
  * previous value. */
 int rag_set_ladder_helpers(int ctas);
 

@@ -23,7 +23,6 @@
 #include <cuda_fp16.h>
 #include <string.h>
 #include <mutex>
-#include <stdlib.h>
 
 namespace rag {
 
@@ -627,7 +626,8 @@ static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBy
 // memory).  An SM has one split at a time and changes it only when it is empty: with different
 // preferences, a convolution CTA could not start on an SM where a ladder warp was still searching,
 // and -- the tiles of a layer being dealt out statically -- every layer then waited for a second
-// round of CTAs.  (Measured at batch 256: forward 0.70 ms alone, 1.07 ms beside the ladder kernels.)
+// round of CTAs.  (Measured at batch 256: forward 0.70 ms alone, 1.07 ms beside the ladder kernels, 0.73 ms with
+// matching splits.)
 static int match_conv_carveout() {
     static std::mutex mu;
     static bool done[64] = {false};
@@ -636,13 +636,10 @@ static int match_conv_carveout() {
     if (dev < 0 || dev >= 64) return fail(RAG_EUNSUPPORTED, "device ordinal %d not supported", dev);
     std::lock_guard<std::mutex> lock(mu);
     if (done[dev]) return RAG_OK;
-    const char* e = getenv("RAG_CARVEOUT");
-    const int pct = e ? atoi(e) : (int)cudaSharedmemCarveoutMaxShared;
-    if (pct >= 0) {
-        RAG_CUDA_CHECK(cudaFuncSetAttribute(analyze_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
-        RAG_CUDA_CHECK(cudaFuncSetAttribute(ladder_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
-        RAG_CUDA_CHECK(cudaFuncSetAttribute(emit_conv_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
-    }
+    const int pct = (int)cudaSharedmemCarveoutMaxShared;
+    RAG_CUDA_CHECK(cudaFuncSetAttribute(analyze_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+    RAG_CUDA_CHECK(cudaFuncSetAttribute(ladder_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+    RAG_CUDA_CHECK(cudaFuncSetAttribute(emit_conv_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
     done[dev] = true;
     return RAG_OK;
 }
@@ -741,7 +738,7 @@ select_moves_kernel(const float* __restrict__ probs, const uint32_t* __restrict_
 }
 
 static int g_steal_after = kStealAfterDefault;      // rag_set_ladder_handover
-static int g_helper_ctas = 1 << 30;                 // rag_set_ladder_helpers
+static int g_helper_ctas = 32;                      // rag_set_ladder_helpers
 
 static int check_size(int size) {
     if (size < 2 || size > kMaxBoard) return fail(RAG_EUNSUPPORTED, "board size %d not in [2, 19]", size);
@@ -869,8 +866,7 @@ int rag_features_ladders(const uint32_t* d_states, int n, int size, void* d_work
     int dev = 0, sms = 148;
     RAG_CUDA_CHECK(cudaGetDevice(&dev));
     RAG_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    static int wpp = getenv("RAG_LADDER_WPP") ? atoi(getenv("RAG_LADDER_WPP")) : 16;
-    long long want = ((long long)n * wpp + kWarpsPerBlock - 1) / kWarpsPerBlock;
+    long long want = ((long long)n * 16 + kWarpsPerBlock - 1) / kWarpsPerBlock;
     int blocks = (int)(want < (long long)sms * 4 ? (want < 1 ? 1 : want) : (long long)sms * 4);
     ladder_kernel<<<blocks, kWarpsPerBlock * 32, 0, (cudaStream_t)stream>>>(d_states, size, g_steal_after, g_helper_ctas, ws);
     RAG_CUDA_CHECK(cudaGetLastError());

@@ -158,16 +158,19 @@ def test_device_playouts_replay_on_oracle():
     assert stones.max() > 200 and stones.min() < 10          # all game phases are covered
 
 
-@pytest.mark.parametrize("handover", [0, 3, 96, -1])
-def test_ladder_planes_do_not_depend_on_reply_handover(handover):
+@pytest.mark.parametrize("handover,helpers", [(0, 32), (3, 32), (96, 32), (-1, 32), (0, 0), (0, 1), (3, -1)])
+def test_ladder_planes_do_not_depend_on_reply_handover(handover, helpers):
     """Long ladder searches hand replies over to idle warps after `handover` tried moves
-    (0: from the start, -1: never).  The planes must be the reference's either way."""
+    (0: from the start, -1: never); `helpers` CTAs keep a warp waiting for such replies (0: nobody
+    helps and every search takes its offers back, -1: every CTA).  The planes must be the
+    reference's either way."""
     from rocalphago_b200 import _cabi
     L = _cabi.lib()
     g = gu.load_features("features_playouts_19.npz")
     b, a, ko, pl = go_oracle.random_playouts(4000, size=19, seed=301, max_ply=400, stride=5)
     want = go_oracle.features(b, a, ko, pl, ["ladder_capture", "ladder_escape"])
     old = L.rag_set_ladder_handover(handover)
+    old_helpers = L.rag_set_ladder_helpers(helpers)
     try:
         for rep in range(2):
             got = _gpu_planes(g["board"], g["age"], g["ko"], g["player"], ["ladder_capture", "ladder_escape"])
@@ -179,3 +182,4 @@ def test_ladder_planes_do_not_depend_on_reply_handover(handover):
         assert np.array_equal(got, small["planes"][:, [45, 44]])
     finally:
         L.rag_set_ladder_handover(old)
+        L.rag_set_ladder_helpers(old_helpers)

@@ -266,7 +266,7 @@ def test_two_stream_pipeline_gives_the_same_results():
     net = CNNPolicy(go_oracle.DEFAULT_FEATURES, layers=4, filters_per_layer=64, dtype="fp16", seed=31)
     batches = [BatchedGameState.random_playouts(n, seed=500 + i, max_ply=300, stride=4) for i in range(5)]
     want = [net.model.eval_batch_device(b, net.preprocessor.plane_src).cpu().numpy() for b in batches]
-    pipe = EvalPipeline(net, n)
+    pipe = EvalPipeline(net, n, slots=3)
     tickets, got = [], {}
     for i, b in enumerate(batches):
         src = b.packed if i % 2 == 0 else b.packed.cpu().pin_memory()
@@ -279,7 +279,7 @@ def test_two_stream_pipeline_gives_the_same_results():
     for i in range(5):
         assert np.array_equal(got[i], want[i]), i
     with pytest.raises(ValueError):
-        pipe.result(0)                                          # long gone (5 batches through 4 slots)
+        pipe.result(0)                                          # long gone (5 batches through 3 slots)
     with pytest.raises(ValueError):
         pipe.submit(batches[0].packed[:10])
 
@@ -374,7 +374,7 @@ def test_pipeline_with_cuda_graphs_gives_the_same_results():
     net = CNNPolicy(go_oracle.DEFAULT_FEATURES, layers=3, filters_per_layer=64, dtype="fp16", seed=61)
     batches = [BatchedGameState.random_playouts(n, seed=700 + i, max_ply=350, stride=5) for i in range(7)]
     want = [net.model.eval_batch_device(b, net.preprocessor.plane_src).cpu().numpy() for b in batches]
-    pipe = EvalPipeline(net, n, graphs=True)
+    pipe = EvalPipeline(net, n, graphs=True, slots=4)
     for i, b in enumerate(batches):
         src = b.packed if i % 3 else b.packed.cpu().pin_memory()
         t = pipe.submit(src, to_host=(i % 2 == 0))

@@ -11,7 +11,7 @@ for n in (64, 256, 1024):
     bs = [BatchedGameState.random_playouts(n, seed=5 + i) for i in range(4)]
     for helpers in (32, 8):
         L.rag_set_ladder_helpers(helpers)
-        for slots in (4, 6):
+        for slots in (4, 6, 8, 12):
             pipe = EvalPipeline(net, n, graphs=True, slots=slots)
             for i in range(16): pipe.submit(bs[i % 4].packed)
             pipe.drain(); torch.cuda.synchronize()
@@ -20,4 +20,4 @@ for n in (64, 256, 1024):
             for i in range(K): pipe.submit(bs[i % 4].packed)
             pipe.drain(); torch.cuda.synchronize()
             t_all = time.time() - t0
-            print("wpp=%s n=%5d helpers=%4d slots=%d  %.1f us/step -> %.0f pos/s" % (os.environ.get("RAG_LADDER_WPP"), n, helpers, slots, t_all / K * 1e6, n * K / t_all))
+            print("carveout=%s n=%5d helpers=%4d slots=%d  %.1f us/step -> %.0f pos/s" % (os.environ.get("RAG_CARVEOUT"), n, helpers, slots, t_all / K * 1e6, n * K / t_all))
