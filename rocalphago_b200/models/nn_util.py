@@ -7,11 +7,12 @@ forward), not a Keras object: training is out of scope.
 """
 import ctypes
 import json
+import os
 
 import numpy as np
 import torch
 
-from .. import _cabi
+from .. import _cabi, hdf5_lite
 from ..preprocessing import Preprocess, DTYPE_BF16, DTYPE_FP16
 from ..state import _ptr, _stream, _require_cuda
 
@@ -40,7 +41,7 @@ class Network(object):
     get_weights() order and 'th' layouts, so Keras-trained arrays drop in with set_weights().
     """
 
-    def __init__(self, board, input_dim, specs, head="policy", dense_units=256, dtype="bf16",
+    def __init__(self, board, input_dim, specs, head="policy", dense_units=256, dtype="fp16",
                  kernel_flip=True, seed=None, unit_end=None):
         """unit_end (residual networks only, policy.py:141-271): one flag per convolution, 1 where it
         closes a residual unit (the first convolution counts as closing one: its output is the
@@ -106,14 +107,67 @@ class Network(object):
         self._weights = new
         self._dirty = True
 
+    def _keras_layers(self):
+        """[(layer name, [weight names])] in the order Keras 1.x stores them (`layer_names` /
+        `weight_names` attributes of a weight file); the weights follow `get_weights()` order."""
+        layers = []
+        for i in range(len(self.specs)):
+            if self.unit_end is not None and i > 0:
+                bn = "batchnormalization_%d" % i
+                layers.append((bn, [bn + "_gamma", bn + "_beta", bn + "_running_mean", bn + "_running_std"]))
+            cv = "convolution2d_%d" % (i + 1)
+            layers.append((cv, [cv + "_W", cv + "_b"]))
+        cv = "convolution2d_%d" % (len(self.specs) + 1)
+        layers += [(cv, [cv + "_W", cv + "_b"]), ("flatten_1", [])]
+        if self.head == "policy":
+            layers += [("bias_1", ["param_0"]), ("activation_1", [])]
+        else:
+            layers += [("dense_1", ["dense_1_W", "dense_1_b"]), ("dense_2", ["dense_2_W", "dense_2_b"])]
+        return layers
+
     def save_weights(self, path, overwrite=True):
-        """.npz twin of Keras' HDF5 weight file (no HDF5 library on this image)."""
-        with open(path, "wb") as f:
-            np.savez(f, **{"w%03d" % i: w for i, w in enumerate(self._weights)})
+        """Keras 1.x weight file (HDF5: root attribute `layer_names`, one group per layer with a
+        `weight_names` attribute and one dataset per array) when `path` ends in .hdf5/.h5 -- what
+        nn_util.py:93-96 writes through `model.save_weights`; any other extension gives an .npz
+        with the same arrays in `get_weights()` order."""
+        if not overwrite and os.path.exists(path):
+            raise IOError("%s exists" % path)
+        if not path.lower().endswith((".hdf5", ".h5")):
+            with open(path, "wb") as f:
+                np.savez(f, **{"w%03d" % i: w for i, w in enumerate(self._weights)})
+            return
+        w = hdf5_lite.Writer()
+        layers = self._keras_layers()
+        w.attrs["layer_names"] = np.array([n.encode() for n, _ in layers])
+        it = iter(self._weights)
+        for name, wnames in layers:
+            g = w.create_group(name)
+            g.attrs["weight_names"] = np.array([n.encode() for n in wnames]) if wnames else np.zeros(0, "S1")
+            for wn in wnames:
+                g[wn] = next(it)
+        w.save(path)
 
     def load_weights(self, path):
-        z = np.load(path)
-        self.set_weights([z["w%03d" % i] for i in range(len(z.files))])
+        """Reads a Keras 1.x HDF5 weight file (e.g. the reference's
+        tests/test_data/hdf5/random_minimodel_weights.hdf5) or this class's .npz."""
+        with open(path, "rb") as f:
+            magic = f.read(8)
+        if magic != hdf5_lite.SIGNATURE:
+            z = np.load(path)
+            self.set_weights([z["w%03d" % i] for i in range(len(z.files))])
+            return
+        f = hdf5_lite.File(path)
+        if "layer_names" not in f.attrs and "model_weights" in f:
+            f = f["model_weights"]                          # a full `model.save()` file
+        if "layer_names" not in f.attrs:
+            raise ValueError("%s has no layer_names attribute: not a Keras weight file" % path)
+        arrays = []
+        for layer in f.attrs["layer_names"]:
+            g = f[layer.decode("utf-8")]
+            for wn in np.atleast_1d(g.attrs.get("weight_names", [])):
+                if isinstance(wn, bytes):
+                    arrays.append(g[wn.decode("utf-8")][...])
+        self.set_weights(arrays)
 
     # -- (de)serialisation in Keras-1 Sequential JSON -------------------------------------------
     def to_json(self):
@@ -153,7 +207,7 @@ class Network(object):
         ext = km.get("rocalphago_b200", {})
         if ext.get("arch") == "resnet":
             return Network(ext["board"], ext["input_dim"], [tuple(x) for x in ext["specs"]], head="policy",
-                           dtype=ext.get("dtype", "bf16"), kernel_flip=ext.get("kernel_flip", True),
+                           dtype=ext.get("dtype", "fp16"), kernel_flip=ext.get("kernel_flip", True),
                            unit_end=ext["unit_end"])
         if km.get("class_name") != "Sequential":
             raise ValueError("only Sequential models are supported on this path (got %s)" % km.get("class_name"))
@@ -186,7 +240,7 @@ class Network(object):
             head = "value"
         extra = km.get("rocalphago_b200", {})
         return Network(board, input_dim, [(f, w) for f, w, _ in convs[:-1]], head=head,
-                       dense_units=dense[0][0] if dense else 256, dtype=extra.get("dtype", "bf16"),
+                       dense_units=dense[0][0] if dense else 256, dtype=extra.get("dtype", "fp16"),
                        kernel_flip=extra.get("kernel_flip", True))
 
     # -- the CUDA forward ---------------------------------------------------------------------
@@ -314,7 +368,7 @@ class NeuralNetBase(object):
         new_net = network_class(object_specs["feature_list"], init_network=False)
         new_net.model = Network.from_json(object_specs["keras_model"])
         if "weights_file" in object_specs:
-            new_net.model.load_weights(object_specs["weights_file"])
+            new_net.model.load_weights(_find_relative(object_specs["weights_file"], json_file))
         new_net.forward = new_net._model_forward()
         return new_net
 
@@ -329,6 +383,23 @@ class NeuralNetBase(object):
             object_specs["weights_file"] = weights_file
         with open(json_file, "w") as f:
             json.dump(object_specs, f)
+
+
+def _find_relative(path, json_file):
+    """The reference resolves `weights_file` against the working directory (its files say e.g.
+    'tests/test_data/hdf5/...' and are loaded from the repository root).  Same here; if that fails,
+    the directories above the JSON file are tried, so that a model can be loaded from anywhere."""
+    if os.path.isabs(path) or os.path.exists(path):
+        return path
+    d = os.path.dirname(os.path.abspath(json_file))
+    while True:
+        cand = os.path.join(d, path)
+        if os.path.exists(cand):
+            return cand
+        parent = os.path.dirname(d)
+        if parent == d:
+            return path
+        d = parent
 
 
 def neuralnet(cls):

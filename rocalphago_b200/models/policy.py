@@ -80,7 +80,7 @@ class CNNPolicy(NeuralNetBase):
             nb = params.get("filters_per_layer_%d" % i, params["filters_per_layer"])
             specs.append((nb, width))
         return Network(params["board"], params["input_dim"], specs, head="policy",
-                       dtype=params.get("dtype", "bf16"), kernel_flip=params.get("kernel_flip", True),
+                       dtype=params.get("dtype", "fp16"), kernel_flip=params.get("kernel_flip", True),
                        seed=params.get("seed"))
 
 
@@ -109,7 +109,7 @@ class ResnetPolicy(CNNPolicy):
                 specs.append((params["filters_per_layer"], params.get("filter_width_%d" % (layer + i), 3)))
                 unit_end.append(1 if i == n_skip - 1 else 0)
             layer += n_skip
-        return Network(params["board"], params["input_dim"], specs, head="policy", dtype=params.get("dtype", "bf16"),
+        return Network(params["board"], params["input_dim"], specs, head="policy", dtype=params.get("dtype", "fp16"),
                        kernel_flip=params.get("kernel_flip", True), seed=params.get("seed"), unit_end=unit_end)
 
 

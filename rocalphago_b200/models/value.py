@@ -49,7 +49,7 @@ class CNNValue(NeuralNetBase):
             nb = params.get("filters_per_layer_%d" % i, params["filters_per_layer"])
             specs.append((nb, width))
         return Network(params["board"], params["input_dim"], specs, head="value",
-                       dense_units=params["dense_units"], dtype=params.get("dtype", "bf16"),
+                       dense_units=params["dense_units"], dtype=params.get("dtype", "fp16"),
                        kernel_flip=params.get("kernel_flip", True), seed=params.get("seed"))
 
 

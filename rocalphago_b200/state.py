@@ -125,7 +125,7 @@ class BatchedGameState(object):
         Returns an int32 tensor: 0 played, -1 illegal (that position is left untouched)."""
         mv = [-1 if m is None else (m if np.isscalar(m) else m[0] * self.size + m[1]) for m in moves] \
             if not torch.is_tensor(moves) else moves
-        mv = torch.as_tensor(mv, dtype=torch.int32).to(self.device)
+        mv = torch.as_tensor(mv, dtype=torch.int32).to(self.device).contiguous()
         status = torch.empty(len(self), dtype=torch.int32, device=self.device)
         with torch.cuda.device(self.device):
             _cabi.check(_cabi.lib().rag_do_move(_ptr(self.packed), len(self), self.size, _ptr(mv), _ptr(status),
