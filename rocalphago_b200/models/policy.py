@@ -1,6 +1,7 @@
 """CNNPolicy on the B200 path (drop-in for AlphaGo/models/policy.py:9-138)."""
 import numpy as np
 
+from ..preprocessing import _points
 from ..state import BatchedGameState
 from .nn_util import NeuralNetBase, Network, neuralnet
 
@@ -44,7 +45,17 @@ class CNNPolicy(NeuralNetBase):
             batch = BatchedGameState.from_states(states)
         probs = self.model.eval_batch_device(batch, self.preprocessor.plane_src)
         if not moves_lists:
-            moves_lists = self.preprocessor.legal_move_lists(self.model.features_workspace(), n_states, state_size)
+            # all legal moves of every state: select and renormalise in one vectorised pass
+            which, flat, counts = self.preprocessor.legal_move_indices(self.model.features_workspace(), n_states, state_size)
+            network_output = probs.cpu().numpy()
+            picked = network_output[which, flat]
+            starts = np.concatenate([[0], np.cumsum(counts)[:-1]])
+            sums = np.add.reduceat(picked, np.minimum(starts, max(len(picked) - 1, 0))) if len(picked) else np.zeros(n_states, np.float32)
+            picked = (picked / np.repeat(sums, counts)).tolist()
+            points = _points(state_size)
+            moves = [points[p] for p in flat.tolist()]
+            ends = np.cumsum(counts).tolist()
+            return [list(zip(moves[e - c:e], picked[e - c:e])) for e, c in zip(ends, counts.tolist())]
         network_output = probs.cpu().numpy()
         results = [None] * n_states
         for i in range(n_states):

@@ -42,6 +42,16 @@ DTYPE_BF16, DTYPE_FP16 = 0, 1
 _MOVE_PLANES = np.asarray([46, 48], np.int32)      # sensibleness, legal
 
 
+_POINTS = {}
+
+
+def _points(size):
+    """[(x, y)] indexed by the flat point x*S+y (util.py:15-17), cached per board size."""
+    if size not in _POINTS:
+        _POINTS[size] = [(p // size, p % size) for p in range(size * size)]
+    return _POINTS[size]
+
+
 class _Workspace(object):
     """Grows-only scratch for the analyse step, one per (device)."""
 
@@ -112,17 +122,23 @@ class Preprocess(object):
         ws = self.analyze(batch)
         return self.emit(ws, len(batch), batch.size, layout=layout, **kw)
 
+    def legal_move_indices(self, ws, n, size):
+        """get_legal_moves() of every position in reference order (go.py:465-480): legal non-eye
+        points x-major, then legal own eyes x-major.  Returns (state index, flat point x*S+y) of
+        every move, both int64 arrays sorted by state, and the number of moves per state."""
+        P = size * size
+        two = self.emit(ws, n, size, LAYOUT_NCHW_U8, plane_src=_MOVE_PLANES).cpu().numpy().reshape(n, 2, P)
+        two[:, 1] &= 1 - two[:, 0]                       # own eyes only where not already listed
+        which, col = np.nonzero(two.reshape(n, 2 * P))   # row-major: by state, non-eyes before eyes, then by point
+        return which, col % P, np.bincount(which, minlength=n)
+
     def legal_move_lists(self, ws, n, size):
-        """get_legal_moves() of every position in reference order (go.py:465-480): legal
-        non-eye points x-major, then legal own eyes x-major.  Returns lists of (x, y)."""
-        two = self.emit(ws, n, size, LAYOUT_NCHW_U8, plane_src=_MOVE_PLANES).cpu().numpy().reshape(n, 2, -1)
-        out = []
-        for i in range(n):
-            sens = np.flatnonzero(two[i, 0])
-            eyes = np.flatnonzero(two[i, 1] & (1 - two[i, 0]))
-            idx = np.concatenate([sens, eyes])
-            out.append([(int(p) // size, int(p) % size) for p in idx])
-        return out
+        """The same as lists of (x, y) tuples, one list per position."""
+        _, flat, counts = self.legal_move_indices(ws, n, size)
+        points = _points(size)
+        moves = [points[p] for p in flat.tolist()]
+        ends = np.cumsum(counts).tolist()
+        return [moves[e - c:e] for e, c in zip(ends, counts.tolist())]
 
     # ------------------------------------------------------------------ reference-shaped API
     def states_to_tensor(self, states):

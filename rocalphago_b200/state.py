@@ -51,15 +51,10 @@ def arrays_from_states(states):
     size = states[0].size
     if not all(st.size == size for st in states):
         raise ValueError("all states must have the same size")       # policy.py:39-40
-    board = np.empty((n, size, size), np.int8)
-    age = np.empty((n, size, size), np.int16)
-    ko = np.empty(n, np.int32)
-    player = np.empty(n, np.int32)
-    for i, st in enumerate(states):
-        board[i] = st.board
-        age[i] = st.stone_ages
-        ko[i] = -1 if st.ko is None else st.ko[0] * size + st.ko[1]
-        player[i] = st.current_player
+    board = np.stack([st.board for st in states]).astype(np.int8, copy=False)
+    age = np.stack([st.stone_ages for st in states]).astype(np.int16, copy=False)
+    ko = np.array([-1 if st.ko is None else st.ko[0] * size + st.ko[1] for st in states], np.int32)
+    player = np.array([st.current_player for st in states], np.int32)
     return board, age, ko, player
 
 
@@ -93,7 +88,7 @@ class BatchedGameState(object):
     @classmethod
     def from_arrays(cls, board, age, ko, player, device=None):
         _require_cuda()
-        host = pack_arrays(board, age, ko, player, pinned=True)
+        host = pack_arrays(board, age, ko, player, pinned=len(ko) >= 1024)      # pinning costs more than it saves on small batches
         size = np.asarray(board).shape[-1]
         return cls(host.to(device or "cuda", non_blocking=True), size)
 
