@@ -122,7 +122,8 @@ def cpu_path(n_positions, cores, seed=99, pool=None):
     planes = np.concatenate(parts, axis=0)
     cnn_oracle.forward(weights, planes[:2], specs, threads=cores)
     t2 = time.time()
-    cnn_oracle.forward(weights, planes, specs, threads=cores)
+    for i in range(0, len(planes), 1024):               # bounded activations: 1,024 positions per forward call
+        cnn_oracle.forward(weights, planes[i:i + 1024], specs, threads=cores)
     t3 = time.time()
     if own_pool:
         pool.close()
@@ -449,7 +450,7 @@ def main():
     ap.add_argument("--pool", type=int, default=4, help="distinct input batches cycled through")
     ap.add_argument("--dtype", default="fp16", choices=["fp16", "bf16"])
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--cpu-sample", type=int, default=512)
+    ap.add_argument("--cpu-sample", type=int, default=8192, help="positions the CPU port is timed on (~15 s on 16 cores)")
     ap.add_argument("--ref-sample", type=int, default=256)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--workload", default="policy", choices=["policy", "features", "policy+value", "value"],
