@@ -323,6 +323,11 @@ __device__ __forceinline__ int ladder_search_steal(const Workspace& ws, const Ge
     return ladder_dfs_steal(ws, g, H, P, G, ko, pending, is_capture, remaining - 1, nodes + 1, steal_after, st, sf, own_status, t_start);
 }
 
+// kBesideConv only makes two copies of the kernel, so that each can have its own shared-memory / L1
+// preference (match_conv_carveout): 0 = launched by the one-call entry points, nothing else on the
+// GPU, keeps the default split (large L1 for the search stacks); 1 = the pipeline's separate ladder
+// stage, which runs underneath the convolutions of another stream.
+template <int kBesideConv>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 ladder_kernel(const uint32_t* __restrict__ states, int S, int steal_after, int helper_ctas, Workspace ws)
 {
@@ -621,8 +626,8 @@ constexpr size_t kStaticScratchBytes =                              // = workspa
     + (size_t)(kStaticMaxPositions / 2) * (sizeof(StealTask) + 4);
 static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
 
-// The kernels that run next to the convolutions in a pipeline (analysis, ladder reader, conv-layout
-// emit) ask for the same shared-memory / L1 split as the convolution kernel uses (all of it shared
+// The kernels that run next to the convolutions in a pipeline (analysis, the ladder reader of
+// rag_features_ladders, conv-layout emit) ask for the same shared-memory / L1 split as the convolution kernel uses (all of it shared
 // memory).  An SM has one split at a time and changes it only when it is empty: with different
 // preferences, a convolution CTA could not start on an SM where a ladder warp was still searching,
 // and -- the tiles of a layer being dealt out statically -- every layer then waited for a second
@@ -638,7 +643,7 @@ static int match_conv_carveout() {
     if (done[dev]) return RAG_OK;
     const int pct = (int)cudaSharedmemCarveoutMaxShared;
     RAG_CUDA_CHECK(cudaFuncSetAttribute(analyze_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
-    RAG_CUDA_CHECK(cudaFuncSetAttribute(ladder_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+    RAG_CUDA_CHECK(cudaFuncSetAttribute(ladder_kernel<1>, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
     RAG_CUDA_CHECK(cudaFuncSetAttribute(emit_conv_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
     done[dev] = true;
     return RAG_OK;
@@ -846,7 +851,7 @@ int rag_features_analyze(const uint32_t* d_states, int n, int size, int with_lad
         // and a convolution CTA of another stream (conv.cu) must still fit beside them.
         long long want = ((long long)n * 16 + kWarpsPerBlock - 1) / kWarpsPerBlock;
         int blocks = (int)(want < (long long)sms * 4 ? (want < 1 ? 1 : want) : (long long)sms * 4);
-        ladder_kernel<<<blocks, kWarpsPerBlock * 32, 0, s>>>(d_states, size, g_steal_after, g_helper_ctas, ws);
+        ladder_kernel<0><<<blocks, kWarpsPerBlock * 32, 0, s>>>(d_states, size, g_steal_after, g_helper_ctas, ws);
         RAG_CUDA_CHECK(cudaGetLastError());
     }
     return RAG_OK;
@@ -868,7 +873,7 @@ int rag_features_ladders(const uint32_t* d_states, int n, int size, void* d_work
     RAG_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     long long want = ((long long)n * 16 + kWarpsPerBlock - 1) / kWarpsPerBlock;
     int blocks = (int)(want < (long long)sms * 4 ? (want < 1 ? 1 : want) : (long long)sms * 4);
-    ladder_kernel<<<blocks, kWarpsPerBlock * 32, 0, (cudaStream_t)stream>>>(d_states, size, g_steal_after, g_helper_ctas, ws);
+    ladder_kernel<1><<<blocks, kWarpsPerBlock * 32, 0, (cudaStream_t)stream>>>(d_states, size, g_steal_after, g_helper_ctas, ws);
     RAG_CUDA_CHECK(cudaGetLastError());
     return RAG_OK;
 }
