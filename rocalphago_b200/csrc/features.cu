@@ -100,13 +100,18 @@ __device__ __forceinline__ int q_to_p(int q, int S) { return q < 0 ? -1 : ((q >>
 
 // ---- kernel 1: planes without look-ahead + ladder work items ---------------------------------
 
-__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+// Two warps (16 KB of shared memory) per CTA, so that a CTA still fits on an SM whose shared memory
+// is otherwise taken by a convolution CTA of another stream (conv.cu: ~208 of 228 KB): the analysis
+// of the next batch then runs beside the convolutions instead of in the gaps between their layers.
+constexpr int kAnalyzeWarps = 2;
+
+__global__ void __launch_bounds__(kAnalyzeWarps * 32)
 analyze_kernel(const uint32_t* __restrict__ states, int n, int S, int with_ladders, Workspace ws)
 {
-    __shared__ uint32_t sm_planes[kWarpsPerBlock][kPlaneWords];
-    __shared__ EyeStack sm_eye[kWarpsPerBlock];
+    __shared__ uint32_t sm_planes[kAnalyzeWarps][kPlaneWords];
+    __shared__ EyeStack sm_eye[kAnalyzeWarps];
     const int warp = threadIdx.x >> 5;
-    const int pos = blockIdx.x * kWarpsPerBlock + warp;
+    const int pos = blockIdx.x * kAnalyzeWarps + warp;
     if (pos >= n) return;
     const Geo g = make_geo(S);
     uint32_t* planes = sm_planes[warp];
@@ -840,7 +845,7 @@ int rag_features_analyze(const uint32_t* d_states, int n, int size, int with_lad
     Workspace ws = carve(d_workspace, n);
     RAG_CUDA_CHECK(cudaMemsetAsync(ws.counters, 0, kCounterBytes, s));
     RAG_CUDA_CHECK(cudaMemsetAsync(ws.tasks, 0, (size_t)ws.task_cap * (sizeof(StealTask) + 4), s));     // all tasks free, ring empty
-    analyze_kernel<<<(n + kWarpsPerBlock - 1) / kWarpsPerBlock, kWarpsPerBlock * 32, 0, s>>>(d_states, n, size, with_ladders, ws);
+    analyze_kernel<<<(n + kAnalyzeWarps - 1) / kAnalyzeWarps, kAnalyzeWarps * 32, 0, s>>>(d_states, n, size, with_ladders, ws);
     RAG_CUDA_CHECK(cudaGetLastError());
     if (with_ladders == 1) {
         int dev = 0, sms = 148;

@@ -59,7 +59,8 @@ class EvalPipeline(object):
         `graphs`: replay each stage as a CUDA graph from the second use of a slot on; cuts the host's
         cost of a step from ~450 us to ~60 us.  (Per-layer profiling -- rag_net_set_profiling -- must
         be off then.)
-        `slots`: batches in flight (default 2 for large batches, 8 below 2,048 positions).  Each slot
+        `slots`: batches in flight (default 3 for large batches -- two stall the forwards whenever a batch's
+        ladder stage outlasts one forward -- and 8 below 2,048 positions).  Each slot
         has its own stream for the feature stage, so with more slots several ladder searches --
         latency-bound, a few warps each at small batch sizes -- run side by side under the forwards;
         forwards run in submission order, so the slots must cover the longest search (~2.5 ms against
@@ -85,7 +86,7 @@ class EvalPipeline(object):
             self.vchannels = int(self.L.rag_net_input_channels(self.vhandle))
             self.vdtype_code = 0 if value_net.model.dtype == "bf16" else 1
         self.trace = None       # set to [] to collect, per batch, timing events [start, analysis end, features end, forward start, forward end] (tools/pipeline_timeline.py)
-        self.nslots = int(slots) if slots else (2 if self.n >= 2048 else 8)
+        self.nslots = int(slots) if slots else (3 if self.n >= 2048 else 8)
         if self.nslots < 2:
             raise ValueError("at least two slots")
         with torch.cuda.device(self.device):
