@@ -448,7 +448,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--batch", type=int, default=4096, help="positions per GPU per step")
     ap.add_argument("--pool", type=int, default=4, help="distinct input batches cycled through")
-    ap.add_argument("--dtype", default="fp16", choices=["fp16", "bf16"])
+    ap.add_argument("--dtype", default="fp16", choices=["fp16", "bf16", "fp16x3"], help="operand precision of the convolutions (fp16x3: split operands, fp32-like results, a third of the speed)")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--cpu-sample", type=int, default=8192, help="positions the CPU port is timed on (~15 s on 16 cores)")
     ap.add_argument("--ref-sample", type=int, default=256)

@@ -84,6 +84,10 @@ int rag_unpack_states(int n, int size, const uint32_t* h_packed, int8_t* h_board
 
 #define RAG_DTYPE_BF16 0
 #define RAG_DTYPE_FP16 1
+/* fp16 tensor-core operands, every product formed from split operands (x = hi + lo): hi*hi + lo*hi +
+ * hi*lo with fp32 accumulation -- fp32-like results at a third of the speed.  For callers that need the
+ * reference's fp32 arg-max on nearly flat outputs (random-init networks); not for residual networks. */
+#define RAG_DTYPE_FP16X3 2
 
 /* bytes of scratch rag_features / rag_features_analyze need for n positions */
 size_t rag_features_workspace_bytes(int n);
@@ -199,7 +203,7 @@ typedef struct rag_net_desc {
     int widths[RAG_MAX_LAYERS];      /* filter_width_K (odd, <= 7)          policy.py:108-110 */
     int head;                        /* RAG_HEAD_POLICY / RAG_HEAD_VALUE    */
     int dense_units;                 /* value head: 256                     value.py:27   */
-    int dtype;                       /* RAG_DTYPE_BF16 / RAG_DTYPE_FP16 operands */
+    int dtype;                       /* RAG_DTYPE_BF16 / RAG_DTYPE_FP16 operands, or RAG_DTYPE_FP16X3 */
     int kernel_flip;                 /* 1: Theano semantics (true convolution, the reference's
                                         pinned backend); 0: cross-correlation (TensorFlow) */
     int resnet;                      /* 1: ResnetPolicy (policy.py:141-271): convolution 1 is linear, every

@@ -36,7 +36,6 @@ namespace rag {
 
 constexpr int kTileM = 128;           // rows (pixels) per accumulator tile
 constexpr int kChunkK = 64;           // channels per smem stage (= one 128-byte swizzled row)
-constexpr int kMaxTaps = 49;
 constexpr int kMaxBoardPoints = 361;
 constexpr int kTmemCols = 512;
 constexpr int kConvThreads = 192;
@@ -59,6 +58,10 @@ struct ConvParams {
     uint16_t* linear_out;         // [rows][N] or null
     const float* bn_scale;        // [S] (indexed by y, the reference's BatchNormalization axis) or null
     const float* bn_shift;
+    // split-operand mode (RAG_DTYPE_FP16X3): activation rows hold [hi | lo] halves, the K walk reads
+    // the A chunks [hi, lo, hi] against weights stored as [W_hi, W_hi, W_lo] (see rag_net_load_weights)
+    int a_wrap;                   // A chunk index = c < a_wrap ? c : c - a_wrap   (0: no wrap)
+    int split_out;                // mode 0: write fp16 hi and lo halves, row pitch 2 N
 };
 
 // ---- PTX wrappers ----------------------------------------------------------------------------
@@ -253,16 +256,17 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                             const uint32_t ph = (it / (uint32_t)p.stages) & 1u;
                             mbar_wait(empty_bar(s), ph ^ 1u);
                             const uint32_t sa = base + (uint32_t)s * stage_bytes;
+                            const int ca = (p.a_wrap && c >= p.a_wrap) ? c - p.a_wrap : c;    // split mode: [hi, lo, hi]
                             // tensor dims are (C, y, x, board): y is the fast spatial index
                             if (kPair) {
                                 // both CTAs' bytes are counted on the leader's barrier
                                 if (rank == 0) mbar_expect_tx(full_bar(s), 2u * stage_bytes);
                                 const uint32_t lb = full_bar(s) & kPeerBitMask;
-                                tma_load_im2col_pair(sa, &tmA, c * kChunkK, y0 - pad, x0 - pad, b0, (uint16_t)j, (uint16_t)i, lb);
+                                tma_load_im2col_pair(sa, &tmA, ca * kChunkK, y0 - pad, x0 - pad, b0, (uint16_t)j, (uint16_t)i, lb);
                                 tma_load_2d_pair(sa + kATileBytes, &tmB, c * kChunkK, t * p.N + (int)(rank * b_rows), lb);
                             } else {
                                 mbar_expect_tx(full_bar(s), stage_bytes);
-                                tma_load_im2col(sa, &tmA, c * kChunkK, y0 - pad, x0 - pad, b0, (uint16_t)j, (uint16_t)i, full_bar(s));
+                                tma_load_im2col(sa, &tmA, ca * kChunkK, y0 - pad, x0 - pad, b0, (uint16_t)j, (uint16_t)i, full_bar(s));
                                 tma_load_2d(sa + kATileBytes, &tmB, c * kChunkK, t * p.N, full_bar(s));
                             }
                         }
@@ -309,7 +313,36 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             mbar_wait(tfull_bar((int)a), aph);
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + a * (uint32_t)p.N;
-            if (p.mode == 0) {
+            if (p.mode == 0 && p.split_out) {
+                // x = hi + lo with both halves fp16: the next layer multiplies both by the weights
+                uint16_t* orow = reinterpret_cast<uint16_t*>(p.out) + row * (2 * p.N);
+                for (int c0 = 0; c0 < p.N; c0 += 32) {
+                    uint32_t v[32];
+                    tc_ld32(taddr + (uint32_t)c0, v);
+                    tc_wait_ld();
+                    uint32_t hi[16], lo[16];
+                    #pragma unroll
+                    for (int j = 0; j < 16; j++) {
+                        float f0 = __uint_as_float(v[2 * j]) + s_bias[c0 + 2 * j];
+                        float f1 = __uint_as_float(v[2 * j + 1]) + s_bias[c0 + 2 * j + 1];
+                        if (p.relu) { f0 = fmaxf(f0, 0.f); f1 = fmaxf(f1, 0.f); }
+                        __half2 h = __floats2half2_rn(f0, f1);
+                        const float2 back = __half22float2(h);
+                        __half2 l = __floats2half2_rn(f0 - back.x, f1 - back.y);
+                        hi[j] = *reinterpret_cast<uint32_t*>(&h);
+                        lo[j] = *reinterpret_cast<uint32_t*>(&l);
+                    }
+                    if (real) {
+                        uint4* dh = reinterpret_cast<uint4*>(orow + c0);
+                        uint4* dl = reinterpret_cast<uint4*>(orow + p.N + c0);
+                        #pragma unroll
+                        for (int j = 0; j < 4; j++) {
+                            dh[j] = make_uint4(hi[4 * j], hi[4 * j + 1], hi[4 * j + 2], hi[4 * j + 3]);
+                            dl[j] = make_uint4(lo[4 * j], lo[4 * j + 1], lo[4 * j + 2], lo[4 * j + 3]);
+                        }
+                    }
+                }
+            } else if (p.mode == 0) {
                 uint16_t* orow = reinterpret_cast<uint16_t*>(p.out) + row * p.N;
                 for (int c0 = 0; c0 < p.N; c0 += 32) {
                     uint32_t v[32];
@@ -425,7 +458,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
 // (N, F, S, S) float -> pixel rows (what NeuralNetBase.forward is handed, nn_util.py:57-58)
 __global__ void __launch_bounds__(256)
-nchw_to_rows_kernel(const float* __restrict__ in, int n, int F, int S, int C, int dtype, uint16_t* __restrict__ out)
+nchw_to_rows_kernel(const float* __restrict__ in, int n, int F, int S, int C, int dtype, int split, uint16_t* __restrict__ out)
 {
     const int S2 = S * S, chunks = C / 8;
     const long long total = (long long)n * S2 * chunks;
@@ -436,8 +469,11 @@ nchw_to_rows_kernel(const float* __restrict__ in, int n, int F, int S, int C, in
         __align__(16) uint16_t v[8];
         #pragma unroll
         for (int j = 0; j < 8; j++) {
-            const int f = ch * 8 + j;
+            // split mode: channels [0, C/2) hold fp16(x), channels [C/2, C) hold fp16(x - fp16(x))
+            const bool lo_half = split && ch * 8 >= C / 2;
+            const int f = ch * 8 + j - (lo_half ? C / 2 : 0);
             float val = f < F ? in[((long long)pos * F + f) * S2 + r] : 0.f;
+            if (lo_half) val -= __half2float(__float2half_rn(val));
             if (dtype == RAG_DTYPE_BF16) { __nv_bfloat16 h = __float2bfloat16_rn(val); v[j] = *reinterpret_cast<uint16_t*>(&h); }
             else { __half h = __float2half_rn(val); v[j] = *reinterpret_cast<uint16_t*>(&h); }
         }
@@ -550,7 +586,9 @@ static int round_up(int v, int m) { return (v + m - 1) / m * m; }
 
 struct Layer {
     int width, cin, cout, cin_pad, n_pad, taps;
-    uint16_t* d_w = nullptr;      // [taps][n_pad][cin_pad]
+    int cin_store = 0;            // channels of this layer's input rows: cin_pad, or 2 * cin_pad ([hi | lo]) in split mode
+    int kdim = 0;                 // K extent of the weights per tap: cin_pad, or 3 * cin_pad ([W_hi | W_hi | W_lo])
+    uint16_t* d_w = nullptr;      // [taps][n_pad][kdim]
     float* d_bias = nullptr;      // [n_pad]
     float* d_bn_scale = nullptr;  // residual nets: BatchNormalization applied to this layer's INPUT, [S] each
     float* d_bn_shift = nullptr;
@@ -572,6 +610,8 @@ struct rag_net {
     float* d_dense1_b = nullptr;
     float* d_dense2_w = nullptr;   // [D]
     float* d_dense2_b = nullptr;   // [1]
+    bool split = false;            // RAG_DTYPE_FP16X3: fp16 operands, every product formed as hi*hi + lo*hi + hi*lo
+    int op_dtype = RAG_DTYPE_FP16; // what the tensor cores are fed
     bool loaded = false;
     bool profiling = false;        // record a CUDA event around every convolution launch
     std::vector<cudaEvent_t> events;   // layers + 1
@@ -614,8 +654,8 @@ static NetBuffers carve_net(const rag_net* net, int n, void* ws, bool with_input
     NetBuffers b;
     auto al = [](size_t v) { return (v + 1023) / 1024 * 1024; };
     const long long rows = dense_rows(n, net->desc.board);
-    b.act_bytes = al((size_t)rows * net->max_c * 2);
-    b.in_bytes = with_input ? al((size_t)rows * net->layers[0].cin_pad * 2) : 0;
+    b.act_bytes = al((size_t)rows * net->max_c * 2 * (net->split ? 2 : 1));
+    b.in_bytes = with_input ? al((size_t)rows * net->layers[0].cin_store * 2) : 0;
     size_t logits_bytes = al((size_t)n * net->desc.board * net->desc.board * 4);
     char* p = (char*)ws;
     b.act[0] = (uint16_t*)p; p += b.act_bytes;
@@ -646,8 +686,9 @@ static int run_layers(rag_net* net, const uint16_t* d_in, int n, float* d_out, c
         memset(&p, 0, sizeof p);
         p.rows = (long long)n * S * S;
         p.tiles = (int)((p.rows + kTileM - 1) / kTileM);
-        p.width = ly.width; p.kchunks = ly.cin_pad / kChunkK; p.N = ly.n_pad;
-        p.stages = pick_stages(ly.n_pad); p.dtype = net->desc.dtype;
+        p.width = ly.width; p.kchunks = ly.kdim / kChunkK; p.N = ly.n_pad;
+        p.stages = pick_stages(ly.n_pad); p.dtype = net->op_dtype;
+        if (net->split) { p.a_wrap = 2 * ly.cin_pad / kChunkK; p.split_out = 1; }
         p.S = S; p.n = n;
         p.mode = last ? 1 : 0; p.relu = 1;
         p.bias = ly.d_bias; p.head_w = net->d_head_w; p.head_b = net->head_b;
@@ -668,8 +709,8 @@ static int run_layers(rag_net* net, const uint16_t* d_in, int n, float* d_out, c
             p.stages = pick_stages(ly.n_pad / 2);
         }
         CUtensorMap tmA, tmB;
-        if (int rc = make_map_im2col(&tmA, cur, n, S, ly.cin_pad, ly.width, net->desc.dtype)) return rc;
-        if (int rc = make_map(&tmB, ly.d_w, (long long)ly.taps * ly.n_pad, ly.cin_pad, pair ? ly.n_pad / 2 : ly.n_pad, net->desc.dtype)) return rc;
+        if (int rc = make_map_im2col(&tmA, cur, n, S, ly.cin_store, ly.width, net->op_dtype)) return rc;
+        if (int rc = make_map(&tmB, ly.d_w, (long long)ly.taps * ly.n_pad, ly.kdim, pair ? ly.n_pad / 2 : ly.n_pad, net->op_dtype)) return rc;
         if (net->profiling) RAG_CUDA_CHECK(cudaEventRecord(net->events[l], s));
         if (pair) {
             const size_t smem = conv_smem_bytes(ly.n_pad / 2, p.stages) + (size_t)ly.n_pad * 4;      // bias/head tables are N wide
@@ -728,7 +769,9 @@ int rag_net_create(const rag_net_desc* desc, rag_net** out)
     if (desc->layers < 1 || desc->layers > RAG_MAX_LAYERS) return fail(RAG_EINVAL, "layers %d not in [1, %d]", desc->layers, RAG_MAX_LAYERS);
     if (desc->in_planes < 1 || desc->in_planes > 128) return fail(RAG_EUNSUPPORTED, "in_planes %d not in [1, 128]", desc->in_planes);
     if (desc->head != RAG_HEAD_POLICY && desc->head != RAG_HEAD_VALUE) return fail(RAG_EINVAL, "head %d", desc->head);
-    if (desc->dtype != RAG_DTYPE_BF16 && desc->dtype != RAG_DTYPE_FP16) return fail(RAG_EINVAL, "dtype %d", desc->dtype);
+    if (desc->dtype != RAG_DTYPE_BF16 && desc->dtype != RAG_DTYPE_FP16 && desc->dtype != RAG_DTYPE_FP16X3) return fail(RAG_EINVAL, "dtype %d", desc->dtype);
+    if (desc->dtype == RAG_DTYPE_FP16X3 && desc->resnet) return fail(RAG_EUNSUPPORTED, "split-operand precision is not available for residual networks");
+    if (desc->dtype == RAG_DTYPE_FP16X3 && desc->in_planes > 64) return fail(RAG_EUNSUPPORTED, "split-operand precision takes at most 64 input planes (%d given)", desc->in_planes);
     if (desc->head == RAG_HEAD_VALUE && (desc->dense_units < 1 || desc->dense_units > 4096)) return fail(RAG_EINVAL, "dense_units %d", desc->dense_units);
     if (desc->resnet) {
         if (desc->head != RAG_HEAD_POLICY) return fail(RAG_EUNSUPPORTED, "residual networks are policy networks (policy.py:141)");
@@ -738,6 +781,8 @@ int rag_net_create(const rag_net_desc* desc, rag_net** out)
     }
     rag_net* net = new rag_net();
     net->desc = *desc;
+    net->split = desc->dtype == RAG_DTYPE_FP16X3;
+    net->op_dtype = desc->dtype == RAG_DTYPE_BF16 ? RAG_DTYPE_BF16 : RAG_DTYPE_FP16;
     int cin = desc->in_planes;
     for (int l = 0; l < desc->layers; l++) {
         Layer ly;
@@ -745,6 +790,7 @@ int rag_net_create(const rag_net_desc* desc, rag_net** out)
         if (ly.width < 1 || ly.width > 7 || ly.width % 2 == 0) { delete net; return fail(RAG_EUNSUPPORTED, "filter_width_%d = %d (odd, <= 7 supported)", l + 1, ly.width); }
         if (ly.cout < 1 || ly.cout > 256) { delete net; return fail(RAG_EUNSUPPORTED, "filters_per_layer_%d = %d (<= 256 supported)", l + 1, ly.cout); }
         ly.cin_pad = round_up(cin, kChunkK); ly.n_pad = round_up(ly.cout, kChunkK); ly.taps = ly.width * ly.width;
+        ly.cin_store = net->split ? 2 * ly.cin_pad : ly.cin_pad; ly.kdim = net->split ? 3 * ly.cin_pad : ly.cin_pad;
         if (pick_stages(ly.n_pad) < 2) { delete net; return fail(RAG_EUNSUPPORTED, "layer %d does not fit shared memory", l + 1); }
         if (ly.n_pad > net->max_c) net->max_c = ly.n_pad;
         net->layers.push_back(ly);
@@ -785,7 +831,7 @@ int rag_net_load_weights(rag_net* net, const float* const* h_arrays, int n_array
     if (n_arrays != rag_net_num_weight_arrays(net)) return fail(RAG_EINVAL, "expected %d weight arrays, got %d", rag_net_num_weight_arrays(net), n_arrays);
     for (int i = 0; i < n_arrays; i++) if (!h_arrays[i]) return fail(RAG_EINVAL, "weight array %d is null", i);
     RAG_CUDA_CHECK(cudaSetDevice(net->device));
-    const int dtype = net->desc.dtype, L = (int)net->layers.size(), P = net->desc.board * net->desc.board;
+    const int dtype = net->op_dtype, L = (int)net->layers.size(), P = net->desc.board * net->desc.board;
     int ai = 0;
     for (int l = 0; l < L; l++) {
         Layer& ly = net->layers[l];
@@ -804,16 +850,25 @@ int rag_net_load_weights(rag_net* net, const float* const* h_arrays, int n_array
         const float* W = h_arrays[ai++];      // (cout, cin, kh, kw)  Keras 'th' kernel layout
         const float* bsrc = h_arrays[ai++];   // (cout,)
         const int k = ly.width;
-        std::vector<uint16_t> w((size_t)ly.taps * ly.n_pad * ly.cin_pad, 0);
+        std::vector<uint16_t> w((size_t)ly.taps * ly.n_pad * ly.kdim, 0);
         for (int i = 0; i < k; i++)
             for (int j = 0; j < k; j++) {
                 // tap (i, j) reads in[x + i - pad, y + j - pad].  Theano's conv2d is a true
                 // convolution, i.e. a correlation with the kernel rotated by 180 degrees.
                 const int si = net->desc.kernel_flip ? k - 1 - i : i, sj = net->desc.kernel_flip ? k - 1 - j : j;
                 for (int co = 0; co < ly.cout; co++)
-                    for (int ci = 0; ci < ly.cin; ci++)
-                        w[((size_t)(i * k + j) * ly.n_pad + co) * ly.cin_pad + ci] =
-                            to16(W[(((size_t)co * ly.cin + ci) * k + si) * k + sj], dtype);
+                    for (int ci = 0; ci < ly.cin; ci++) {
+                        const float v = W[(((size_t)co * ly.cin + ci) * k + si) * k + sj];
+                        uint16_t* row = &w[((size_t)(i * k + j) * ly.n_pad + co) * ly.kdim];
+                        row[ci] = to16(v, dtype);
+                        if (net->split) {
+                            // the K walk reads activations as [hi, lo, hi]: weights [W_hi, W_hi, W_lo]
+                            // give hi*W_hi + lo*W_hi + hi*W_lo; the lo*lo term (2^-22 relative) is dropped
+                            const __half h = __float2half_rn(v);
+                            row[ly.cin_pad + ci] = row[ci];
+                            row[2 * ly.cin_pad + ci] = to16(v - __half2float(h), dtype);
+                        }
+                    }
             }
         std::vector<float> bias(ly.n_pad, 0.f);
         for (int co = 0; co < ly.cout; co++) bias[co] = bsrc[co];
@@ -885,7 +940,7 @@ size_t rag_net_logits_offset(const rag_net* net, int n)
 }
 
 long long rag_net_input_rows(const rag_net* net, int n) { return net ? dense_rows(n, net->desc.board) : 0; }
-int rag_net_input_channels(const rag_net* net) { return net ? net->layers[0].cin_pad : 0; }
+int rag_net_input_channels(const rag_net* net) { return net ? net->layers[0].cin_store : 0; }
 
 static int net_ready(const rag_net* net, int n, const void* in, const void* out, const void* ws, size_t bytes) {
     if (!net) return fail(RAG_EINVAL, "null net");
@@ -911,8 +966,8 @@ int rag_net_forward(rag_net* net, const float* d_nchw, int n, float* d_out, void
     NetBuffers b = carve_net(net, n, d_workspace, true);
     const Layer& l0 = net->layers[0];
     const int S = net->desc.board;
-    long long threads = (long long)n * S * S * (l0.cin_pad / 8);
-    nchw_to_rows_kernel<<<(int)((threads + 255) / 256), 256, 0, s>>>(d_nchw, n, net->desc.in_planes, S, l0.cin_pad, net->desc.dtype, b.in_rows);
+    long long threads = (long long)n * S * S * (l0.cin_store / 8);
+    nchw_to_rows_kernel<<<(int)((threads + 255) / 256), 256, 0, s>>>(d_nchw, n, net->desc.in_planes, S, l0.cin_store, net->op_dtype, net->split ? 1 : 0, b.in_rows);
     RAG_CUDA_CHECK(cudaGetLastError());
     return run_layers(net, b.in_rows, n, d_out, b, s);
 }
@@ -938,8 +993,9 @@ int rag_eval_batch(rag_net* net, const uint32_t* d_states, int n, const int32_t*
     char* ws = (char*)d_workspace;
     NetBuffers b = carve_net(net, n, ws + fbytes, true);
     const Layer& l0 = net->layers[0];
-    if (int rc = rag_features(d_states, n, net->desc.board, h_plane_src, F, RAG_LAYOUT_CONV_IN, net->desc.dtype,
-                              l0.cin_pad, b.in_rows, ws, fbytes, stream)) return rc;
+    // feature planes are 0/1, exact in 16 bits: in split mode the lo half of the rows is the zero padding
+    if (int rc = rag_features(d_states, n, net->desc.board, h_plane_src, F, RAG_LAYOUT_CONV_IN, net->op_dtype,
+                              l0.cin_store, b.in_rows, ws, fbytes, stream)) return rc;
     return run_layers(net, b.in_rows, n, d_out, b, (cudaStream_t)stream);
 }
 

@@ -13,7 +13,7 @@ import numpy as np
 import torch
 
 from .. import _cabi, hdf5_lite
-from ..preprocessing import Preprocess, DTYPE_BF16, DTYPE_FP16
+from ..preprocessing import Preprocess, DTYPE_BF16, DTYPE_FP16, DTYPE_FP16X3
 from ..state import _ptr, _stream, _require_cuda
 
 HEAD_POLICY, HEAD_VALUE = 0, 1
@@ -52,6 +52,8 @@ class Network(object):
         if self.unit_end is not None and (len(self.unit_end) != len(self.specs) or not self.unit_end[0] or not self.unit_end[-1]):
             raise ValueError("unit_end needs one flag per convolution, set on the first and the last")
         self.head, self.dense_units = head, int(dense_units)
+        if dtype not in ("fp16", "bf16", "fp16x3"):
+            raise ValueError("dtype must be 'fp16', 'bf16' or 'fp16x3' (got %r)" % (dtype,))
         self.dtype, self.kernel_flip = dtype, bool(kernel_flip)
         self.input_shape = (None, self.input_dim, self.board, self.board)      # read by trainers
         self.output_shape = (None, self.board * self.board) if head == "policy" else (None, 1)
@@ -258,7 +260,7 @@ class Network(object):
                 d.filters[i], d.widths[i] = nb, k
             d.head = HEAD_POLICY if self.head == "policy" else HEAD_VALUE
             d.dense_units = self.dense_units
-            d.dtype = DTYPE_BF16 if self.dtype == "bf16" else DTYPE_FP16
+            d.dtype = {"bf16": DTYPE_BF16, "fp16": DTYPE_FP16, "fp16x3": DTYPE_FP16X3}[self.dtype]
             d.kernel_flip = int(self.kernel_flip)
             d.resnet = int(self.unit_end is not None)
             for i, u in enumerate(self.unit_end or []):

@@ -74,7 +74,8 @@ class CNNPolicy(NeuralNetBase):
         Keyword Arguments (same names as the reference):
         - input_dim, board (19), filters_per_layer (128), filters_per_layer_K, layers (12),
           filter_width_K (3; first layer 5)
-        and, for this implementation: dtype ('bf16' | 'fp16' operands of the convolutions),
+        and, for this implementation: dtype ('fp16' (default) | 'bf16' operands of the convolutions, or 'fp16x3': fp16 operands
+        split into hi + lo parts, fp32-like results at a third of the speed),
         kernel_flip (True = Theano convolution semantics), seed (None = fresh random weights).
         """
         defaults = {

@@ -38,7 +38,7 @@ DEFAULT_FEATURES = [
     "sensibleness", "zeros"]
 
 LAYOUT_NCHW_U8, LAYOUT_NCHW_F32, LAYOUT_CONV_IN = 0, 1, 2
-DTYPE_BF16, DTYPE_FP16 = 0, 1
+DTYPE_BF16, DTYPE_FP16, DTYPE_FP16X3 = 0, 1, 2        # include/rocalphago_b200.h: RAG_DTYPE_*
 _MOVE_PLANES = np.asarray([46, 48], np.int32)      # sensibleness, legal
 
 

@@ -94,6 +94,58 @@ def test_policy_13x192_parity_and_top1():
     assert report["bf16"]["logit_rel"] <= 0.25, report
 
 
+def test_split_operand_mode_meets_the_top1_gate_on_random_init_weights():
+    """dtype='fp16x3' (every product formed as hi*hi + lo*hi + hi*lo from fp16 halves, fp32
+    accumulation): fp32-like logits, so the north_star gates hold even where the outputs are nearly
+    flat -- the case fp16 (99.4 %) and bf16 (96 %) operands cannot decide."""
+    feats = go_oracle.DEFAULT_FEATURES
+    n = 1024
+    b, a, ko, pl = _positions(n, seed=23)
+    planes = go_oracle.features(b, a, ko, pl, feats)
+    specs = cnn_oracle.layer_specs(input_dim=48, layers=12, filters_per_layer=192)
+    weights = cnn_oracle.uniform_weights(specs, 48, 19, seed=7)
+    want = cnn_oracle.forward(weights, planes, specs, threads=os.cpu_count())
+    net = CNNPolicy(feats, layers=12, filters_per_layer=192, dtype="fp16x3")
+    net.model.set_weights(weights)
+    batch = BatchedGameState.from_arrays(b, a, ko, pl)
+    got = net.model.eval_batch_device(batch, net.preprocessor.plane_src).cpu().numpy()
+    st = _policy_stats(got, want)
+    print("policy 13x192 fp16x3:", json.dumps(st))
+    assert st["max_abs"] <= PROB_TOL and st["top1"] >= TOP1_MIN, st
+    assert st["logit_rel"] <= 1e-3, st
+    # the same through NeuralNetBase.forward (float planes in) and the pipeline
+    from rocalphago_b200.pipeline import EvalPipeline
+    got2 = net.forward(planes[:64])
+    assert np.abs(got2 - want[:64]).max() <= 1e-6 + 1e-4 * want[:64].max()
+    pipe = EvalPipeline(net, n, slots=2)
+    got3 = pipe.result(pipe.submit(batch.packed)).cpu().numpy()
+    assert np.array_equal(got3, got)
+
+
+@pytest.mark.parametrize("arch,n", [
+    (dict(layers=3, filters_per_layer=32), 16),
+    (dict(layers=4, filters_per_layer=128, filter_width_2=1, filter_width_3=5, filters_per_layer_2=64), 9),
+    (dict(layers=3, filters_per_layer=152), 9),
+])
+def test_split_operand_mode_small_networks_and_real_valued_inputs(arch, n):
+    """forward() accepts any float planes (nn_util.py:57-58), not only 0/1 features: the split of
+    the input into hi + lo halves is exercised with Gaussian inputs."""
+    feats = go_oracle.DEFAULT_FEATURES
+    net = CNNPolicy(feats, dtype="fp16x3", seed=4, **arch)
+    x = np.random.RandomState(8).normal(0, 1, size=(n, 48, 19, 19)).astype(np.float32)
+    want = cnn_oracle.forward(net.model.get_weights(), x, net.model.specs)
+    got = net.forward(x)
+    st = _policy_stats(got, want)
+    assert st["max_abs"] <= 1e-6 and st["logit_rel"] <= 1e-3 and st["top1"] == 1.0, st
+    val = CNNValue(feats + ["color"], dtype="fp16x3", seed=5, dense_units=64, **arch)
+    b, a, ko, pl = _positions(n)
+    planes = go_oracle.features(b, a, ko, pl, feats + ["color"])
+    want_v = cnn_oracle.forward(val.model.get_weights(), planes, val.model.specs, head="value")
+    assert np.abs(val.forward(planes).reshape(-1) - want_v.reshape(-1)).max() <= 1e-5
+    with pytest.raises(ValueError):
+        CNNPolicy(feats, dtype="fp32", **arch)
+
+
 def test_policy_sharper_weights_top1():
     """With a trained-like (sharper) output distribution fp16 operands meet both gates (2e-3 and
     99.5 % top-1).  bf16's 8-bit mantissa does not hold 2e-3 once probabilities are of order 0.1
