@@ -355,10 +355,13 @@ def run_gpu(args):
                          "ms_per_launch": k3,
                          # dram__bytes_read.sum + dram__bytes_write.sum per launch from the ncu --set full capture
                          # of this kernel at batch 4096 (profiles/r1_final_ncu_summary.md); scales with the batch
-                         "traffic": {"bytes": int(1.0892e9 * n / 4096), "algorithmic_bytes": int(n * 361 * 192 * 2 * 2),
+                         "traffic": None if args.dtype == "fp16x3" else
+                                    {"bytes": int(1.0892e9 * n / 4096), "algorithmic_bytes": int(n * 361 * 192 * 2 * 2),
                                      "source": "profiles/r1_final_ncu_summary.md"},
                          "note": "CUDA events recorded by the library on the launching stream, sampled %d time(s) inside "
-                                 "the timed region while the next batch's feature kernels share the SMs" % samples},
+                                 "the timed region while the next batch's feature kernels share the SMs" % samples
+                                 + ("; fp16x3 issues three MMAs per algorithmic product, so the achievable fraction is 1/3"
+                                    if args.dtype == "fp16x3" else "")},
             "stage_ms": {"conv_layer1": float(layer_ms[0]), "conv_3x3_mean": k3, "conv_all": float(layer_ms.sum()),
                          "pipelined_step": dev_ms / K, "serial_step": serial_ms},
             "whole_net_tflops": FLOP_POLICY * n / (float(layer_ms.sum()) / 1e3) / 1e12,
