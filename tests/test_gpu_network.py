@@ -433,3 +433,24 @@ def test_pipeline_with_cuda_graphs_gives_the_same_results():
         assert np.array_equal(pipe.result(t).cpu().numpy(), want[i]), i
     assert all(len(s.graphs) == 3 for s in pipe.slots[:3])      # 7 batches over 4 slots: slots 0-2 were used twice
     pipe.drain()
+
+
+def test_integration_md_ctypes_stub_runs_as_written():
+    """The binding shown to RocAlphaGo maintainers in INTEGRATION.md section 2 is executed verbatim
+    (only the library path is filled in) and must give what CNNPolicy.batch_eval_state's device
+    part gives."""
+    import re
+    from rocalphago_b200 import build as rb
+    text = open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "INTEGRATION.md")).read()
+    code = re.search(r"```python\n(.*?)```", text, re.S).group(1)
+    code = code.replace(chr(34) + "librocalphago_b200.so" + chr(34), repr(rb.LIB_PATH))
+    ns = {}
+    exec(compile(code, "INTEGRATION.md", "exec"), ns)
+    feats = go_oracle.DEFAULT_FEATURES
+    net = CNNPolicy(feats, layers=12, filters_per_layer=192, dtype="fp16", seed=77)
+    views = BatchedGameState.random_playouts(24, seed=12).views()
+    h = ns["make_net"](net.model.get_weights())
+    got = ns["batch_eval"](h, views, list(range(48)))
+    want = net.model.eval_batch_device(BatchedGameState.from_states(views), net.preprocessor.plane_src).cpu().numpy()
+    assert got.shape == (24, 361) and np.array_equal(got, want)
+    ns["ok"](ns["L"].rag_net_destroy(h))
