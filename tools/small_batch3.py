@@ -16,12 +16,12 @@ def emit_only(self, slot, stream):
     _cabi.check(L.rag_features_emit(_ptr(slot.fws), self.n, self.size, self.plane_src.ctypes.data_as(vp), len(self.plane_src),
                                     LAYOUT_CONV_IN, self.dtype_code, self.channels, _ptr(slot.rows), st))
 def nothing(self, slot, stream): pass
-def run(tag, n, slots=4):
+def run(tag, n, slots=int(os.environ.get('SLOTS', '4'))):
     bs = [BatchedGameState.random_playouts(n, seed=5 + i) for i in range(4)]
     pipe = EvalPipeline(net, n, graphs=False, slots=slots)
     for i in range(16): pipe.submit(bs[i % 4].packed)
     pipe.drain(); torch.cuda.synchronize()
-    K = 200
+    K = int(os.environ.get('K', '200'))
     pipe.trace = []
     t0 = time.time()
     for i in range(K): pipe.submit(bs[i % 4].packed)
@@ -30,7 +30,7 @@ def run(tag, n, slots=4):
     fw = sorted(tr[3].elapsed_time(tr[4]) for tr in pipe.trace)[K // 2]
     ft = sorted(tr[0].elapsed_time(tr[2]) for tr in pipe.trace)[K // 2]
     print("%-28s n=%5d  %.1f us/step  median forward %.3f ms  median feature stage %.3f ms" % (tag, n, t_all / K * 1e6, fw, ft))
-for n in (64, 256, 1024):
+for n in [int(x) for x in os.environ.get('NS', '64,256,1024').split(',')]:
     run("full", n)
     if os.environ.get("ONLY_FULL"): continue
     L.rag_set_ladder_handover(-1); run("no hand-over", n); L.rag_set_ladder_handover(96)
