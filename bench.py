@@ -281,7 +281,7 @@ def run_gpu(args):
     layer_ms /= samples
 
     # ---- end to end with host buffers: pinned packed states -> H2D -> features -> net -> D2H, every step;
-    #      the caller collects each result (on the host) one step behind the submission
+    #      the caller collects each result (on the host) as late as the pipeline allows (slots - 1 steps behind)
     for i in range(2):
         pipe.submit(host_in[i % pool], to_host=True)
     pipe.drain()
@@ -289,11 +289,13 @@ def run_gpu(args):
     t0 = time.time()
     f0 = pipe.mark()
     checksum = 0.0
+    lag = pipe.nslots - 1            # a result stays readable until `slots` later batches have been submitted
     for k in range(K):
         t = pipe.submit(host_in[k % pool], to_host=True)
-        if k > 0:
-            checksum += one(first(pipe.result(t - 1)))
-    checksum += one(first(pipe.result(pipe.count - 1)))
+        if k >= lag:
+            checksum += one(first(pipe.result(t - lag)))
+    for t in range(max(pipe.count - lag, pipe.count - K), pipe.count):
+        checksum += one(first(pipe.result(t)))
     f1 = pipe.mark()
     pipe.drain()
     barrier()
@@ -329,23 +331,30 @@ def run_gpu(args):
         e2e_val = total_pos / (max(e2e_ms, e2e_wall_ms) / 1e3)
         k3 = float(np.mean(layer_ms[1:]))                      # the eleven 3x3 192->192 launches
         achieved = FLOP_3X3 * n / (k3 / 1e3) / 1e12
+        act_mb = n * 361 * 192 * 2 * 2 / 1e6              # the two ping-pong activation buffers every layer reads and writes
+        l2_note = ("no flush needed: every layer of a step reads and writes %.0f MB of activations (%.1fx the 126 MB L2) and the "
+                   "input batches rotate; the --serial pass writes 256 MiB between steps" % (act_mb, act_mb / 126)) if act_mb > 252 else \
+                  ("NOT flushed: a step's activations (%.0f MB) fit the 126 MB L2 at this batch size, as they do for a "
+                   "service running such batches back to back; the headline configuration is batch 4096" % act_mb)
         line = {
             "metric": ("positions/sec: 49-plane features + value CNN fwd, 19x19" if args.workload == "value" else METRIC)
                       if vnet is None else "positions/sec: 48/49-plane features + policy AND value CNN fwd, 19x19",
             "value": value, "unit": "positions/s", "n_gpus": world, "steps": K,
             "warmup": W, "ms_per_step": dev_ms / K, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
-            "config": {"workload": "48 planes (incl. ladders) + 13x192 policy forward, 19x19, batch %d/GPU, "
-                                   "device-generated random-playout positions, random-init weights" % n,
+            "config": {"workload": ("%s, 19x19, batch %d/GPU, device-generated random-playout positions, random-init weights"
+                                    % ({"policy": "48 planes (incl. ladders) + 13x192 policy forward",
+                                        "value": "49 planes (48 incl. ladders + colour) + 13x192 value net forward (Dense 256, tanh)",
+                                        "policy+value": "48/49 planes (one shared analysis) + 13x192 policy AND value forwards"}[args.workload], n)),
                        "batch_per_gpu": n,
                        "schedule": "two-stage pipeline, %d batches in flight: the feature kernels of the next batches run "
                                    "on their own streams underneath the convolutions of the current one "
                                    "(rocalphago_b200/pipeline.py)" % pipe.nslots,
-                       "l2": "no flush needed: each step streams 1.6 GB of activations (13x the 126 MB L2) and the "
-                             "input batches rotate; the --serial pass writes 256 MiB between steps",
+                       "l2": l2_note,
                        "parallelism": "dp%d (independent batches, no collective on the data path)" % world},
             "e2e": {"value": e2e_val, "unit": "positions/s", "h2d_bytes_per_step": int(n * 768),
-                    "d2h_bytes_per_step": int(n * 361 * 4) + (int(n * 4) if vnet is not None else 0), "ms_per_step": max(e2e_ms, e2e_wall_ms) / K,
+                    "d2h_bytes_per_step": (int(n * 4) if args.workload == "value" else int(n * 361 * 4) + (int(n * 4) if vnet is not None else 0)),
+                    "ms_per_step": max(e2e_ms, e2e_wall_ms) / K,
                     "checksum": checksum},
             "gpu_launches": (16 if vnet is None else 30) * K,
             "clocks": clocks,
