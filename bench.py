@@ -407,30 +407,53 @@ def run_features(args):
     L = _cabi.lib()
     pp = Preprocess()
     pool = [BatchedGameState.random_playouts(n, seed=20261106 + 7919 * (rank * 4 + i), device=dev) for i in range(4)]
-    ws = pp._ws.get(n, dev)
-    out = torch.empty((n, 48, 19, 19), dtype=torch.uint8, device=dev)
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    # `lanes` batches in flight, each on its own stream with its own workspace and output buffer: the
+    # tail of one batch's ladder search (a few warps) runs under the bulk of the next batch's
+    lanes = max(1, args.slots or 4)
+    streams = [torch.cuda.Stream(device=dev) for _ in range(lanes)]
+    wss = [torch.empty(int(L.rag_features_workspace_bytes(n)), dtype=torch.uint8, device=dev) for _ in range(lanes)]
+    outs = [torch.empty((n, 48, 19, 19), dtype=torch.uint8, device=dev) for _ in range(lanes)]
+    src = np.ascontiguousarray(pp.plane_src, np.int32)
+    vp = ctypes.c_void_p
 
-    def step(b, ev=None):
-        _cabi.check(L.rag_features_analyze(_ptr(b.packed), n, 19, 1, _ptr(ws), ws.numel(), _stream()))
-        if ev: ev[0].record()
-        pp.emit(ws, n, 19, P.LAYOUT_NCHW_U8, out=out)
-        if ev: ev[1].record()
-    for i in range(W):
-        step(pool[i % 4])
+    def step(b, lane, ev=None):
+        st = vp(streams[lane].cuda_stream)
+        _cabi.check(L.rag_features_analyze(_ptr(b.packed), n, 19, 1, _ptr(wss[lane]), wss[lane].numel(), st))
+        if ev: ev[0].record(streams[lane])
+        _cabi.check(L.rag_features_emit(_ptr(wss[lane]), n, 19, src.ctypes.data_as(vp), len(src), P.LAYOUT_NCHW_U8, 0, 0,
+                                        _ptr(outs[lane]), st))
+        if ev: ev[1].record(streams[lane])
+    for i in range(max(W, lanes)):
+        step(pool[i % 4], i % lanes)
     torch.cuda.synchronize()
     if world > 1: dist.barrier()
     sampler = ClockSampler(local)
     if rank == 0: sampler.start()
     E = lambda: torch.cuda.Event(enable_timing=True)
-    evs = [(E(), E(), E(), E()) for _ in range(K)]
+    evs = [(E(), E()) for _ in range(K)]
+    t0, t1 = E(), E()
+    t0.record()
+    for s_ in streams: s_.wait_event(t0)
     for k in range(K):
-        flush.zero_()
-        evs[k][0].record(); step(pool[k % 4], (evs[k][1], evs[k][2])); evs[k][3].record()
+        step(pool[k % 4], k % lanes, evs[k])
+    for s_ in streams: torch.cuda.current_stream().wait_stream(s_)
+    t1.record()
     torch.cuda.synchronize()
     if world > 1: dist.barrier()
     clocks = sampler.stop() if rank == 0 else None
-    tot = sum(e[0].elapsed_time(e[3]) for e in evs); emit = sum(e[1].elapsed_time(e[2]) for e in evs) / K
+    tot = t0.elapsed_time(t1)
+    # the emit kernel alone (nothing else on the GPU), 256 MiB written before each launch: its roofline figure
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    solo = [(E(), E()) for _ in range(5)]
+    with torch.cuda.stream(streams[0]):
+        for a, b in solo:
+            flush.zero_()
+            a.record(streams[0])
+            _cabi.check(L.rag_features_emit(_ptr(wss[0]), n, 19, src.ctypes.data_as(vp), len(src), P.LAYOUT_NCHW_U8, 0, 0,
+                                            _ptr(outs[0]), vp(streams[0].cuda_stream)))
+            b.record(streams[0])
+    torch.cuda.synchronize()
+    emit = sum(a.elapsed_time(b) for a, b in solo) / len(solo)
     t = torch.tensor([tot], dtype=torch.float64, device=dev)
     if world > 1: dist.all_reduce(t, op=dist.ReduceOp.MAX)
     tot = float(t.cpu())
@@ -443,12 +466,16 @@ def run_features(args):
             "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
             "config": {"workload": "feature-extraction-only sweep (BASELINE config 4): 48 planes incl. ladders -> uint8 NCHW, "
                                    "%d positions/GPU/step, device-generated random playouts" % n,
-                       "l2": "256 MiB buffer written between timed steps"},
+                       "schedule": "%d batches in flight on their own streams" % lanes,
+                       "l2": "no flush needed: every step writes %.0f MB of planes (%.1fx the 126 MB L2) and the input batches rotate"
+                             % (n * 17328 / 1e6, n * 17328 / 126e6)},
             "gpu_launches": 3 * K, "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": "emit_u8_kernel", "achieved": achieved, "peak": peaks["hbm"], "unit": "GB/s",
                          "frac": achieved / peaks["hbm"], "ms_per_launch": emit, "traffic": None,
-                         "peak_source": peaks["src"], "note": "17,568 algorithmic bytes per position (SURVEY 8d)"},
-            "stage_ms": {"analyze_plus_ladders": tot / K - emit, "emit_u8": emit}}))
+                         "peak_source": peaks["src"], "note": "17,568 algorithmic bytes per position (SURVEY 8d); the kernel timed alone after "
+                         "the timed region (inside it, it overlaps other batches' ladder searches); the step itself is bound by "
+                         "the latency of the ladder searches, not by HBM"},
+            "stage_ms": {"step": tot / K, "emit_u8_alone": emit}}))
     if world > 1:
         dist.destroy_process_group()
 

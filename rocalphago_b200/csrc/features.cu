@@ -851,11 +851,13 @@ int rag_features_analyze(const uint32_t* d_states, int n, int size, int with_lad
         int dev = 0, sms = 148;
         RAG_CUDA_CHECK(cudaGetDevice(&dev));
         RAG_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-        // Persistent warps, each looping until the queue is drained.  4 CTAs (16 warps, half the
-        // register file) per SM at most: the searches are latency-bound, so more warps buy little,
-        // and a convolution CTA of another stream (conv.cu) must still fit beside them.
+        // Persistent warps, each looping until the queue is drained.  This one-call path has the
+        // SMs to itself: 8 CTAs (32 warps) per SM, measured 3 % faster than 4.  (The pipeline's
+        // separate stage, rag_features_ladders, stays at 4 so that a convolution CTA of another
+        // stream still finds registers beside it.)
+        const int cap = 8;
         long long want = ((long long)n * 16 + kWarpsPerBlock - 1) / kWarpsPerBlock;
-        int blocks = (int)(want < (long long)sms * 4 ? (want < 1 ? 1 : want) : (long long)sms * 4);
+        int blocks = (int)(want < (long long)sms * cap ? (want < 1 ? 1 : want) : (long long)sms * cap);
         ladder_kernel<0><<<blocks, kWarpsPerBlock * 32, 0, s>>>(d_states, size, g_steal_after, g_helper_ctas, ws);
         RAG_CUDA_CHECK(cudaGetLastError());
     }
