@@ -77,7 +77,7 @@ class Preprocess(object):
         for i in range(len(feature_list)):
             feat = feature_list[i].lower()
             if feat in FEATURES:
-                self.processors[i] = feat
+                self.processors[i] = FEATURES[feat].get("function", feat)
                 self.output_dim += FEATURES[feat]["size"]
                 src += list(range(FEATURES[feat]["plane"], FEATURES[feat]["plane"] + FEATURES[feat]["size"]))
             else:
@@ -152,3 +152,89 @@ class Preprocess(object):
         """Convert a GameState to a Theano-compatible tensor: (1, F, S, S) float64 of 0/1
         (preprocessing.py:287-294)."""
         return self.states_to_tensor([state]).astype(np.float64)
+
+
+# ---- the reference's module-level feature functions (preprocessing.py:14-205) ----------------------
+#
+# Each returns the float (k, S, S) planes of ONE feature for one state, as the reference's functions of
+# the same names do; FEATURES[name]["function"] and Preprocess.processors point at them.  They run the
+# same kernels as Preprocess (one position, one feature), so they are for compatibility, not speed.
+
+_SINGLE = {}
+
+
+def _feature(state, name):
+    if name not in _SINGLE:
+        _SINGLE[name] = Preprocess([name])
+    return _SINGLE[name].state_to_tensor(state)[0].astype(np.float64)
+
+
+def _capped(state, name, maximum):
+    """One-hot planes saturating at `maximum` instead of 8: plane min(v, maximum - 1).  The kernels
+    saturate at 8 planes, so 1 <= maximum <= 8 can be folded from them; more cannot."""
+    if not 1 <= maximum <= 8:
+        raise ValueError("maximum must be in [1, 8] on this path (got %d)" % maximum)
+    planes = _feature(state, name)
+    out = planes[:maximum].copy()
+    out[maximum - 1] = planes[maximum - 1:].max(axis=0)
+    return out
+
+
+def get_board(state):
+    """own stones, opponent stones, empty points (preprocessing.py:14-22)"""
+    return _feature(state, "board")
+
+
+def get_turns_since(state, maximum=8):
+    """one-hot age of every stone, saturating (preprocessing.py:25-37)"""
+    return _capped(state, "turns_since", maximum)
+
+
+def get_liberties(state, maximum=8):
+    """one-hot liberty count of every stone's group (preprocessing.py:40-56)"""
+    return _capped(state, "liberties", maximum)
+
+
+def get_capture_size(state, maximum=8):
+    """stones captured by playing at each legal point (preprocessing.py:59-86)"""
+    return _capped(state, "capture_size", maximum)
+
+
+def get_self_atari_size(state, maximum=8):
+    """size of the own group put into atari by playing at each legal point (preprocessing.py:89-126)"""
+    return _capped(state, "self_atari_size", maximum)
+
+
+def get_liberties_after(state, maximum=8):
+    """liberties of the played stone's group after each legal move (preprocessing.py:129-169)"""
+    return _capped(state, "liberties_after", maximum)
+
+
+def get_ladder_capture(state):
+    """legal moves that capture in a ladder (preprocessing.py:172-178)"""
+    return _feature(state, "ladder_capture")
+
+
+def get_ladder_escape(state):
+    """legal moves that escape a ladder (preprocessing.py:181-187)"""
+    return _feature(state, "ladder_escape")
+
+
+def get_sensibleness(state):
+    """legal moves that do not fill an own eye (preprocessing.py:190-196)"""
+    return _feature(state, "sensibleness")
+
+
+def get_legal(state):
+    """legal moves, own eyes included (preprocessing.py:199-205)"""
+    return _feature(state, "legal")
+
+
+for _name, _fn in (("board", get_board), ("turns_since", get_turns_since), ("liberties", get_liberties),
+                   ("capture_size", get_capture_size), ("self_atari_size", get_self_atari_size),
+                   ("liberties_after", get_liberties_after), ("ladder_capture", get_ladder_capture),
+                   ("ladder_escape", get_ladder_escape), ("sensibleness", get_sensibleness), ("legal", get_legal),
+                   ("ones", lambda state: np.ones((1, state.size, state.size))),
+                   ("zeros", lambda state: np.zeros((1, state.size, state.size))),
+                   ("color", lambda state: _feature(state, "color"))):
+    FEATURES[_name]["function"] = _fn

@@ -1,6 +1,7 @@
 """Parity of the CUDA feature path (through the C ABI) with the reference: bit-exact planes
 against the golden fixtures recorded from the reference, and against the C oracle on fresh
 random playouts at sizes the fixtures cannot hold.  Run on the B200 box: pytest -m gpu."""
+import os
 import numpy as np
 import pytest
 import torch
@@ -183,3 +184,32 @@ def test_ladder_planes_do_not_depend_on_reply_handover(handover, helpers):
     finally:
         L.rag_set_ladder_handover(old)
         L.rag_set_ladder_helpers(old_helpers)
+
+
+def test_module_level_feature_functions_and_their_maximum_argument():
+    """get_board ... get_legal (preprocessing.py:14-205) keep their names and signatures; the
+    `maximum` argument folds the saturating planes exactly as the reference does (golden vectors made
+    by calling the reference's functions with maximum in {1, 3, 5, 8}, oracle/make_golden_maximum.py)."""
+    from rocalphago_b200 import preprocessing as P
+    g = gu.load_features("features_sgf.npz")
+    z = np.load(os.path.join(gu.GOLDEN, "feature_functions_maximum.npz"))
+    rows = [int(r) for r in z["rows"]]
+    views = [PositionView(g["board"][i], g["age"][i], int(g["ko"][i]), int(g["player"][i])) for i in rows]
+    for name in [str(s) for s in z["names"]]:
+        fn = getattr(P, "get_" + name)
+        assert P.FEATURES[name]["function"] is fn
+        for m in [int(v) for v in z["maxima"]]:
+            want = np.unpackbits(z["%s_%d" % (name, m)])[:len(rows) * m * 361].reshape(len(rows), m, 19, 19)
+            for k, v in enumerate(views[::6]):
+                got = fn(v, maximum=m)
+                assert got.shape == (m, 19, 19) and got.dtype == np.float64
+                assert np.array_equal(got, want[6 * k]), (name, m, k)
+        with pytest.raises(ValueError):
+            fn(views[0], maximum=9)
+    v, i = views[3], rows[3]
+    for name, lo in (("board", 0), ("ladder_capture", 44), ("ladder_escape", 45), ("sensibleness", 46), ("legal", 48)):
+        got = getattr(P, "get_" + name)(v)
+        assert np.array_equal(got, g["planes"][i, lo:lo + P.FEATURES[name]["size"]]), name
+    assert np.array_equal(P.FEATURES["ones"]["function"](v), np.ones((1, 19, 19)))
+    assert np.array_equal(P.FEATURES["zeros"]["function"](v), np.zeros((1, 19, 19)))
+    assert P.Preprocess(["board", "liberties"]).processors == [P.get_board, P.get_liberties]
