@@ -147,3 +147,50 @@ def ladder_query(board, ko, player, action, prey=-1, escape=False):
     size = board.shape[-1]
     return bool(lib().og_ladder_query(size, board.reshape(-1), int(ko), int(player), int(action),
                                       int(prey), int(bool(escape))))
+
+
+# ---- superko (go.py:242-265): states created with enforce_superko=True ---------------------------
+
+def zobrist_table(size):
+    """hash_lookup of go.py:58-62 as one array [2][size*size]: [0] BLACK, [1] WHITE.  The reference
+    draws WHITE's table first from RandomState(0)."""
+    rng = np.random.RandomState(0)
+    white = rng.randint(np.iinfo(np.uint64).max, size=(size, size), dtype="uint64")
+    black = rng.randint(np.iinfo(np.uint64).max, size=(size, size), dtype="uint64")
+    return np.ascontiguousarray(np.stack([black.reshape(-1), white.reshape(-1)]))
+
+
+def features_superko(board, age, ko, player, sk, feature_list=DEFAULT_FEATURES, with_moves=False):
+    """As `features`, for states that enforce positional superko.  sk: dict with enforce (n,),
+    has_handicap (n,), hist_len (n,), hash (n,) uint64, prev (flat uint64), prev_off (n+1,),
+    masks (n, 3, S*S) uint8 = points in history[0::2] / history[1::2] / handicaps."""
+    n, size, board, age, ko, player = _canon(board, age, ko, player)
+    ids = np.asarray([FEATURE_IDS[f.lower()] for f in feature_list], dtype=np.int32)
+    F = int(sum(lib().og_feature_planes(int(i)) for i in ids))
+    out = np.empty((n, F, size, size), dtype=np.uint8)
+    L = lib()
+    if not getattr(L, "_sk_ready", False):
+        u64p = np.ctypeslib.ndpointer(np.uint64, flags="C")
+        i32p = np.ctypeslib.ndpointer(np.int32, flags="C")
+        i16p = np.ctypeslib.ndpointer(np.int16, flags="C")
+        i8p = np.ctypeslib.ndpointer(np.int8, flags="C")
+        u8p = np.ctypeslib.ndpointer(np.uint8, flags="C")
+        L.og_features_superko.restype = ctypes.c_int
+        L.og_features_superko.argtypes = [ctypes.c_int, ctypes.c_int, i8p, i16p, i32p, i32p, i32p, ctypes.c_int, u8p,
+                                          u64p, i32p, i32p, i32p, u64p, u64p, i32p, u8p, ctypes.c_void_p, ctypes.c_void_p]
+        L._sk_ready = True
+    c = lambda a, t: np.ascontiguousarray(a, dtype=t)  # noqa: E731
+    prev = c(sk["prev"], np.uint64)
+    if prev.size == 0:
+        prev = np.zeros(1, np.uint64)
+    moves = np.full((n, size * size), -1, np.int16)
+    counts = np.zeros((n, 2), np.int32)
+    got = L.og_features_superko(n, size, board, age, ko, player, ids, len(ids), out.reshape(-1), zobrist_table(size).reshape(-1),
+                                c(sk["enforce"], np.int32), c(sk["has_handicap"], np.int32), c(sk["hist_len"], np.int32),
+                                c(sk["hash"], np.uint64), prev, c(sk["prev_off"], np.int32),
+                                c(sk["masks"], np.uint8).reshape(-1), moves.ctypes.data_as(ctypes.c_void_p),
+                                counts.ctypes.data_as(ctypes.c_void_p))
+    assert got == F, got
+    if with_moves:
+        return out, [moves[i, :counts[i, 0]].astype(np.int64) for i in range(n)], counts[:, 1].copy()
+    return out

@@ -42,3 +42,20 @@ def load_kat():
 def load_replay():
     z = np.load(os.path.join(GOLDEN, "replay_sgf.npz"))
     return {k: z[k] for k in z.files}
+
+
+def load_superko():
+    """tests/golden/features_superko.npz (oracle/make_golden_superko.py): per set of positions recorded
+    from reference games played with enforce_superko=True -> dict of arrays + the reference's planes."""
+    z = np.load(os.path.join(GOLDEN, "features_superko.npz"))
+    feats = [str(f) for f in z["feature_list"]]
+    out = {}
+    for key in [str(k) for k in z["sets"]]:
+        g = {name: z["%s_%s" % (name, key)] for name in ("board", "age", "ko", "player", "hash", "prev", "prev_off", "masks",
+                                                        "hist_len", "has_handicap", "moves")}
+        shape = tuple(int(v) for v in z["planes_shape_%s" % key])
+        g["planes"] = np.unpackbits(z["planes_%s" % key])[:int(np.prod(shape))].reshape(shape)
+        g["sk"] = dict(enforce=np.ones(shape[0], np.int32), has_handicap=g["has_handicap"], hist_len=g["hist_len"],
+                       hash=g["hash"], prev=g["prev"], prev_off=g["prev_off"], masks=g["masks"])
+        out[key] = g
+    return feats, out

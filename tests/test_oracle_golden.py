@@ -102,3 +102,23 @@ def test_playout_generator_positions_are_consistent():
             assert f[i, 0].reshape(-1)[mv[i]] == 1
     assert (ko >= 0).sum() >= 0
     assert set(np.unique(pl)) <= {-1, 1}
+
+
+def test_oracle_superko_matches_reference_games_played_with_enforce_superko():
+    """go.py:242-265, 282-283: 5,300 positions from reference games with enforce_superko=True (tiny
+    boards, where positions recur constantly, plus handicap games and the reference's own scenario of
+    tests/test_gamestate.py:60-77): all 49 planes and the legal-move lists; superko changes the planes
+    of 170 of them, the ladder planes of 58."""
+    feats, sets = gu.load_superko()
+    changed = ladder_changed = 0
+    for key, g in sets.items():
+        got, moves, _ = go_oracle.features_superko(g["board"], g["age"], g["ko"], g["player"], g["sk"], feats, with_moves=True)
+        assert np.array_equal(got, g["planes"]), key
+        for i in range(len(moves)):
+            assert np.array_equal(moves[i], g["moves"][i][g["moves"][i] >= 0]), (key, i)
+        plain = go_oracle.features(g["board"], g["age"], g["ko"], g["player"], feats)
+        changed += int((plain != g["planes"]).reshape(len(plain), -1).any(1).sum())
+        ladder_changed += int((plain[:, 44:46] != g["planes"][:, 44:46]).reshape(len(plain), -1).any(1).sum())
+        off = dict(g["sk"], enforce=np.zeros(len(plain), np.int32))
+        assert np.array_equal(go_oracle.features_superko(g["board"], g["age"], g["ko"], g["player"], off, feats), plain)
+    assert changed >= 150 and ladder_changed >= 40
