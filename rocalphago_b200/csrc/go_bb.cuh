@@ -399,8 +399,9 @@ RAG_FN_NOINLINE void bb_moves(const Geo& g, BB own, BB opp, int ko_q, EyeStack& 
 // masks the ladder reader starts from.  `planes` = kNumPlanes x 32 words, zeroed by the caller.
 // own/opp are relative to the side to move (preprocessing.py:19-20); age0..2 = bits of
 // min(stone_ages, 7) (preprocessing.py:33-36); ko_q = q-index of the ko point or -1.
+// `forbid`: points that are illegal for a reason this function cannot see (positional superko).
 RAG_FN_NOINLINE Analysis bb_features(const Geo& g, BB own, BB opp, BB age0, BB age1, BB age2, int ko_q,
-                                     uint32_t* planes, EyeStack& est) {
+                                     uint32_t* planes, EyeStack& est, BB forbid) {
     Analysis A;
     const BB board = bb_board(g);
     const BB stones = own | opp;
@@ -429,7 +430,7 @@ RAG_FN_NOINLINE Analysis bb_features(const Geo& g, BB own, BB opp, BB age0, BB a
     A.opp_atari = opp & lib1;
     A.opp_lib2 = opp & lib2;
 
-    BB legal = bb_legal(g, own, empty, A.own_atari, A.opp_atari, ko_q);
+    BB legal = andnot(bb_legal(g, own, empty, A.own_atari, A.opp_atari, ko_q), forbid);
     A.legal = legal;
     plane_or(planes, kPlaneLegal, legal, g);
 
@@ -542,6 +543,9 @@ static void (*g_ladder_node_hook)(const uint32_t* h32, const uint32_t* p32, int 
 //   escape node  (go.py:413-460): prey plays; >=3 liberties -> 1, 1 liberty -> 0, else
 //       replies = the two liberties; value = no reply is a ladder capture.
 // `remaining` is the reference's remaining_attempts; legality is tested before it (H11).
+RAG_FN int ladder_expand_played(const Geo& g, bool is_capture, BB& H, BB& P, BB& G, int mv, int remaining,
+                                BB& pending, BB ptn);
+
 RAG_FN int ladder_expand(const Geo& g, bool is_capture, BB& H, BB& P, BB& G, int& ko, int mv,
                          int remaining, BB& pending) {
     RAG_LADDER_COUNT_NODE();
@@ -551,6 +555,12 @@ RAG_FN int ladder_expand(const Geo& g, bool is_capture, BB& H, BB& P, BB& G, int
     BB ptn;
     bool ok = is_capture ? bb_play_ex(g, H, P, ko, mv, nullptr, ptn) : bb_play_ex(g, P, H, ko, mv, nullptr, ptn);
     if (!ok) return kLadderValue0;
+    return ladder_expand_played(g, is_capture, H, P, G, mv, remaining, pending, ptn);
+}
+
+// The part of ladder_expand after the (legal) move `mv` has been played; `ptn` = its neighbours.
+RAG_FN int ladder_expand_played(const Geo& g, bool is_capture, BB& H, BB& P, BB& G, int mv, int remaining,
+                                BB& pending, BB ptn) {
     if (remaining <= 0) return is_capture ? kLadderValue1 : kLadderValue0;
     const BB empty = andnot(bb_board(g), H | P);
     if (!is_capture) {
@@ -692,6 +702,157 @@ RAG_FN_NOINLINE int ladder_root(const Geo& g, BB own, BB opp, int ko, int action
         if (r != kLadderValue0) return r;
     }
     return kLadderValue0;
+}
+
+// ------------------------------------------------------------------ positional superko  (go.py:242-265)
+//
+// Only for states created with enforce_superko=True (the GTP front end).  is_legal then also asks
+// is_positional_superko: if the point was played before by the side to move (by the parity of its
+// index in `history`) or is a handicap point, play it on a copy and look the resulting Zobrist hash
+// up in previous_hashes.  copy() carries hash, hash set and history along (go.py:193-199), so the
+// ladder reader's look-ahead enforces it too, against the hashes of its own path as well.
+
+typedef unsigned long long u64;
+
+struct SuperkoRoot {                // constant during one search
+    const u64* zob;                 // hash_lookup by q-index: [0][1024] BLACK, [1][1024] WHITE  (go.py:58-62)
+    const u64* prev;                // previous_hashes of the position
+    int nprev;
+    BB handi;                       // handicaps
+    bool has_handicap;
+};
+
+struct SuperkoCtx {                 // of one state (the position, or a node of a ladder search)
+    u64 hash;                       // current_hash
+    BB even, odd;                   // points of history[0::2] / history[1::2]
+    int hist_len;                   // len(history)
+};
+
+// XOR of table[q] over the points of `stones`
+RAG_FN u64 bb_zobrist(const Geo& g, BB stones, const u64* table) {
+#if RAG_DEVICE_BUILD
+    u64 h = 0;
+    for (uint32_t w = stones.w; w; w &= w - 1) h ^= table[(g.lane << 5) | (uint32_t)(__ffs(w) - 1)];
+    const uint32_t lo = __reduce_xor_sync(kFullMask, (uint32_t)h), hi = __reduce_xor_sync(kFullMask, (uint32_t)(h >> 32));
+    return ((u64)hi << 32) | lo;
+#else
+    u64 h = 0;
+    for (int x = 0; x < 32; x++)
+        for (uint32_t w = stones.w[x]; w; w &= w - 1) h ^= table[(x << 5) | __builtin_ctz(w)];
+    (void)g;
+    return h;
+#endif
+}
+
+// h in previous_hashes of a state whose own moves so far produced path[0 .. npath) ?
+RAG_FN bool sk_seen(const Geo& g, const SuperkoRoot& r, u64 h, const u64* path, int npath) {
+#if RAG_DEVICE_BUILD
+    bool hit = false;
+    for (int i = (int)g.lane; i < r.nprev; i += 32) hit |= r.prev[i] == h;
+    for (int i = (int)g.lane; i < npath; i += 32) hit |= path[i] == h;
+    return __any_sync(kFullMask, hit) != 0;
+#else
+    (void)g;
+    for (int i = 0; i < r.nprev; i++) if (r.prev[i] == h) return true;
+    for (int i = 0; i < npath; i++) if (path[i] == h) return true;
+    return false;
+#endif
+}
+
+// the points is_positional_superko looks at for the side to move (go.py:248-256)
+RAG_FN BB sk_mine(const SuperkoRoot& r, const SuperkoCtx& c, bool mover_is_black) {
+    const bool first_slice = r.has_handicap ? !mover_is_black : mover_is_black;
+    return r.handi | (first_slice ? c.even : c.odd);
+}
+
+// Moves of the side to move (stones M, colour given) that is_legal rejects for superko alone.
+RAG_FN_NOINLINE BB sk_forbidden_moves(const Geo& g, const SuperkoRoot& r, const SuperkoCtx& c, BB M, BB O, int ko_q,
+                                      bool mover_is_black) {
+    BB out = bb_zero();
+    BB rem = andnot(sk_mine(r, c, mover_is_black), M | O);
+    for (;;) {
+        const int q = bb_first(rem);
+        if (q < 0) break;
+        const BB pt = bb_single(q, g);
+        rem = andnot(rem, pt);
+        BB M2 = M, O2 = O;
+        int k2 = ko_q, ncap = 0;
+        if (!bb_play(g, M2, O2, k2, q, &ncap)) continue;              // illegal anyway
+        u64 h = c.hash ^ r.zob[(mover_is_black ? 0 : 1024) + q];
+        if (ncap) h ^= bb_zobrist(g, andnot(O, O2), r.zob + (mover_is_black ? 1024 : 0));
+        if (sk_seen(g, r, h, nullptr, 0)) out = out | pt;
+    }
+    return out;
+}
+
+struct LadderStackSk {
+    LadderStack base;
+    u64 hash[kLadderDepth];
+    BB even[kLadderDepth], odd[kLadderDepth];
+    u64 path[kLadderDepth + 2];     // hashes after each move of the current line
+};
+
+// ladder_expand for a state that enforces superko: `c` is the state's bookkeeping before the move and
+// becomes the child's; `h_out` is the hash after the move.
+RAG_FN int ladder_expand_sk(const Geo& g, bool is_capture, BB& H, BB& P, BB& G, int& ko, int mv, int remaining,
+                            BB& pending, const SuperkoRoot& r, SuperkoCtx& c, bool hunter_is_black,
+                            const u64* path, int npath) {
+    RAG_LADDER_COUNT_NODE();
+    const BB Hb = H, Pb = P;
+    BB ptn;
+    int ncap = 0;
+    const bool ok = is_capture ? bb_play_ex(g, H, P, ko, mv, &ncap, ptn) : bb_play_ex(g, P, H, ko, mv, &ncap, ptn);
+    if (!ok) return kLadderValue0;
+    const bool mover_is_black = is_capture ? hunter_is_black : !hunter_is_black;
+    u64 h = c.hash ^ r.zob[(mover_is_black ? 0 : 1024) + mv];
+    if (ncap) h ^= bb_zobrist(g, is_capture ? andnot(Pb, P) : andnot(Hb, H), r.zob + (mover_is_black ? 1024 : 0));
+    if (bb_test(sk_mine(r, c, mover_is_black), mv) && sk_seen(g, r, h, path, npath)) return kLadderValue0;   // go.py:282-283
+    c.hash = h;
+    if (c.hist_len & 1) c.odd = c.odd | bb_single(mv, g); else c.even = c.even | bb_single(mv, g);
+    c.hist_len++;
+    return ladder_expand_played(g, is_capture, H, P, G, mv, remaining, pending, ptn);
+}
+
+// ladder_search + ladder_dfs with the superko bookkeeping carried per frame.
+RAG_FN_NOINLINE int ladder_search_sk(const Geo& g, BB H, BB P, BB G, int ko, int first_move, bool root_is_capture,
+                                     int remaining0, const SuperkoRoot& r, SuperkoCtx c, bool hunter_is_black,
+                                     LadderStackSk& sk) {
+    LadderStack& st = sk.base;
+    BB pending = bb_zero();
+    int res = ladder_expand_sk(g, root_is_capture, H, P, G, ko, first_move, remaining0, pending, r, c, hunter_is_black, sk.path, 0);
+    if (res != kLadderPush) return res;
+    const int remaining_children = remaining0 - 1;
+    int d = 0;
+    st.hunter[0] = H; st.prey[0] = P; st.group[0] = G; st.pending[0] = pending; st.ko[0] = (int16_t)ko;
+    sk.hash[0] = c.hash; sk.even[0] = c.even; sk.odd[0] = c.odd; sk.path[0] = c.hash;
+    const int len0 = c.hist_len;                         // len(history) of frame 0's state
+    for (;;) {
+        int v;
+        const int m = bb_first(st.pending[d]);
+        if (m < 0) v = 1;
+        else {
+            st.pending[d] = andnot(st.pending[d], bb_single(m, g));
+            const bool node_is_capture = root_is_capture ^ ((d & 1) != 0);
+            H = st.hunter[d]; P = st.prey[d]; G = st.group[d]; ko = st.ko[d];
+            c.hash = sk.hash[d]; c.even = sk.even[d]; c.odd = sk.odd[d]; c.hist_len = len0 + d;
+            res = ladder_expand_sk(g, !node_is_capture, H, P, G, ko, m, remaining_children - d, pending, r, c,
+                                   hunter_is_black, sk.path, d + 1);
+            if (res == kLadderPush) {
+                d++;
+                st.hunter[d] = H; st.prey[d] = P; st.group[d] = G; st.pending[d] = pending; st.ko[d] = (int16_t)ko;
+                sk.hash[d] = c.hash; sk.even[d] = c.even; sk.odd[d] = c.odd; sk.path[d] = c.hash;
+                continue;
+            }
+            if (res == kLadderValue0) continue;
+            v = 0;
+        }
+        for (;;) {
+            if (d == 0) return v;
+            d--;
+            if (v == 0) break;
+            v = 0;
+        }
+    }
 }
 
 }  // namespace rag

@@ -42,3 +42,23 @@ def features49(board, age, ko, player, item_cap=0):
     if item_cap:
         return out, stats, items[:min(item_cap, int(stats[3]))]
     return out, stats
+
+
+def features49_superko(board, age, ko, player, sk, zobrist):
+    """The same for states that enforce positional superko; `sk` as oracle.go_oracle.features_superko
+    takes it, `zobrist` = go_oracle.zobrist_table(size)."""
+    board = np.ascontiguousarray(board, np.int8)
+    n, S = board.shape[0], board.shape[-1]
+    out = np.empty((n, 49, S, S), np.uint8)
+    L = lib()
+    vp = ctypes.c_void_p
+    L.hostsim_features_superko.restype = ctypes.c_int
+    L.hostsim_features_superko.argtypes = [ctypes.c_int, ctypes.c_int] + [vp] * 12
+    keep = [board.reshape(n, -1), np.ascontiguousarray(age, np.int16).reshape(n, -1), np.ascontiguousarray(ko, np.int32),
+            np.ascontiguousarray(player, np.int32), out, np.ascontiguousarray(zobrist, np.uint64),
+            np.ascontiguousarray(sk["has_handicap"], np.int32), np.ascontiguousarray(sk["hist_len"], np.int32),
+            np.ascontiguousarray(sk["hash"], np.uint64),
+            np.ascontiguousarray(sk["prev"] if len(sk["prev"]) else np.zeros(1), np.uint64),
+            np.ascontiguousarray(sk["prev_off"], np.int32), np.ascontiguousarray(sk["masks"], np.uint8)]
+    L.hostsim_features_superko(n, S, *[a.ctypes.data_as(vp) for a in keep])
+    return out

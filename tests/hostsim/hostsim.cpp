@@ -38,7 +38,7 @@ extern "C" int hostsim_features(int n, int S, const int8_t* board, const int16_t
         int ko_q = ko[b] < 0 ? -1 : ((ko[b] / S) << 5) | (ko[b] % S);
         uint32_t planes[kNumPlanes * 32];
         memset(planes, 0, sizeof planes);
-        Analysis A = bb_features(g, own, opp, a0, a1, a2, ko_q, planes, *est);
+        Analysis A = bb_features(g, own, opp, a0, a1, a2, ko_q, planes, *est, bb_zero());
         BB cand_cap = A.legal & bb_nbrs(A.opp_lib2, g);
         BB cand_esc = A.legal & bb_nbrs(A.own_atari, g);
         if (stats) { stats[0] += bb_count(cand_cap); stats[1] += bb_count(cand_esc); }
@@ -65,6 +65,75 @@ extern "C" int hostsim_features(int n, int S, const int8_t* board, const int16_t
                 for (int y = 0; y < S; y++) o[k * np + x * S + y] = (planes[k * 32 + x] >> y) & 1u;
     }
     free(est); free(lst);
+    return 0;
+}
+
+// The same with positional superko enforced (go.py:242-265): per position the Zobrist hash, the
+// earlier hashes and the history masks, as og_features_superko takes them.  zob: [2][S*S], [0] BLACK.
+extern "C" int hostsim_features_superko(int n, int S, const int8_t* board, const int16_t* age, const int32_t* ko,
+                                        const int32_t* player, uint8_t* out, const uint64_t* zob_p,
+                                        const int32_t* has_handicap, const int32_t* hist_len, const uint64_t* hash,
+                                        const uint64_t* prev, const int32_t* prev_off, const uint8_t* masks)
+{
+    const int np = S * S;
+    Geo g = make_geo(S);
+    EyeStack* est = (EyeStack*)malloc(sizeof(EyeStack));
+    LadderStackSk* lst = (LadderStackSk*)malloc(sizeof(LadderStackSk));
+    u64* zob = (u64*)calloc(2048, sizeof(u64));
+    for (int c = 0; c < 2; c++)
+        for (int x = 0; x < S; x++)
+            for (int y = 0; y < S; y++) zob[c * 1024 + (x << 5) + y] = zob_p[(size_t)c * np + x * S + y];
+    for (int b = 0; b < n; b++) {
+        BB own = bb_zero(), opp = bb_zero(), a0 = bb_zero(), a1 = bb_zero(), a2 = bb_zero();
+        SuperkoRoot r; SuperkoCtx c;
+        r.handi = bb_zero(); c.even = bb_zero(); c.odd = bb_zero();
+        for (int x = 0; x < S; x++)
+            for (int y = 0; y < S; y++) {
+                const size_t p = (size_t)b * np + x * S + y;
+                if (masks[((size_t)b * 3 + 0) * np + x * S + y]) c.even.w[x] |= 1u << y;
+                if (masks[((size_t)b * 3 + 1) * np + x * S + y]) c.odd.w[x] |= 1u << y;
+                if (masks[((size_t)b * 3 + 2) * np + x * S + y]) r.handi.w[x] |= 1u << y;
+                int v = board[p];
+                if (v == 0) continue;
+                if (v == player[b]) own.w[x] |= 1u << y; else opp.w[x] |= 1u << y;
+                int ag = age[p];
+                if (ag > 7) ag = 7;
+                if (ag < 0) ag = 0;
+                if (ag & 1) a0.w[x] |= 1u << y;
+                if (ag & 2) a1.w[x] |= 1u << y;
+                if (ag & 4) a2.w[x] |= 1u << y;
+            }
+        r.zob = zob; r.prev = (const u64*)prev + prev_off[b]; r.nprev = prev_off[b + 1] - prev_off[b];
+        r.has_handicap = has_handicap[b] != 0;
+        c.hash = hash[b]; c.hist_len = hist_len[b];
+        const bool black = player[b] > 0;
+        int ko_q = ko[b] < 0 ? -1 : ((ko[b] / S) << 5) | (ko[b] % S);
+        uint32_t planes[kNumPlanes * 32];
+        memset(planes, 0, sizeof planes);
+        const BB forbid = sk_forbidden_moves(g, r, c, own, opp, ko_q, black);
+        Analysis A = bb_features(g, own, opp, a0, a1, a2, ko_q, planes, *est, forbid);
+        BB cand[2] = { A.legal & bb_nbrs(A.opp_lib2, g), A.legal & bb_nbrs(A.own_atari, g) };
+        for (int kind = 0; kind < 2; kind++) {
+            BB rem = cand[kind];
+            for (;;) {
+                int q = bb_first(rem);
+                if (q < 0) break;
+                rem = andnot(rem, bb_single(q, g));
+                BB preys[4];
+                const int npreys = ladder_root_preys(g, own, opp, q, kind == 1, preys);
+                int res = kLadderValue0;
+                for (int i = 0; i < npreys && res == kLadderValue0; i++)
+                    res = kind == 1 ? ladder_search_sk(g, opp, own, preys[i], ko_q, q, false, kLadderDepth, r, c, !black, *lst)
+                                    : ladder_search_sk(g, own, opp, preys[i], ko_q, q, true, kLadderDepth, r, c, black, *lst);
+                if (res == kLadderValue1) planes[(kind ? kPlaneLadderEscape : kPlaneLadderCapture) * 32 + (q >> 5)] |= 1u << (q & 31);
+            }
+        }
+        uint8_t* o = out + (size_t)b * 49 * np;
+        for (int k = 0; k < 49; k++)
+            for (int x = 0; x < S; x++)
+                for (int y = 0; y < S; y++) o[k * np + x * S + y] = (planes[k * 32 + x] >> y) & 1u;
+    }
+    free(est); free(lst); free(zob);
     return 0;
 }
 

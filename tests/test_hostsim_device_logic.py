@@ -30,3 +30,14 @@ def test_device_logic_matches_oracle_on_playouts(size, n, seed):
     want = go_oracle.features(b, a, ko, pl, ALL)
     got, stats = hostsim.features49(b, a, ko, pl)
     assert np.array_equal(got, want), _explain(got, want)
+
+
+def test_device_logic_with_superko_matches_reference_golden():
+    """sk_forbidden_moves + ladder_search_sk (csrc/go_bb.cuh) on the positions recorded from reference
+    games played with enforce_superko=True."""
+    feats, sets = gu.load_superko()
+    assert feats == ALL
+    for key, g in sets.items():
+        size = g["board"].shape[-1]
+        got = hostsim.features49_superko(g["board"], g["age"], g["ko"], g["player"], g["sk"], go_oracle.zobrist_table(size))
+        assert np.array_equal(got, g["planes"]), (key, _explain(got, g["planes"]))
