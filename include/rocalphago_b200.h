@@ -108,6 +108,29 @@ int rag_set_ladder_handover(int moves);
  * previous value. */
 int rag_set_ladder_helpers(int ctas);
 
+/* Positional superko (go.py:242-265, 282-283) for states created with enforce_superko=True: what
+ * is_positional_superko reads, per position, in device memory.  q = x*32 + y.
+ *   d_zobrist  uint64 [2][1024]: hash_lookup by q, [0] BLACK, [1] WHITE           (go.py:58-62)
+ *   d_hash     uint64 [n]: current_hash                                            (go.py:63)
+ *   d_prev     uint64 [..]: previous_hashes of all positions, position b's in
+ *              [d_prev_off[b], d_prev_off[b+1]);  d_prev_off int32 [n+1]          (go.py:64)
+ *   d_masks    uint32 [n][3][32] row words (as in a packed state): the points of history[0::2],
+ *              of history[1::2], and of handicaps                                 (go.py:248-256)
+ *   d_flags    int32 [n]: bit 0 enforce_superko, bit 1 len(handicaps) > 0, bits 8.. len(history)
+ * rag_features_analyze_superko is rag_features_analyze(with_ladders = 0 or 1) with these rules added:
+ * superko-forbidden moves are illegal in every plane and move list, and the ladder look-ahead
+ * enforces superko on its own line as GameState.copy() makes the reference do (go.py:193-199). */
+typedef struct rag_superko {
+    const uint64_t* d_zobrist;
+    const uint64_t* d_hash;
+    const uint64_t* d_prev;
+    const int32_t*  d_prev_off;
+    const uint32_t* d_masks;
+    const int32_t*  d_flags;
+} rag_superko;
+int rag_features_analyze_superko(const uint32_t* d_states, int n, int size, int with_ladders, const rag_superko* sk,
+                                 void* d_workspace, size_t workspace_bytes, void* stream);
+
 /* Step 1b: the ladder reader over the candidates queued by rag_features_analyze(with_ladders = 2). */
 int rag_features_ladders(const uint32_t* d_states, int n, int size, void* d_workspace,
                          size_t workspace_bytes, void* stream);

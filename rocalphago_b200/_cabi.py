@@ -24,6 +24,11 @@ def _declared_symbols():
     return sorted(set(re.findall(r"\b(rag_[a-z0-9_]+)\s*\(", text)))
 
 
+class RagSuperko(ctypes.Structure):
+    """rag_superko (include/rocalphago_b200.h)"""
+    _fields_ = [(name, ctypes.c_void_p) for name in ("d_zobrist", "d_hash", "d_prev", "d_prev_off", "d_masks", "d_flags")]
+
+
 def lib():
     global _lib
     if _lib is not None:
@@ -48,6 +53,7 @@ def lib():
         "rag_set_ladder_handover": (i32, [i32]),
         "rag_set_ladder_helpers": (i32, [i32]),
         "rag_features_ladders": (i32, [vp, i32, i32, vp, sz, vp]),
+        "rag_features_analyze_superko": (i32, [vp, i32, i32, i32, vp, vp, sz, vp]),
         "rag_features_emit": (i32, [vp, i32, i32, vp, i32, i32, i32, i32, vp, vp]),
         "rag_features": (i32, [vp, i32, i32, vp, i32, i32, i32, i32, vp, vp, sz, vp]),
         "rag_features_static": (i32, [vp, i32, i32, vp, i32, i32, i32, i32, vp, vp]),

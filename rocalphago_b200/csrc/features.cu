@@ -105,8 +105,25 @@ __device__ __forceinline__ int q_to_p(int q, int S) { return q < 0 ? -1 : ((q >>
 // of the next batch then runs beside the convolutions instead of in the gaps between their layers.
 constexpr int kAnalyzeWarps = 2;
 
+// What is_positional_superko reads, per position (rag_superko in the header), as device pointers.
+struct SuperkoArgs {
+    const u64* zob; const u64* hash; const u64* prev; const int32_t* prev_off;
+    const uint32_t* masks; const int32_t* flags;
+};
+
+__device__ __forceinline__ void load_superko(const SuperkoArgs& a, int pos, const Geo& g, SuperkoRoot& r, SuperkoCtx& c) {
+    const uint32_t* m = a.masks + (size_t)pos * 96;
+    const int flags = a.flags[pos];
+    c.even = bb_load(m, g); c.odd = bb_load(m + 32, g); r.handi = bb_load(m + 64, g);
+    c.hash = a.hash[pos]; c.hist_len = flags >> 8;
+    r.zob = a.zob; r.prev = a.prev + a.prev_off[pos]; r.nprev = a.prev_off[pos + 1] - a.prev_off[pos];
+    r.has_handicap = (flags & 2) != 0;
+    r.enforce = (flags & 1) != 0;
+}
+
+template <bool kSuperko>
 __global__ void __launch_bounds__(kAnalyzeWarps * 32)
-analyze_kernel(const uint32_t* __restrict__ states, int n, int S, int with_ladders, Workspace ws)
+analyze_kernel(const uint32_t* __restrict__ states, int n, int S, int with_ladders, Workspace ws, SuperkoArgs ska)
 {
     __shared__ uint32_t sm_planes[kAnalyzeWarps][kPlaneWords];
     __shared__ EyeStack sm_eye[kAnalyzeWarps];
@@ -121,7 +138,13 @@ analyze_kernel(const uint32_t* __restrict__ states, int n, int S, int with_ladde
     const LoadedState s = load_state(states + (size_t)pos * RAG_STATE_WORDS, g);
     const BB own = s.player > 0 ? s.black : s.white;
     const BB opp = s.player > 0 ? s.white : s.black;
-    const Analysis A = bb_features(g, own, opp, s.age0, s.age1, s.age2, p_to_q(s.ko_p, S), planes, sm_eye[warp]);
+    BB forbid = bb_zero();
+    if (kSuperko) {
+        SuperkoRoot r; SuperkoCtx c;
+        load_superko(ska, pos, g, r, c);
+        forbid = sk_forbidden_moves(g, r, c, own, opp, p_to_q(s.ko_p, S), s.player > 0);
+    }
+    const Analysis A = bb_features(g, own, opp, s.age0, s.age1, s.age2, p_to_q(s.ko_p, S), planes, sm_eye[warp], forbid);
     if (s.player > 0) plane_or(planes, kPlaneColor, bb_board(g), g);
     __syncwarp();
 
@@ -435,6 +458,40 @@ ladder_kernel(const uint32_t* __restrict__ states, int S, int steal_after, int h
     }
 }
 
+// The ladder reader for positions that enforce positional superko: the same queue, one warp per item,
+// ladder_search_sk (go_bb.cuh) carrying hash, history masks and the hashes of its own line.  No reply
+// hand-over here: this path serves a GTP front end, a few positions at a time.
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+ladder_superko_kernel(const uint32_t* __restrict__ states, int S, Workspace ws, SuperkoArgs ska)
+{
+    const Geo g = make_geo(S);
+    LadderStackSk st;
+    const unsigned total = min((unsigned)ws.queue_cap, ws.counters[kCtlQueued]);
+    for (;;) {
+        unsigned idx = 0;
+        if (g.lane == 0) idx = atomicAdd(&ws.counters[kCtlTaken], 1u);
+        idx = __shfl_sync(kFullMask, idx, 0);
+        if (idx >= total) break;
+        const uint32_t item = ws.queue[idx];
+        const int pos = (int)(item >> 11), kind = (int)((item >> 10) & 1u), q = (int)(item & 1023u);
+        const LoadedState s = load_state(states + (size_t)pos * RAG_STATE_WORDS, g);
+        const BB own = s.player > 0 ? s.black : s.white;
+        const BB opp = s.player > 0 ? s.white : s.black;
+        const int ko = p_to_q(s.ko_p, S);
+        const bool is_escape = kind == 1, black = s.player > 0;
+        SuperkoRoot r; SuperkoCtx c;
+        load_superko(ska, pos, g, r, c);
+        BB preys[4];
+        const int np = ladder_root_preys(g, own, opp, q, is_escape, preys);
+        int res = kLadderValue0;
+        for (int i = 0; i < np && res == kLadderValue0; i++)
+            res = is_escape ? ladder_search_sk(g, opp, own, preys[i], ko, q, false, kLadderDepth, r, c, !black, st)
+                            : ladder_search_sk(g, own, opp, preys[i], ko, q, true, kLadderDepth, r, c, black, st);
+        if (g.lane == 0 && res == kLadderValue1)
+            atomicOr(ws.planes + (size_t)pos * kPlaneWords + (kPlaneLadderCapture + kind) * 32 + (q >> 5), 1u << (q & 31));
+    }
+}
+
 // ---- kernel 3: emit ---------------------------------------------------------------------------
 
 struct PlaneMap { int F; uint8_t src[RAG_MAX_OUT_PLANES]; };
@@ -647,7 +704,7 @@ static int match_conv_carveout() {
     std::lock_guard<std::mutex> lock(mu);
     if (done[dev]) return RAG_OK;
     const int pct = (int)cudaSharedmemCarveoutMaxShared;
-    RAG_CUDA_CHECK(cudaFuncSetAttribute(analyze_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+    RAG_CUDA_CHECK(cudaFuncSetAttribute(analyze_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
     RAG_CUDA_CHECK(cudaFuncSetAttribute(ladder_kernel<1>, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
     RAG_CUDA_CHECK(cudaFuncSetAttribute(emit_conv_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
     done[dev] = true;
@@ -774,7 +831,7 @@ using namespace rag;
 extern "C" {
 
 const char* rag_last_error(void) { return last_error_buffer(); }
-int rag_abi_version(void) { return 3; }
+int rag_abi_version(void) { return 4; }
 
 int rag_pack_states(int n, int size, const int8_t* h_board, const int16_t* h_age, const int32_t* h_ko,
                     const int32_t* h_player, uint32_t* h_packed)
@@ -845,7 +902,7 @@ int rag_features_analyze(const uint32_t* d_states, int n, int size, int with_lad
     Workspace ws = carve(d_workspace, n);
     RAG_CUDA_CHECK(cudaMemsetAsync(ws.counters, 0, kCounterBytes, s));
     RAG_CUDA_CHECK(cudaMemsetAsync(ws.tasks, 0, (size_t)ws.task_cap * (sizeof(StealTask) + 4), s));     // all tasks free, ring empty
-    analyze_kernel<<<(n + kAnalyzeWarps - 1) / kAnalyzeWarps, kAnalyzeWarps * 32, 0, s>>>(d_states, n, size, with_ladders, ws);
+    analyze_kernel<false><<<(n + kAnalyzeWarps - 1) / kAnalyzeWarps, kAnalyzeWarps * 32, 0, s>>>(d_states, n, size, with_ladders, ws, SuperkoArgs());
     RAG_CUDA_CHECK(cudaGetLastError());
     if (with_ladders == 1) {
         int dev = 0, sms = 148;
@@ -882,6 +939,39 @@ int rag_features_ladders(const uint32_t* d_states, int n, int size, void* d_work
     int blocks = (int)(want < (long long)sms * 4 ? (want < 1 ? 1 : want) : (long long)sms * 4);
     ladder_kernel<1><<<blocks, kWarpsPerBlock * 32, 0, (cudaStream_t)stream>>>(d_states, size, g_steal_after, g_helper_ctas, ws);
     RAG_CUDA_CHECK(cudaGetLastError());
+    return RAG_OK;
+}
+
+int rag_features_analyze_superko(const uint32_t* d_states, int n, int size, int with_ladders, const rag_superko* sk,
+                                 void* d_workspace, size_t workspace_bytes_given, void* stream)
+{
+    if (!sk) return fail(RAG_EINVAL, "null superko description");
+    if (n < 0 || (n > 0 && (!d_states || !d_workspace))) return fail(RAG_EINVAL, "null argument");
+    if (n > 0 && (!sk->d_zobrist || !sk->d_hash || !sk->d_prev || !sk->d_prev_off || !sk->d_masks || !sk->d_flags))
+        return fail(RAG_EINVAL, "null pointer in the superko description");
+    if (int rc = check_size(size)) return rc;
+    if (with_ladders != 0 && with_ladders != 1) return fail(RAG_EINVAL, "with_ladders must be 0 or 1 here");
+    if (n > kMaxPositionsPerLaunch) return fail(RAG_EUNSUPPORTED, "n = %d exceeds %d positions per call", n, kMaxPositionsPerLaunch);
+    if (workspace_bytes_given < workspace_bytes(n))
+        return fail(RAG_ENOMEM, "workspace has %zu bytes, %zu needed for n = %d", workspace_bytes_given, workspace_bytes(n), n);
+    if (n == 0) return RAG_OK;
+    cudaStream_t s = (cudaStream_t)stream;
+    Workspace ws = carve(d_workspace, n);
+    SuperkoArgs a;
+    a.zob = (const u64*)sk->d_zobrist; a.hash = (const u64*)sk->d_hash; a.prev = (const u64*)sk->d_prev;
+    a.prev_off = sk->d_prev_off; a.masks = sk->d_masks; a.flags = sk->d_flags;
+    RAG_CUDA_CHECK(cudaMemsetAsync(ws.counters, 0, kCounterBytes, s));
+    analyze_kernel<true><<<(n + kAnalyzeWarps - 1) / kAnalyzeWarps, kAnalyzeWarps * 32, 0, s>>>(d_states, n, size, with_ladders, ws, a);
+    RAG_CUDA_CHECK(cudaGetLastError());
+    if (with_ladders) {
+        int dev = 0, sms = 148;
+        RAG_CUDA_CHECK(cudaGetDevice(&dev));
+        RAG_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        long long want = ((long long)n * 16 + kWarpsPerBlock - 1) / kWarpsPerBlock;
+        int blocks = (int)(want < (long long)sms * 4 ? (want < 1 ? 1 : want) : (long long)sms * 4);
+        ladder_superko_kernel<<<blocks, kWarpsPerBlock * 32, 0, s>>>(d_states, size, ws, a);
+        RAG_CUDA_CHECK(cudaGetLastError());
+    }
     return RAG_OK;
 }
 

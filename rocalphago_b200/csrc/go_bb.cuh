@@ -720,6 +720,7 @@ struct SuperkoRoot {                // constant during one search
     int nprev;
     BB handi;                       // handicaps
     bool has_handicap;
+    bool enforce;                   // enforce_superko of this position (a batch may mix both kinds)
 };
 
 struct SuperkoCtx {                 // of one state (the position, or a node of a ladder search)
@@ -769,6 +770,7 @@ RAG_FN BB sk_mine(const SuperkoRoot& r, const SuperkoCtx& c, bool mover_is_black
 RAG_FN_NOINLINE BB sk_forbidden_moves(const Geo& g, const SuperkoRoot& r, const SuperkoCtx& c, BB M, BB O, int ko_q,
                                       bool mover_is_black) {
     BB out = bb_zero();
+    if (!r.enforce) return out;
     BB rem = andnot(sk_mine(r, c, mover_is_black), M | O);
     for (;;) {
         const int q = bb_first(rem);
@@ -806,7 +808,7 @@ RAG_FN int ladder_expand_sk(const Geo& g, bool is_capture, BB& H, BB& P, BB& G, 
     const bool mover_is_black = is_capture ? hunter_is_black : !hunter_is_black;
     u64 h = c.hash ^ r.zob[(mover_is_black ? 0 : 1024) + mv];
     if (ncap) h ^= bb_zobrist(g, is_capture ? andnot(Pb, P) : andnot(Hb, H), r.zob + (mover_is_black ? 1024 : 0));
-    if (bb_test(sk_mine(r, c, mover_is_black), mv) && sk_seen(g, r, h, path, npath)) return kLadderValue0;   // go.py:282-283
+    if (r.enforce && bb_test(sk_mine(r, c, mover_is_black), mv) && sk_seen(g, r, h, path, npath)) return kLadderValue0;   // go.py:282-283
     c.hash = h;
     if (c.hist_len & 1) c.odd = c.odd | bb_single(mv, g); else c.even = c.even | bb_single(mv, g);
     c.hist_len++;

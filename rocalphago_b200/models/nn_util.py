@@ -13,7 +13,7 @@ import numpy as np
 import torch
 
 from .. import _cabi, hdf5_lite
-from ..preprocessing import Preprocess, DTYPE_BF16, DTYPE_FP16, DTYPE_FP16X3
+from ..preprocessing import Preprocess, DTYPE_BF16, DTYPE_FP16, DTYPE_FP16X3, LAYOUT_CONV_IN, analyze_into
 from ..state import _ptr, _stream, _require_cuda
 
 HEAD_POLICY, HEAD_VALUE = 0, 1
@@ -311,8 +311,23 @@ class Network(object):
         if n == 0:
             return out
         L = _cabi.lib()
-        ws = self._workspace(L.rag_eval_workspace_bytes(h, n), batch.device)
         src = np.ascontiguousarray(plane_src, np.int32)
+        if getattr(batch, "superko", None) is not None:
+            # positional superko needs the analysis entry point that knows the move history; the rest
+            # is what rag_eval_batch does: conv-layout emit, then the forward over pixel rows
+            vp = ctypes.c_void_p
+            self._ws = fws = torch.empty(int(L.rag_features_workspace_bytes(n)), dtype=torch.uint8, device=batch.device)
+            rows = torch.empty((int(L.rag_net_input_rows(h, n)), int(L.rag_net_input_channels(h))), dtype=torch.float16,
+                               device=batch.device)
+            nws = torch.empty(int(L.rag_net_workspace_bytes(h, n)), dtype=torch.uint8, device=batch.device)
+            analyze_into(batch, fws, True)
+            with torch.cuda.device(batch.device):
+                _cabi.check(L.rag_features_emit(_ptr(fws), n, batch.size, src.ctypes.data_as(vp), len(src), LAYOUT_CONV_IN,
+                                                DTYPE_BF16 if self.dtype == "bf16" else DTYPE_FP16, rows.shape[1],
+                                                _ptr(rows), _stream()))
+                _cabi.check(L.rag_net_forward_rows(h, _ptr(rows), n, _ptr(out), _ptr(nws), nws.numel(), _stream()))
+            return out
+        ws = self._workspace(L.rag_eval_workspace_bytes(h, n), batch.device)
         with torch.cuda.device(batch.device):
             _cabi.check(L.rag_eval_batch(h, _ptr(batch.packed), n, src.ctypes.data_as(ctypes.c_void_p), len(src),
                                          _ptr(out), _ptr(ws), ws.numel(), _stream()))

@@ -65,6 +65,20 @@ class _Workspace(object):
         return self.buf
 
 
+def analyze_into(batch, ws, with_ladders=True):
+    """rag_features_analyze -- or, for a batch built from states that enforce positional superko,
+    rag_features_analyze_superko -- of `batch` into the workspace tensor `ws`, on the current stream."""
+    L = _cabi.lib()
+    with torch.cuda.device(batch.device):
+        if getattr(batch, "superko", None) is not None:
+            sk = batch.superko.struct()
+            _cabi.check(L.rag_features_analyze_superko(_ptr(batch.packed), len(batch), batch.size, int(bool(with_ladders)),
+                                                       ctypes.byref(sk), _ptr(ws), ws.numel(), _stream()))
+        else:
+            _cabi.check(L.rag_features_analyze(_ptr(batch.packed), len(batch), batch.size, int(bool(with_ladders)),
+                                               _ptr(ws), ws.numel(), _stream()))
+
+
 class Preprocess(object):
     """a class to convert from AlphaGo GameState objects to tensors of one-hot
     features for NN inputs (preprocessing.py:266-294)"""
@@ -92,9 +106,7 @@ class Preprocess(object):
         if with_ladders is None:
             with_ladders = bool(np.any((self.plane_src == 44) | (self.plane_src == 45)))
         ws = self._ws.get(len(batch), batch.device)
-        with torch.cuda.device(batch.device):
-            _cabi.check(_cabi.lib().rag_features_analyze(_ptr(batch.packed), len(batch), batch.size,
-                                                         int(with_ladders), _ptr(ws), ws.numel(), _stream()))
+        analyze_into(batch, ws, with_ladders)
         return ws
 
     def emit(self, ws, n, size, layout=LAYOUT_NCHW_U8, plane_src=None, conv_dtype=DTYPE_BF16,

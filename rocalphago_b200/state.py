@@ -71,12 +71,89 @@ def pack_arrays(board, age, ko, player, pinned=False):
     return packed
 
 
-class BatchedGameState(object):
-    """n positions of one board size, packed (n, 192) int32 on a CUDA device."""
+_ZOBRIST = {}
 
-    def __init__(self, packed, size):
+
+def zobrist_table(size):
+    """GameState.hash_lookup (go.py:58-62) laid out for the device: uint64 [2][1024] indexed by
+    q = x*32 + y, [0] BLACK, [1] WHITE.  The reference draws WHITE's table first from RandomState(0)."""
+    if size not in _ZOBRIST:
+        rng = np.random.RandomState(0)
+        white = rng.randint(np.iinfo(np.uint64).max, size=(size, size), dtype="uint64")
+        black = rng.randint(np.iinfo(np.uint64).max, size=(size, size), dtype="uint64")
+        t = np.zeros((2, 32, 32), np.uint64)
+        t[0, :size, :size], t[1, :size, :size] = black, white
+        _ZOBRIST[size] = t.reshape(2, 1024)
+    return _ZOBRIST[size]
+
+
+class SuperkoData(object):
+    """What is_positional_superko (go.py:242-265) reads from each state, on the device (rag_superko).
+    Built by BatchedGameState.from_states when a state has enforce_superko set."""
+
+    def __init__(self, states, size, device):
+        n = len(states)
+        masks = np.zeros((n, 3, 32), np.uint32)
+        enforce, handi, hist_len = np.zeros(n, np.int32), np.zeros(n, np.int32), np.zeros(n, np.int32)
+        hashes = np.zeros(n, np.uint64)
+        prev, off = [], np.zeros(n + 1, np.int32)
+        for i, st in enumerate(states):
+            if getattr(st, "enforce_superko", False):
+                for k, mv in enumerate(st.history):
+                    if mv is not None:
+                        masks[i, k & 1, mv[0]] |= np.uint32(1 << mv[1])
+                for mv in st.handicaps:
+                    masks[i, 2, mv[0]] |= np.uint32(1 << mv[1])
+                enforce[i], handi[i], hist_len[i] = 1, int(len(st.handicaps) > 0), len(st.history)
+                hashes[i] = np.uint64(st.current_hash)
+                prev.append(np.fromiter((int(h) for h in st.previous_hashes), np.uint64, len(st.previous_hashes)))
+                off[i + 1] = off[i] + len(prev[-1])
+            else:
+                off[i + 1] = off[i]
+        self._upload(size, device, enforce, handi, hist_len, hashes,
+                     np.concatenate(prev) if prev else np.zeros(0, np.uint64), off, masks)
+
+    @classmethod
+    def from_arrays(cls, size, device, enforce, has_handicap, hist_len, hashes, prev, prev_off, point_masks):
+        """From plain arrays: point_masks uint8 (n, 3, S*S) = points of history[0::2] / history[1::2] /
+        handicaps (flat index x*S+y); prev = all previous_hashes, position b's in prev_off[b]:prev_off[b+1]."""
+        self = cls.__new__(cls)
+        pm = np.asarray(point_masks).reshape(len(enforce), 3, size, size).astype(bool)
+        masks = np.zeros((len(enforce), 3, 32), np.uint32)
+        masks[:, :, :size] = (pm * (np.uint32(1) << np.arange(size, dtype=np.uint32))).sum(axis=3).astype(np.uint32)
+        self._upload(size, device, np.asarray(enforce, np.int32), np.asarray(has_handicap, np.int32),
+                     np.asarray(hist_len, np.int32), np.asarray(hashes, np.uint64), np.asarray(prev, np.uint64),
+                     np.asarray(prev_off, np.int32), masks)
+        return self
+
+    def _upload(self, size, device, enforce, has_handicap, hist_len, hashes, prev, prev_off, masks):
+        masks = masks * enforce[:, None, None].astype(np.uint32)          # a position that does not enforce superko has no history here
+        flags = (enforce | (has_handicap << 1) | (hist_len << 8)).astype(np.int32) * enforce      # 0 = evaluated without superko
+        if prev.size == 0:
+            prev = np.zeros(1, np.uint64)
+        as_i64 = lambda a: torch.as_tensor(np.ascontiguousarray(a).view(np.int64)).to(device)  # noqa: E731  (only the bits travel)
+        self.zobrist = as_i64(zobrist_table(size))
+        self.hash, self.prev = as_i64(hashes), as_i64(prev)
+        self.prev_off = torch.as_tensor(np.ascontiguousarray(prev_off)).to(device)
+        self.masks = torch.as_tensor(np.ascontiguousarray(masks).view(np.int32)).to(device)
+        self.flags = torch.as_tensor(flags).to(device)
+
+    def struct(self):
+        """ctypes rag_superko pointing at the tensors (keep `self` alive while it is in use)."""
+        return _cabi.RagSuperko(*[ctypes.c_void_p(t.data_ptr()) for t in
+                                  (self.zobrist, self.hash, self.prev, self.prev_off, self.masks, self.flags)])
+
+
+class BatchedGameState(object):
+    """n positions of one board size, packed (n, 192) int32 on a CUDA device.  `superko` is None unless
+    the batch was built from states that enforce positional superko (then features, move lists and
+    network evaluations honour it; states advanced on the device -- do_move, playouts -- carry no
+    history and never have it)."""
+
+    def __init__(self, packed, size, superko=None):
         self.packed = packed
         self.size = int(size)
+        self.superko = superko
 
     def __len__(self):
         return int(self.packed.shape[0])
@@ -94,7 +171,10 @@ class BatchedGameState(object):
 
     @classmethod
     def from_states(cls, states, device=None):
-        return cls.from_arrays(*arrays_from_states(states), device=device)
+        batch = cls.from_arrays(*arrays_from_states(states), device=device)
+        if any(getattr(st, "enforce_superko", False) for st in states):
+            batch.superko = SuperkoData(states, batch.size, batch.device)
+        return batch
 
     @classmethod
     def random_playouts(cls, n, size=19, seed=20261106, max_ply=400, stride=8, device=None, with_log=False):
@@ -122,6 +202,7 @@ class BatchedGameState(object):
             if not torch.is_tensor(moves) else moves
         mv = torch.as_tensor(mv, dtype=torch.int32).to(self.device).contiguous()
         status = torch.empty(len(self), dtype=torch.int32, device=self.device)
+        self.superko = None                 # the device keeps no move history: from here on superko is not enforced
         with torch.cuda.device(self.device):
             _cabi.check(_cabi.lib().rag_do_move(_ptr(self.packed), len(self), self.size, _ptr(mv), _ptr(status),
                                                 _stream()))

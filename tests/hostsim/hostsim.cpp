@@ -105,6 +105,7 @@ extern "C" int hostsim_features_superko(int n, int S, const int8_t* board, const
             }
         r.zob = zob; r.prev = (const u64*)prev + prev_off[b]; r.nprev = prev_off[b + 1] - prev_off[b];
         r.has_handicap = has_handicap[b] != 0;
+        r.enforce = true;
         c.hash = hash[b]; c.hist_len = hist_len[b];
         const bool black = player[b] > 0;
         int ko_q = ko[b] < 0 ? -1 : ((ko[b] / S) << 5) | (ko[b] % S);
