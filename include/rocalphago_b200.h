@@ -46,7 +46,9 @@ int rag_abi_version(void);
  * A position on the device is RAG_STATE_WORDS uint32: six planes of 32 row words
  * (row x in word x, point (x, y) in bit y): black, white, three bit-planes of
  * min(stone_ages, 7), and a meta plane (word 0 = ko point p or -1, word 1 =
- * current_player +1/-1, word 2 = board size).  This is the device twin of the
+ * current_player +1/-1, word 2 = board size, words 8..26 = rows of the stones that have NO age:
+ * stone_ages is -1 under every stone of a GameState.copy() (go.py:186-217 does not copy it), such
+ * stones are in no turns_since plane and are never aged (go.py:533) -- what MCTS feeds the networks).  This is the device twin of the
  * fields of GameState the 48 planes depend on (go.py:18-22,55).
  */
 #define RAG_STATE_WORDS 192
@@ -54,7 +56,7 @@ int rag_abi_version(void);
 
 /* Host-side packing of GameState fields (go.py:18-22,55) into the device format.
  * board int8 [n][S*S] in {+1 black, -1 white, 0}; age int16 [n][S*S] (stone_ages,
- * -1 on empties); ko int32 [n] (x*S+y or -1); player int32 [n] (+1/-1).
+ * -1 on empties, and -1 under a stone that has no age); ko int32 [n] (x*S+y or -1); player int32 [n] (+1/-1).
  * h_packed: n * RAG_STATE_WORDS uint32 (pinned memory recommended). */
 int rag_pack_states(int n, int size, const int8_t* h_board, const int16_t* h_age,
                     const int32_t* h_ko, const int32_t* h_player, uint32_t* h_packed);
@@ -192,6 +194,14 @@ int rag_select_moves(const float* d_probs, const void* d_workspace, int n, int s
  * untouched; the reference raises IllegalMove). */
 int rag_do_move(uint32_t* d_states, int n, int size, const int32_t* d_moves, int32_t* d_status,
                 void* stream);
+
+/* MCTS._evaluate_rollout (mcts.py:171-189) for a batch, with uniformly random sensible moves in place of
+ * the greedy rollout policy, then GameState.get_winner (go.py:482-506, area scoring, komi to WHITE).
+ * Each position is played on (the input is not modified) until the side to move has no sensible move
+ * or `limit` moves were made.  d_result int32 [n]: +1 the player to move in d_states[i] wins, -1 the
+ * opponent, 0 tie.  Draws are a pure function of (seed, i). */
+int rag_rollout_winners(const uint32_t* d_states, int n, int size, int limit, uint64_t seed, float komi,
+                        int32_t* d_result, void* stream);
 
 /* Random playouts on the device (the synthetic workload of BASELINE.json /
  * SURVEY 8(d)).  Warp w owns output slots [w*quota, (w+1)*quota), quota =

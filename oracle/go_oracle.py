@@ -194,3 +194,22 @@ def features_superko(board, age, ko, player, sk, feature_list=DEFAULT_FEATURES, 
     if with_moves:
         return out, [moves[i, :counts[i, 0]].astype(np.int64) for i in range(n)], counts[:, 1].copy()
     return out
+
+
+def winners(board, age, ko, player, komi=7.5):
+    """GameState.get_winner() (go.py:482-506) of each position, no passes made: +1 BLACK, -1 WHITE, 0 tie."""
+    res = rollout_winners(board, age, ko, player, limit=0, seed=0, komi=komi)
+    return res * np.asarray(player, np.int32).reshape(-1)                                   # rollout results are relative to the side to move
+
+
+def rollout_winners(board, age, ko, player, limit=500, seed=0, komi=7.5):
+    """+1 / -1 / 0 for the player to move after a uniformly random sensible-move rollout (see go_oracle.c)."""
+    n, size, board, age, ko, player = _canon(board, age, ko, player)
+    L = lib()
+    L.og_rollout_winners.restype = None
+    L.og_rollout_winners.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                     ctypes.c_void_p, ctypes.c_int, ctypes.c_uint64, ctypes.c_double, ctypes.c_void_p]
+    out = np.zeros(n, np.int32)
+    L.og_rollout_winners(n, size, board.ctypes.data, age.ctypes.data, ko.ctypes.data, player.ctypes.data,
+                         int(limit), int(seed), float(komi), out.ctypes.data)
+    return out

@@ -53,6 +53,7 @@ def lib():
         "rag_set_ladder_handover": (i32, [i32]),
         "rag_set_ladder_helpers": (i32, [i32]),
         "rag_features_ladders": (i32, [vp, i32, i32, vp, sz, vp]),
+        "rag_rollout_winners": (i32, [vp, i32, i32, i32, c.c_uint64, c.c_float, vp, vp]),
         "rag_features_analyze_superko": (i32, [vp, i32, i32, i32, vp, vp, sz, vp]),
         "rag_features_emit": (i32, [vp, i32, i32, vp, i32, i32, i32, i32, vp, vp]),
         "rag_features": (i32, [vp, i32, i32, vp, i32, i32, i32, i32, vp, vp, sz, vp]),

@@ -85,6 +85,7 @@ static Workspace carve(void* base, int n) {
 
 // ---- packed state access --------------------------------------------------------------------
 
+constexpr int kAgelessWord = 168;          // meta plane words 8..26: rows of the stones that have no age
 struct LoadedState { BB black, white, age0, age1, age2; int ko_p, player; };
 
 __device__ __forceinline__ LoadedState load_state(const uint32_t* __restrict__ st, const Geo& g) {
@@ -145,6 +146,11 @@ analyze_kernel(const uint32_t* __restrict__ states, int n, int S, int with_ladde
         forbid = sk_forbidden_moves(g, r, c, own, opp, p_to_q(s.ko_p, S), s.player > 0);
     }
     const Analysis A = bb_features(g, own, opp, s.age0, s.age1, s.age2, p_to_q(s.ko_p, S), planes, sm_eye[warp], forbid);
+    // stones without an age (stone_ages -1 under a stone: what GameState.copy() leaves behind, go.py:186-217)
+    // are in no turns_since plane (preprocessing.py:33-36)
+    const uint32_t ageless = g.lane < 24u ? __ldg(states + (size_t)pos * RAG_STATE_WORDS + kAgelessWord + g.lane) : 0u;
+    if (__any_sync(kFullMask, ageless != 0u))
+        for (int k = 0; k < 8; k++) planes[(kPlaneTurnsSince + k) * 32 + g.lane] &= ~ageless;
     if (s.player > 0) plane_or(planes, kPlaneColor, bb_board(g), g);
     __syncwarp();
 
@@ -604,14 +610,17 @@ emit_conv_kernel(const uint32_t* __restrict__ planes, int n, int S, int C, Plane
 
 // ---- do_move / playouts -----------------------------------------------------------------------
 
-__device__ __forceinline__ void store_state(uint32_t* st, const FullState& s, int S, const Geo& g) {
+// `ageless`: this lane's row of the stones that have no age (every word of the meta plane is written by
+// exactly one lane: 160..167 by lanes 0..7, 168..191 by lanes 0..23)
+__device__ __forceinline__ void store_state(uint32_t* st, const FullState& s, int S, const Geo& g, uint32_t ageless = 0u) {
     bb_store(st + 0, s.black, g);  bb_store(st + 32, s.white, g);
     bb_store(st + 64, s.age0, g);  bb_store(st + 96, s.age1, g);  bb_store(st + 128, s.age2, g);
     uint32_t m = 0;
     if (g.lane == 0) m = (uint32_t)q_to_p(s.ko_q, S);
     if (g.lane == 1) m = (uint32_t)s.player;
     if (g.lane == 2) m = (uint32_t)S;
-    st[160 + g.lane] = m;
+    if (g.lane < 8u) st[160 + g.lane] = m;
+    if (g.lane < 24u) st[kAgelessWord + g.lane] = ageless;
 }
 
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
@@ -625,8 +634,10 @@ do_move_kernel(uint32_t* states, int n, int S, const int32_t* __restrict__ moves
     FullState s{l.black, l.white, l.age0, l.age1, l.age2, p_to_q(l.ko_p, S), l.player};
     const int mv = moves[pos];
     bool ok = mv < S * S;
+    const uint32_t ageless = g.lane < 24u ? st[kAgelessWord + g.lane] : 0u;
     if (ok) ok = bb_do_move(g, s, mv < 0 ? -1 : p_to_q(mv, S));
-    if (ok) store_state(st, s, S, g);
+    // stones without an age stay so until they are captured (go.py:533 ages only stone_ages >= 0)
+    if (ok) store_state(st, s, S, g, ageless & (s.black.w | s.white.w));
     if (g.lane == 0 && status) status[pos] = ok ? 0 : -1;
 }
 
@@ -675,6 +686,42 @@ playout_kernel(uint32_t* out, int n_positions, int S, uint64_t seed, int max_ply
             if (passes >= 2) break;
         }
     }
+}
+
+// Rollout to the end and winner (mcts.py:171-189 with uniformly random sensible moves; go.py:482-506).
+// One warp per position: plays until the side to move has no sensible move or `limit` moves were made,
+// then scores by area -- stones plus empty points whose neighbours all have one colour, komi to WHITE
+// (no passes are made here, so the pass counters of get_winner do not change).  result = +1 if the
+// player to move at the START wins, -1 if the opponent does, 0 on a tie.
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+rollout_kernel(const uint32_t* __restrict__ states, int n, int S, uint64_t seed, int limit, float komi, int32_t* result)
+{
+    __shared__ EyeStack sm_eye[kWarpsPerBlock];
+    const int warp = threadIdx.x >> 5;
+    const int pos = blockIdx.x * kWarpsPerBlock + warp;
+    if (pos >= n) return;
+    const Geo g = make_geo(S);
+    const LoadedState l = load_state(states + (size_t)pos * RAG_STATE_WORDS, g);
+    FullState s{l.black, l.white, l.age0, l.age1, l.age2, p_to_q(l.ko_p, S), l.player};
+    const int player0 = s.player;
+    uint64_t rng = seed ^ (0xD1B54A32D192ED03ull * (uint64_t)(pos + 1));
+    for (int t = 0; t < limit; t++) {
+        const BB own = s.player > 0 ? s.black : s.white, opp = s.player > 0 ? s.white : s.black;
+        BB legal, sensible;
+        bb_moves(g, own, opp, s.ko_q, sm_eye[warp], legal, sensible);
+        const int cnt = bb_count(sensible);
+        if (cnt == 0) break;
+        bb_do_move(g, s, bb_select(sensible, (int)(splitmix64(rng) % (uint64_t)cnt)));
+    }
+    const BB empty = andnot(bb_board(g), s.black | s.white);
+    const BB eb = empty & bb_from_north(s.black, g, true) & bb_from_south(s.black, g, true) &
+                  bb_from_west(s.black, g, true) & bb_from_east(s.black, g, true);
+    const BB ew = andnot(empty & bb_from_north(s.white, g, true) & bb_from_south(s.white, g, true) &
+                         bb_from_west(s.white, g, true) & bb_from_east(s.white, g, true), eb);
+    const float black = (float)(bb_count(s.black) + bb_count(eb));
+    const float white = (float)(bb_count(s.white) + bb_count(ew)) + komi;
+    const int winner = black > white ? +1 : (white > black ? -1 : 0);
+    if (g.lane == 0) result[pos] = winner == 0 ? 0 : (winner == player0 ? +1 : -1);
 }
 
 // ---- scratch that nobody allocates (rag_features_static) -----------------------------------------
@@ -831,7 +878,7 @@ using namespace rag;
 extern "C" {
 
 const char* rag_last_error(void) { return last_error_buffer(); }
-int rag_abi_version(void) { return 4; }
+int rag_abi_version(void) { return 5; }
 
 int rag_pack_states(int n, int size, const int8_t* h_board, const int16_t* h_age, const int32_t* h_ko,
                     const int32_t* h_player, uint32_t* h_packed)
@@ -851,6 +898,7 @@ int rag_pack_states(int n, int size, const int8_t* h_board, const int16_t* h_age
                 if (v != 1 && v != -1) return fail(RAG_EINVAL, "board[%d][%d][%d] = %d", b, x, y, v);
                 st[(v > 0 ? 0 : 32) + x] |= 1u << y;
                 int a = ag[x * size + y];
+                if (a < 0) st[kAgelessWord + x] |= 1u << y;       // a stone GameState.copy() left without an age
                 a = a < 0 ? 0 : (a > 7 ? 7 : a);
                 if (a & 1) st[64 + x] |= 1u << y;
                 if (a & 2) st[96 + x] |= 1u << y;
@@ -878,7 +926,8 @@ int rag_unpack_states(int n, int size, const uint32_t* h_packed, int8_t* h_board
                 int bl = (st[x] >> y) & 1u, wh = (st[32 + x] >> y) & 1u;
                 h_board[(size_t)b * np + x * size + y] = (int8_t)(bl ? 1 : (wh ? -1 : 0));
                 int a = ((st[64 + x] >> y) & 1u) | (((st[96 + x] >> y) & 1u) << 1) | (((st[128 + x] >> y) & 1u) << 2);
-                h_age[(size_t)b * np + x * size + y] = (int16_t)((bl || wh) ? a : -1);
+                const int ageless = (st[kAgelessWord + x] >> y) & 1u;
+                h_age[(size_t)b * np + x * size + y] = (int16_t)(((bl || wh) && !ageless) ? a : -1);
             }
         h_ko[b] = (int32_t)st[160];
         h_player[b] = (int32_t)st[161];
@@ -1085,6 +1134,19 @@ int rag_random_playouts(uint32_t* d_states_out, int n_positions, int size, uint6
     const int warps = (n_positions + quota - 1) / quota;
     playout_kernel<<<(warps + kWarpsPerBlock - 1) / kWarpsPerBlock, kWarpsPerBlock * 32, 0, (cudaStream_t)stream>>>(
         d_states_out, n_positions, size, seed, max_ply, stride, quota, d_move_log, d_move_log ? log_stride : 0);
+    RAG_CUDA_CHECK(cudaGetLastError());
+    return RAG_OK;
+}
+
+int rag_rollout_winners(const uint32_t* d_states, int n, int size, int limit, uint64_t seed, float komi,
+                        int32_t* d_result, void* stream)
+{
+    if (n < 0 || (n > 0 && (!d_states || !d_result))) return fail(RAG_EINVAL, "null argument");
+    if (int rc = check_size(size)) return rc;
+    if (limit < 0) return fail(RAG_EINVAL, "limit must not be negative");
+    if (n == 0) return RAG_OK;
+    rollout_kernel<<<(n + kWarpsPerBlock - 1) / kWarpsPerBlock, kWarpsPerBlock * 32, 0, (cudaStream_t)stream>>>(
+        d_states, n, size, seed, limit, komi, d_result);
     RAG_CUDA_CHECK(cudaGetLastError());
     return RAG_OK;
 }

@@ -26,6 +26,18 @@ class CNNPolicy(NeuralNetBase):
         distribution = distribution / distribution.sum()
         return list(zip(moves, distribution))
 
+    def eval_arrays(self, batch):
+        """batch_eval_state of a BatchedGameState as flat arrays: (state index, flat move x*S+y,
+        moves per state, probability renormalised over each state's legal moves), moves in
+        get_legal_moves() order.  What batched callers (players, tree search) consume."""
+        n = len(batch)
+        probs = self.model.eval_batch_device(batch, self.preprocessor.plane_src)
+        which, flat, counts = self.preprocessor.legal_move_indices(self.model.features_workspace(), n, batch.size)
+        picked = probs.cpu().numpy()[which, flat]
+        starts = np.concatenate([[0], np.cumsum(counts)[:-1]])
+        sums = np.add.reduceat(picked, np.minimum(starts, max(len(picked) - 1, 0))) if len(picked) else np.zeros(n, np.float32)
+        return which, flat, counts, picked / np.repeat(sums, counts)
+
     def batch_eval_state(self, states, moves_lists=None):
         """Given a list of states (or a BatchedGameState), evaluates them all at once.
         Returns a parallel list of move distributions as in eval_state (policy.py:27-52).
@@ -43,19 +55,15 @@ class CNNPolicy(NeuralNetBase):
             if not all([st.size == state_size for st in states]):
                 raise ValueError("all states must have the same size")
             batch = BatchedGameState.from_states(states)
-        probs = self.model.eval_batch_device(batch, self.preprocessor.plane_src)
         if not moves_lists:
             # all legal moves of every state: select and renormalise in one vectorised pass
-            which, flat, counts = self.preprocessor.legal_move_indices(self.model.features_workspace(), n_states, state_size)
-            network_output = probs.cpu().numpy()
-            picked = network_output[which, flat]
-            starts = np.concatenate([[0], np.cumsum(counts)[:-1]])
-            sums = np.add.reduceat(picked, np.minimum(starts, max(len(picked) - 1, 0))) if len(picked) else np.zeros(n_states, np.float32)
-            picked = (picked / np.repeat(sums, counts)).tolist()
+            _, flat, counts, picked = self.eval_arrays(batch)
+            picked = picked.tolist()
             points = _points(state_size)
             moves = [points[p] for p in flat.tolist()]
             ends = np.cumsum(counts).tolist()
             return [list(zip(moves[e - c:e], picked[e - c:e])) for e, c in zip(ends, counts.tolist())]
+        probs = self.model.eval_batch_device(batch, self.preprocessor.plane_src)
         network_output = probs.cpu().numpy()
         results = [None] * n_states
         for i in range(n_states):

@@ -12,6 +12,7 @@ import torch
 from . import _cabi
 
 STATE_WORDS = 192
+AGELESS_WORD = 5 * 32 + 8          # meta plane words 8..26 (include/rocalphago_b200.h)
 PASS_MOVE = None
 
 
@@ -207,6 +208,15 @@ class BatchedGameState(object):
             _cabi.check(_cabi.lib().rag_do_move(_ptr(self.packed), len(self), self.size, _ptr(mv), _ptr(status),
                                                 _stream()))
         return status
+
+    def forget_ages(self):
+        """What GameState.copy() does to stone_ages (go.py:186-217 does not copy them): every stone on
+        the board loses its age -- it is in no turns_since plane and later moves do not age it -- while
+        stones played from here on age as usual.  In place; returns self."""
+        stones = self.packed[:, 0:32] | self.packed[:, 32:64]
+        self.packed[:, 64:160] = 0
+        self.packed[:, AGELESS_WORD:AGELESS_WORD + 24] = stones[:, :24]
+        return self
 
     def to_arrays(self):
         """(board, age (saturated at 7), ko, player) numpy arrays."""

@@ -39,6 +39,10 @@ extern "C" int hostsim_features(int n, int S, const int8_t* board, const int16_t
         uint32_t planes[kNumPlanes * 32];
         memset(planes, 0, sizeof planes);
         Analysis A = bb_features(g, own, opp, a0, a1, a2, ko_q, planes, *est, bb_zero());
+        for (int x = 0; x < S; x++)                            // stones without an age are in no turns_since plane
+            for (int y = 0; y < S; y++)
+                if (board[(size_t)b * np + x * S + y] != 0 && age[(size_t)b * np + x * S + y] < 0)
+                    for (int k = 0; k < 8; k++) planes[(kPlaneTurnsSince + k) * 32 + x] &= ~(1u << y);
         BB cand_cap = A.legal & bb_nbrs(A.opp_lib2, g);
         BB cand_esc = A.legal & bb_nbrs(A.own_atari, g);
         if (stats) { stats[0] += bb_count(cand_cap); stats[1] += bb_count(cand_esc); }

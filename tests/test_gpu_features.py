@@ -213,3 +213,26 @@ def test_module_level_feature_functions_and_their_maximum_argument():
     assert np.array_equal(P.FEATURES["ones"]["function"](v), np.ones((1, 19, 19)))
     assert np.array_equal(P.FEATURES["zeros"]["function"](v), np.zeros((1, 19, 19)))
     assert P.Preprocess(["board", "liberties"]).processors == [P.get_board, P.get_liberties]
+
+
+def test_copied_states_without_ages_and_forget_ages():
+    """Stones with stone_ages -1 (what GameState.copy() leaves, go.py:186-217): planes against the
+    reference's, pack/unpack round trip, and do_move keeping such stones ageless while new ones age."""
+    z = np.load(os.path.join(gu.GOLDEN, "features_copied_states.npz"))
+    shape = tuple(int(v) for v in z["planes_shape"])
+    want = np.unpackbits(z["planes"])[:int(np.prod(shape))].reshape(shape)
+    feats = [str(f) for f in z["feature_list"]]
+    batch = BatchedGameState.from_arrays(z["board"], z["age"], z["ko"], z["player"])
+    assert np.array_equal(Preprocess(feats).to_device(batch).cpu().numpy(), want)
+    b, a, ko, pl = batch.to_arrays()
+    assert np.array_equal(a, np.where(z["age"] < 0, -1, np.minimum(z["age"], 7))) and np.array_equal(b, z["board"])
+    # forget_ages on the original positions + the recorded moves == the reference's copy() + do_move
+    g = gu.load_features("features_sgf.npz")
+    rows = z["source_rows"]
+    orig = BatchedGameState.from_arrays(g["board"][rows], g["age"][rows], g["ko"][rows], g["player"][rows]).forget_ages()
+    for step in range(4):
+        mv = z["played"][:, step]
+        keep = orig.packed.clone()
+        orig.do_move(np.where(mv >= 0, mv, -1))
+        orig.packed = torch.where(torch.as_tensor(mv >= 0, device=orig.device)[:, None], orig.packed, keep)
+    assert np.array_equal(Preprocess(feats).to_device(orig).cpu().numpy(), want)

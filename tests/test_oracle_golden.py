@@ -1,5 +1,7 @@
 """Pins oracle/go_oracle.c to the reference: it must reproduce every fixture that
 oracle/make_golden.py recorded from the reference's own Python (CPU only)."""
+import os
+
 import numpy as np
 import pytest
 
@@ -122,3 +124,17 @@ def test_oracle_superko_matches_reference_games_played_with_enforce_superko():
         off = dict(g["sk"], enforce=np.zeros(len(plain), np.int32))
         assert np.array_equal(go_oracle.features_superko(g["board"], g["age"], g["ko"], g["player"], off, feats), plain)
     assert changed >= 150 and ladder_changed >= 40
+
+
+def test_copied_states_have_no_ages_on_old_stones():
+    """GameState.copy() drops stone_ages (go.py:186-217): golden planes of copies with 0-4 moves played on
+    them (oracle/make_golden_copy.py), against the oracle and the host model of the device code."""
+    from tests import hostsim
+    z = np.load(os.path.join(gu.GOLDEN, "features_copied_states.npz"))
+    shape = tuple(int(v) for v in z["planes_shape"])
+    want = np.unpackbits(z["planes"])[:int(np.prod(shape))].reshape(shape)
+    assert ((z["age"] < 0) & (z["board"] != 0)).sum() > 5000
+    got = go_oracle.features(z["board"], z["age"], z["ko"], z["player"], [str(f) for f in z["feature_list"]])
+    assert np.array_equal(got, want)
+    got2, _ = hostsim.features49(z["board"], z["age"], z["ko"], z["player"])
+    assert np.array_equal(got2, want)
