@@ -282,7 +282,13 @@ def run_gpu(args):
 
     # ---- end to end with host buffers: pinned packed states -> H2D -> features -> net -> D2H, every step;
     #      the caller collects each result (on the host) as late as the pipeline allows (slots - 1 steps behind)
-    for i in range(2):
+    #      -- through a pipeline that replays its stages as CUDA graphs (host cost per step 0.45 -> 0.06 ms, which
+    #      matters when eight ranks share the host's cores); per-layer profiling events cannot be captured, so off
+    _cabi.check(L.rag_net_set_profiling(h, 0))
+    if args.e2e_graphs:
+        pipe.drain()
+        pipe = EvalPipeline(net, n, device=dev, value_net=vnet, slots=args.slots, graphs=True)
+    for i in range(2 * pipe.nslots + 1):
         pipe.submit(host_in[i % pool], to_host=True)
     pipe.drain()
     barrier()
@@ -498,6 +504,7 @@ def main():
     ap.add_argument("--serial", action="store_true", help="also time the single-stream rag_eval_batch step")
     ap.add_argument("--conv-pair", type=int, default=0, help="0: one CTA per tile; 1: CTA pairs (cta_group::2)")
     ap.add_argument("--no-pipeline", action="store_true", help="debug: skip the pipelined passes")
+    ap.add_argument("--e2e-graphs", type=int, default=1, help="1: the end-to-end pass replays each pipeline stage as a CUDA graph")
     ap.add_argument("--slots", type=int, default=None, help="batches in flight in the pipeline (default: 2, or 4 below 2048 positions)")
     args = ap.parse_args()
     if args.impl == "reference":
