@@ -943,9 +943,9 @@ int rag_features_analyze(const uint32_t* d_states, int n, int size, int with_lad
     if (n < 0 || (n > 0 && (!d_states || !d_workspace))) return fail(RAG_EINVAL, "null argument");
     if (int rc = check_size(size)) return rc;
     if (n > kMaxPositionsPerLaunch) return fail(RAG_EUNSUPPORTED, "n = %d exceeds %d positions per call", n, kMaxPositionsPerLaunch);
+    if (n == 0) return RAG_OK;
     if (workspace_bytes_given < workspace_bytes(n))
         return fail(RAG_ENOMEM, "workspace has %zu bytes, %zu needed for n = %d", workspace_bytes_given, workspace_bytes(n), n);
-    if (n == 0) return RAG_OK;
     cudaStream_t s = (cudaStream_t)stream;
     if (int rc = match_conv_carveout()) return rc;
     Workspace ws = carve(d_workspace, n);
@@ -976,9 +976,9 @@ int rag_features_ladders(const uint32_t* d_states, int n, int size, void* d_work
     if (n < 0 || (n > 0 && (!d_states || !d_workspace))) return fail(RAG_EINVAL, "null argument");
     if (int rc = check_size(size)) return rc;
     if (n > kMaxPositionsPerLaunch) return fail(RAG_EUNSUPPORTED, "n = %d exceeds %d positions per call", n, kMaxPositionsPerLaunch);
+    if (n == 0) return RAG_OK;
     if (workspace_bytes_given < workspace_bytes(n))
         return fail(RAG_ENOMEM, "workspace has %zu bytes, %zu needed for n = %d", workspace_bytes_given, workspace_bytes(n), n);
-    if (n == 0) return RAG_OK;
     if (int rc = match_conv_carveout()) return rc;
     Workspace ws = carve(d_workspace, n);
     int dev = 0, sms = 148;
@@ -1001,9 +1001,9 @@ int rag_features_analyze_superko(const uint32_t* d_states, int n, int size, int 
     if (int rc = check_size(size)) return rc;
     if (with_ladders != 0 && with_ladders != 1) return fail(RAG_EINVAL, "with_ladders must be 0 or 1 here");
     if (n > kMaxPositionsPerLaunch) return fail(RAG_EUNSUPPORTED, "n = %d exceeds %d positions per call", n, kMaxPositionsPerLaunch);
+    if (n == 0) return RAG_OK;
     if (workspace_bytes_given < workspace_bytes(n))
         return fail(RAG_ENOMEM, "workspace has %zu bytes, %zu needed for n = %d", workspace_bytes_given, workspace_bytes(n), n);
-    if (n == 0) return RAG_OK;
     cudaStream_t s = (cudaStream_t)stream;
     Workspace ws = carve(d_workspace, n);
     SuperkoArgs a;
