@@ -37,6 +37,7 @@ sys.path.insert(0, ROOT)
 METRIC = "positions/sec: 48-plane features + policy CNN fwd, 19x19"
 FLOP_3X3 = 2 * 361 * 192 * 192 * 9            # per position, one 3x3 192->192 layer
 FLOP_POLICY = 2_801_452_416                    # per position, whole 13x192 policy
+ISSUED = {"fp16": 1.0, "bf16": 1.0, "fp16c32": 4.0 / 3.0, "fp16c64": 5.0 / 3.0, "fp16x3": 3.0}   # MMA work per algorithmic flop, 3x3 layers
 FEATURE_BYTES = 17_568                         # per position, packed state in + 48x361 u8 out
 
 
@@ -102,15 +103,17 @@ def _cpu_features_worker(args):
     return go_oracle.features(b, a, ko, pl, go_oracle.DEFAULT_FEATURES)
 
 
-def cpu_path(n_positions, cores, seed=99, pool=None):
+def cpu_path(n_positions, cores, seed=99, pool=None, weights=None, keep=False):
     """The reference's serial features -> forward (policy.py:42-45) in its CPU port: C oracle
     feature planes on `cores` processes, then the torch fp32 forward on `cores` threads.
-    Returns (seconds_features, seconds_forward)."""
+    Returns (seconds_features, seconds_forward) and, with keep=True, the positions and the
+    probabilities (the checker's side of the bench line's `parity` entry)."""
     import multiprocessing as mp
     from oracle import cnn_oracle, go_oracle
     b, a, ko, pl = go_oracle.random_playouts(n_positions, size=19, seed=seed)
     specs = cnn_oracle.layer_specs(input_dim=48, layers=12, filters_per_layer=192)
-    weights = cnn_oracle.uniform_weights(specs, 48, 19, seed=1)
+    if weights is None:
+        weights = cnn_oracle.uniform_weights(specs, 48, 19, seed=1)
     chunks = [(b[i::cores], a[i::cores], ko[i::cores], pl[i::cores]) for i in range(cores) if len(b[i::cores])]
     own_pool = pool is None
     if own_pool:
@@ -122,11 +125,14 @@ def cpu_path(n_positions, cores, seed=99, pool=None):
     planes = np.concatenate(parts, axis=0)
     cnn_oracle.forward(weights, planes[:2], specs, threads=cores)
     t2 = time.time()
+    probs = []
     for i in range(0, len(planes), 1024):               # bounded activations: 1,024 positions per forward call
-        cnn_oracle.forward(weights, planes[i:i + 1024], specs, threads=cores)
+        probs.append(cnn_oracle.forward(weights, planes[i:i + 1024], specs, threads=cores))
     t3 = time.time()
     if own_pool:
         pool.close()
+    if keep:
+        return t1 - t0, t3 - t2, (b, a, ko, pl, np.concatenate(probs))
     return t1 - t0, t3 - t2
 
 
@@ -370,13 +376,16 @@ def run_gpu(args):
                          "ms_per_launch": k3,
                          # dram__bytes_read.sum + dram__bytes_write.sum per launch from the ncu --set full capture
                          # of this kernel at batch 4096 (profiles/r1_final_ncu_summary.md); scales with the batch
-                         "traffic": None if args.dtype == "fp16x3" else
+                         "traffic": None if args.dtype not in ("fp16", "bf16") else
                                     {"bytes": int(1.0892e9 * n / 4096), "algorithmic_bytes": int(n * 361 * 192 * 2 * 2),
                                      "source": "profiles/r1_final_ncu_summary.md"},
+                         "issued_over_algorithmic": ISSUED[args.dtype],
+                         "issued_tflops": achieved * ISSUED[args.dtype],
                          "note": "CUDA events recorded by the library on the launching stream, sampled %d time(s) inside "
                                  "the timed region while the next batch's feature kernels share the SMs" % samples
-                                 + ("; fp16x3 issues three MMAs per algorithmic product, so the achievable fraction is 1/3"
-                                    if args.dtype == "fp16x3" else "")},
+                                 + ("; `achieved` counts ALGORITHMIC flops (2*361*192*192*9 per position): this precision issues "
+                                    "%.2fx as many MMAs (extra K steps for the corrected channels), so the tensor pipe runs at "
+                                    "`issued_tflops`" % ISSUED[args.dtype] if ISSUED[args.dtype] > 1 else "")},
             "stage_ms": {"conv_layer1": float(layer_ms[0]), "conv_3x3_mean": k3, "conv_all": float(layer_ms.sum()),
                          "pipelined_step": dev_ms / K, "serial_step": serial_ms},
             "whole_net_tflops": FLOP_POLICY * n / (float(layer_ms.sum()) / 1e3) / 1e12,
@@ -386,7 +395,19 @@ def run_gpu(args):
         if world == 1 and not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
             sample = args.cpu_sample
-            tf, tn = cpu_path(sample, cores)
+            if args.workload == "policy":
+                # the same positions and weights through the device path, checked against the CPU forward just timed
+                tf, tn, (pb, pa, pko, ppl, want) = cpu_path(sample, cores, weights=model.get_weights(), keep=True)
+                chk = BatchedGameState.from_arrays(pb, pa, pko, ppl, device=dev)
+                got = np.concatenate([model.eval_batch_device(BatchedGameState(chk.packed[i:i + n].contiguous(), 19), plane_src).cpu().numpy()
+                                      for i in range(0, sample, n)])
+                miss = int((got.argmax(1) != want.argmax(1)).sum())
+                line["parity"] = {"dtype": args.dtype, "top1": 1.0 - miss / float(sample), "miss": miss, "n": sample,
+                                  "max_abs": float(np.abs(got - want).max()), "gate": {"top1": 0.995, "max_abs": 2e-3},
+                                  "against": "the fp32 CPU forward timed for cpu_baseline, same positions and weights; "
+                                             "outside the timed region (the 3-seed, 24,576-position gate is tests/test_gpu_network.py)"}
+            else:
+                tf, tn = cpu_path(sample, cores)
             line["cpu_baseline"] = {"value": sample / (tf + tn), "unit": "positions/s", "cores": cores, "kind": "port",
                                     "sample": "%d random-playout positions once: C feature oracle on %d processes %.2fs "
                                               "(%.0f pos/s) + torch fp32 13x192 forward on %d threads %.2fs (%.0f pos/s)"
@@ -493,7 +514,10 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--batch", type=int, default=4096, help="positions per GPU per step")
     ap.add_argument("--pool", type=int, default=4, help="distinct input batches cycled through")
-    ap.add_argument("--dtype", default="fp16", choices=["fp16", "bf16", "fp16x3"], help="operand precision of the convolutions (fp16x3: split operands, fp32-like results, a third of the speed)")
+    ap.add_argument("--dtype", default="fp16c32", choices=["fp16c32", "fp16c64", "fp16", "bf16", "fp16x3"],
+                    help="operand precision of the convolutions: fp16c32 (default; fp16 with the 32 most energetic input channels of "
+                         "layers 2.. corrected by their fp16 remainders -- holds the 99.5 %% top-1 gate), fp16 / bf16 (plain 16-bit "
+                         "operands, 1.3x faster, at / below the gate on random-init weights), fp16x3 (fp32-like, 3x the MMA work)")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--cpu-sample", type=int, default=8192, help="positions the CPU port is timed on (~15 s on 16 cores)")
     ap.add_argument("--ref-sample", type=int, default=256)

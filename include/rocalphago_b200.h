@@ -90,6 +90,13 @@ int rag_unpack_states(int n, int size, const uint32_t* h_packed, int8_t* h_board
  * hi*lo with fp32 accumulation -- fp32-like results at a third of the speed.  For callers that need the
  * reference's fp32 arg-max on nearly flat outputs (random-init networks); not for residual networks. */
 #define RAG_DTYPE_FP16X3 2
+/* fp16 operands, with the split above applied only to the 32 (64) input channels of every layer after
+ * the first that are expected to carry the most energy (filters are reordered at load time so that
+ * these come first): one (two) extra 64-deep K step(s) per filter tap, i.e. 4/3 (5/3) of the fp16
+ * work for a 192-filter layer, for 0.6x (0.45x) of fp16's rounding noise in the logits.  The mode
+ * that keeps the reference's fp32 arg-max on >= 99.5 % of random-init positions at near-fp16 speed. */
+#define RAG_DTYPE_FP16C32 3
+#define RAG_DTYPE_FP16C64 4
 
 /* bytes of scratch rag_features / rag_features_analyze need for n positions */
 size_t rag_features_workspace_bytes(int n);
@@ -236,7 +243,7 @@ typedef struct rag_net_desc {
     int widths[RAG_MAX_LAYERS];      /* filter_width_K (odd, <= 7)          policy.py:108-110 */
     int head;                        /* RAG_HEAD_POLICY / RAG_HEAD_VALUE    */
     int dense_units;                 /* value head: 256                     value.py:27   */
-    int dtype;                       /* RAG_DTYPE_BF16 / RAG_DTYPE_FP16 operands, or RAG_DTYPE_FP16X3 */
+    int dtype;                       /* RAG_DTYPE_BF16 / RAG_DTYPE_FP16 operands, or a split mode: FP16X3, FP16C32, FP16C64 */
     int kernel_flip;                 /* 1: Theano semantics (true convolution, the reference's
                                         pinned backend); 0: cross-correlation (TensorFlow) */
     int resnet;                      /* 1: ResnetPolicy (policy.py:141-271): convolution 1 is linear, every
@@ -258,6 +265,11 @@ int rag_net_destroy(rag_net* net);
  * Host float arrays; copies them to the device (synchronous). */
 int rag_net_num_weight_arrays(const rag_net* net);
 int rag_net_load_weights(rag_net* net, const float* const* h_arrays, int n_arrays);
+/* Optional, before rag_net_load_weights, for RAG_DTYPE_FP16C32 / FP16C64: which canonical feature
+ * plane every input plane is (the list rag_eval_batch is given; Preprocess's feature order,
+ * preprocessing.py:266-285).  Only sharpens the ranking of channels by expected energy -- results
+ * are valid without it; without it every input plane counts the same. */
+int rag_net_set_input_planes(rag_net* net, const int32_t* h_plane_src, int F);
 
 size_t rag_net_workspace_bytes(const rag_net* net, int n);
 /* layout of the input the *_rows entry expects: rag_conv_rows(n, board) rows of `channels` */

@@ -68,6 +68,7 @@ def lib():
         "rag_net_destroy": (i32, [vp]),
         "rag_net_num_weight_arrays": (i32, [vp]),
         "rag_net_load_weights": (i32, [vp, vp, i32]),
+        "rag_net_set_input_planes": (i32, [vp, vp, i32]),
         "rag_net_workspace_bytes": (sz, [vp, i32]),
         "rag_net_logits_offset": (sz, [vp, i32]),
         "rag_set_conv_pair": (i32, [i32]),

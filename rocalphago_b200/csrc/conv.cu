@@ -30,6 +30,7 @@
 #include <math.h>
 #include <stdlib.h>
 #include <string.h>
+#include <algorithm>
 #include <vector>
 
 namespace rag {
@@ -58,10 +59,14 @@ struct ConvParams {
     uint16_t* linear_out;         // [rows][N] or null
     const float* bn_scale;        // [S] (indexed by y, the reference's BatchNormalization axis) or null
     const float* bn_shift;
-    // split-operand mode (RAG_DTYPE_FP16X3): activation rows hold [hi | lo] halves, the K walk reads
-    // the A chunks [hi, lo, hi] against weights stored as [W_hi, W_hi, W_lo] (see rag_net_load_weights)
-    int a_wrap;                   // A chunk index = c < a_wrap ? c : c - a_wrap   (0: no wrap)
-    int split_out;                // mode 0: write fp16 hi and lo halves, row pitch 2 N
+    // split operands (RAG_DTYPE_FP16X3 / FP16C32 / FP16C64): besides the fp16 value `hi` of every channel an
+    // activation row carries lo = fp16(x - hi) of its first `lo_cols` channels; the K walk reads extra A
+    // chunks against extra weight columns so that those channels contribute hi.W_hi + lo.W_hi + hi.W_lo
+    // (layouts in rag_net_create / rag_net_load_weights)
+    unsigned long long a_map;     // 4 bits per K chunk: which 64-channel chunk of the A row it reads
+    int out_pitch;                // mode 0: channels per output row
+    int lo_cols;                  // mode 0: leading channels whose lo half is written at column N + c
+    int dup_hi;                   // mode 0: also copy hi of channels 0..31 to columns N + 32 .. N + 63
 };
 
 // ---- PTX wrappers ----------------------------------------------------------------------------
@@ -256,7 +261,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                             const uint32_t ph = (it / (uint32_t)p.stages) & 1u;
                             mbar_wait(empty_bar(s), ph ^ 1u);
                             const uint32_t sa = base + (uint32_t)s * stage_bytes;
-                            const int ca = (p.a_wrap && c >= p.a_wrap) ? c - p.a_wrap : c;    // split mode: [hi, lo, hi]
+                            const int ca = (int)((p.a_map >> (4 * c)) & 15ull);
                             // tensor dims are (C, y, x, board): y is the fast spatial index
                             if (kPair) {
                                 // both CTAs' bytes are counted on the leader's barrier
@@ -313,42 +318,14 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             mbar_wait(tfull_bar((int)a), aph);
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + a * (uint32_t)p.N;
-            if (p.mode == 0 && p.split_out) {
-                // x = hi + lo with both halves fp16: the next layer multiplies both by the weights
-                uint16_t* orow = reinterpret_cast<uint16_t*>(p.out) + row * (2 * p.N);
+            if (p.mode == 0) {
+                uint16_t* orow = reinterpret_cast<uint16_t*>(p.out) + row * p.out_pitch;
                 for (int c0 = 0; c0 < p.N; c0 += 32) {
                     uint32_t v[32];
                     tc_ld32(taddr + (uint32_t)c0, v);
                     tc_wait_ld();
-                    uint32_t hi[16], lo[16];
-                    #pragma unroll
-                    for (int j = 0; j < 16; j++) {
-                        float f0 = __uint_as_float(v[2 * j]) + s_bias[c0 + 2 * j];
-                        float f1 = __uint_as_float(v[2 * j + 1]) + s_bias[c0 + 2 * j + 1];
-                        if (p.relu) { f0 = fmaxf(f0, 0.f); f1 = fmaxf(f1, 0.f); }
-                        __half2 h = __floats2half2_rn(f0, f1);
-                        const float2 back = __half22float2(h);
-                        __half2 l = __floats2half2_rn(f0 - back.x, f1 - back.y);
-                        hi[j] = *reinterpret_cast<uint32_t*>(&h);
-                        lo[j] = *reinterpret_cast<uint32_t*>(&l);
-                    }
-                    if (real) {
-                        uint4* dh = reinterpret_cast<uint4*>(orow + c0);
-                        uint4* dl = reinterpret_cast<uint4*>(orow + p.N + c0);
-                        #pragma unroll
-                        for (int j = 0; j < 4; j++) {
-                            dh[j] = make_uint4(hi[4 * j], hi[4 * j + 1], hi[4 * j + 2], hi[4 * j + 3]);
-                            dl[j] = make_uint4(lo[4 * j], lo[4 * j + 1], lo[4 * j + 2], lo[4 * j + 3]);
-                        }
-                    }
-                }
-            } else if (p.mode == 0) {
-                uint16_t* orow = reinterpret_cast<uint16_t*>(p.out) + row * p.N;
-                for (int c0 = 0; c0 < p.N; c0 += 32) {
-                    uint32_t v[32];
-                    tc_ld32(taddr + (uint32_t)c0, v);
-                    tc_wait_ld();
-                    uint32_t packed[16];
+                    const bool with_lo = c0 < p.lo_cols;          // x = hi + lo, both fp16: the next layer multiplies both
+                    uint32_t packed[16], lo[16];
                     #pragma unroll
                     for (int j = 0; j < 16; j++) {
                         float f0 = __uint_as_float(v[2 * j]) + s_bias[c0 + 2 * j];
@@ -360,6 +337,11 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         } else {
                             __half2 h = __floats2half2_rn(f0, f1);
                             packed[j] = *reinterpret_cast<uint32_t*>(&h);
+                            if (with_lo) {
+                                const float2 back = __half22float2(h);
+                                __half2 l = __floats2half2_rn(f0 - back.x, f1 - back.y);
+                                lo[j] = *reinterpret_cast<uint32_t*>(&l);
+                            }
                         }
                     }
                     if (real) {
@@ -367,6 +349,18 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         #pragma unroll
                         for (int j = 0; j < 4; j++)
                             dst[j] = make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
+                        if (with_lo) {
+                            uint4* dl = reinterpret_cast<uint4*>(orow + p.N + c0);
+                            #pragma unroll
+                            for (int j = 0; j < 4; j++)
+                                dl[j] = make_uint4(lo[4 * j], lo[4 * j + 1], lo[4 * j + 2], lo[4 * j + 3]);
+                            if (p.dup_hi) {
+                                uint4* dd = reinterpret_cast<uint4*>(orow + p.N + 32 + c0);
+                                #pragma unroll
+                                for (int j = 0; j < 4; j++)
+                                    dd[j] = make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
+                            }
+                        }
                     }
                 }
             } else if (p.mode == 1) {
@@ -586,8 +580,20 @@ static int round_up(int v, int m) { return (v + m - 1) / m * m; }
 
 struct Layer {
     int width, cin, cout, cin_pad, n_pad, taps;
-    int cin_store = 0;            // channels of this layer's input rows: cin_pad, or 2 * cin_pad ([hi | lo]) in split mode
-    int kdim = 0;                 // K extent of the weights per tap: cin_pad, or 3 * cin_pad ([W_hi | W_hi | W_lo])
+    // split operands: the first lo_in input channels come as hi + lo.  Input row / weight columns per tap:
+    //   lo_in = 0        [hi]                          [W_hi]
+    //   lo_in = cin_pad  [hi | lo]                     [W_hi | W_hi | W_lo]            (fp16x3; A chunks hi, lo, hi)
+    //   lo_in = 64       [hi | lo 0..63]               [W_hi | W_hi 0..63 | W_lo 0..63] (A chunks hi.., lo, hi chunk 0)
+    //   lo_in = 32       [hi | lo 0..31 | hi 0..31]    [W_hi | W_hi 0..31 | W_lo 0..31] (one extra chunk)
+    int lo_in = 0;
+    int cin_store = 0;            // channels of this layer's input rows
+    int kdim = 0;                 // K extent of the weights per tap
+    unsigned long long a_map = 0; // K chunk -> chunk of the input row, 4 bits each
+    std::vector<int> out_order;   // position j of this layer's output holds filter out_order[j] (energetic first)
+    CUtensorMap tmB, tmB_pair;    // weight tiles, encoded by rag_net_load_weights
+    struct ACache { const void* ptr; int n; CUtensorMap map; };
+    std::vector<ACache> a_maps;   // im2col views of recently used input buffers
+    int a_next = 0;
     uint16_t* d_w = nullptr;      // [taps][n_pad][kdim]
     float* d_bias = nullptr;      // [n_pad]
     float* d_bn_scale = nullptr;  // residual nets: BatchNormalization applied to this layer's INPUT, [S] each
@@ -611,6 +617,9 @@ struct rag_net {
     float* d_dense2_w = nullptr;   // [D]
     float* d_dense2_b = nullptr;   // [1]
     bool split = false;            // RAG_DTYPE_FP16X3: fp16 operands, every product formed as hi*hi + lo*hi + hi*lo
+    int corr = 0;                  // RAG_DTYPE_FP16C32 / FP16C64: the same for the 32 / 64 most energetic input channels of layers 2..
+    int max_pitch = 0;             // widest activation row any layer writes (channels)
+    std::vector<float> in_density; // expected mean of every input plane (rag_net_set_input_planes), for the channel ranking
     int op_dtype = RAG_DTYPE_FP16; // what the tensor cores are fed
     bool loaded = false;
     bool profiling = false;        // record a CUDA event around every convolution launch
@@ -654,7 +663,7 @@ static NetBuffers carve_net(const rag_net* net, int n, void* ws, bool with_input
     NetBuffers b;
     auto al = [](size_t v) { return (v + 1023) / 1024 * 1024; };
     const long long rows = dense_rows(n, net->desc.board);
-    b.act_bytes = al((size_t)rows * net->max_c * 2 * (net->split ? 2 : 1));
+    b.act_bytes = al((size_t)rows * net->max_pitch * 2);
     b.in_bytes = with_input ? al((size_t)rows * net->layers[0].cin_store * 2) : 0;
     size_t logits_bytes = al((size_t)n * net->desc.board * net->desc.board * 4);
     char* p = (char*)ws;
@@ -673,12 +682,33 @@ static NetBuffers carve_net(const rag_net* net, int n, void* ws, bool with_input
     return b;
 }
 
+// the im2col view of an input buffer: encoded once per (buffer, batch size) and kept with the layer
+static int input_map(rag_net* net, Layer& ly, const void* ptr, int n, const CUtensorMap** out) {
+    for (auto& e : ly.a_maps)
+        if (e.ptr == ptr && e.n == n) { *out = &e.map; return RAG_OK; }
+    Layer::ACache e;
+    e.ptr = ptr; e.n = n;
+    if (int rc = make_map_im2col(&e.map, ptr, n, net->desc.board, ly.cin_store, ly.width, net->op_dtype)) return rc;
+    if (ly.a_maps.size() < 16) { ly.a_maps.push_back(e); *out = &ly.a_maps.back().map; }
+    else { ly.a_maps[ly.a_next] = e; *out = &ly.a_maps[ly.a_next].map; ly.a_next = (ly.a_next + 1) % 16; }
+    return RAG_OK;
+}
+
+static int conv_smem_limit(bool pair, size_t smem) {
+    static size_t set[2] = {0, 0};      // largest dynamic shared memory size already granted to each kernel
+    if (smem <= set[pair]) return RAG_OK;
+    if (pair) RAG_CUDA_CHECK(cudaFuncSetAttribute(conv_umma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    else RAG_CUDA_CHECK(cudaFuncSetAttribute(conv_umma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    set[pair] = smem;
+    return RAG_OK;
+}
+
 static int run_layers(rag_net* net, const uint16_t* d_in, int n, float* d_out, const NetBuffers& b, cudaStream_t s) {
     const int S = net->desc.board, L = (int)net->layers.size();
     int lin_cur = 0;
     const uint16_t* cur = d_in;
     for (int l = 0; l < L; l++) {
-        const Layer& ly = net->layers[l];
+        Layer& ly = net->layers[l];
         const bool last = l == L - 1;
         uint16_t* dst = last ? nullptr : b.act[l & 1];
 
@@ -688,7 +718,11 @@ static int run_layers(rag_net* net, const uint16_t* d_in, int n, float* d_out, c
         p.tiles = (int)((p.rows + kTileM - 1) / kTileM);
         p.width = ly.width; p.kchunks = ly.kdim / kChunkK; p.N = ly.n_pad;
         p.stages = pick_stages(ly.n_pad); p.dtype = net->op_dtype;
-        if (net->split) { p.a_wrap = 2 * ly.cin_pad / kChunkK; p.split_out = 1; }
+        p.a_map = ly.a_map;
+        if (!last) {
+            const Layer& nx = net->layers[l + 1];
+            p.out_pitch = nx.cin_store; p.lo_cols = nx.lo_in; p.dup_hi = nx.lo_in == 32;
+        }
         p.S = S; p.n = n;
         p.mode = last ? 1 : 0; p.relu = 1;
         p.bias = ly.d_bias; p.head_w = net->d_head_w; p.head_b = net->head_b;
@@ -708,13 +742,12 @@ static int run_layers(rag_net* net, const uint16_t* d_in, int n, float* d_out, c
             p.tiles = (int)((p.rows + 2 * kTileM - 1) / (2 * kTileM));
             p.stages = pick_stages(ly.n_pad / 2);
         }
-        CUtensorMap tmA, tmB;
-        if (int rc = make_map_im2col(&tmA, cur, n, S, ly.cin_store, ly.width, net->op_dtype)) return rc;
-        if (int rc = make_map(&tmB, ly.d_w, (long long)ly.taps * ly.n_pad, ly.kdim, pair ? ly.n_pad / 2 : ly.n_pad, net->op_dtype)) return rc;
+        const CUtensorMap* tmA = nullptr;
+        if (int rc = input_map(net, ly, cur, n, &tmA)) return rc;
         if (net->profiling) RAG_CUDA_CHECK(cudaEventRecord(net->events[l], s));
         if (pair) {
             const size_t smem = conv_smem_bytes(ly.n_pad / 2, p.stages) + (size_t)ly.n_pad * 4;      // bias/head tables are N wide
-            RAG_CUDA_CHECK(cudaFuncSetAttribute(conv_umma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            if (int rc = conv_smem_limit(true, smem)) return rc;
             const int pairs = p.tiles < net->sms / 2 ? p.tiles : net->sms / 2;
             cudaLaunchConfig_t cfg;
             memset(&cfg, 0, sizeof cfg);
@@ -723,12 +756,12 @@ static int run_layers(rag_net* net, const uint16_t* d_in, int n, float* d_out, c
             attr[0].id = cudaLaunchAttributeClusterDimension;
             attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
             cfg.attrs = attr; cfg.numAttrs = 1;
-            RAG_CUDA_CHECK(cudaLaunchKernelEx(&cfg, conv_umma_kernel<true>, tmA, tmB, p));
+            RAG_CUDA_CHECK(cudaLaunchKernelEx(&cfg, conv_umma_kernel<true>, *tmA, ly.tmB_pair, p));
         } else {
             const size_t smem = conv_smem_bytes(ly.n_pad, p.stages);
-            RAG_CUDA_CHECK(cudaFuncSetAttribute(conv_umma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            if (int rc = conv_smem_limit(false, smem)) return rc;
             const int grid = p.tiles < net->sms ? p.tiles : net->sms;
-            conv_umma_kernel<false><<<grid, kConvThreads, smem, s>>>(tmA, tmB, p);
+            conv_umma_kernel<false><<<grid, kConvThreads, smem, s>>>(*tmA, ly.tmB, p);
         }
         RAG_CUDA_CHECK(cudaGetLastError());
         if (net->profiling && last) RAG_CUDA_CHECK(cudaEventRecord(net->events[L], s));
@@ -769,8 +802,8 @@ int rag_net_create(const rag_net_desc* desc, rag_net** out)
     if (desc->layers < 1 || desc->layers > RAG_MAX_LAYERS) return fail(RAG_EINVAL, "layers %d not in [1, %d]", desc->layers, RAG_MAX_LAYERS);
     if (desc->in_planes < 1 || desc->in_planes > 128) return fail(RAG_EUNSUPPORTED, "in_planes %d not in [1, 128]", desc->in_planes);
     if (desc->head != RAG_HEAD_POLICY && desc->head != RAG_HEAD_VALUE) return fail(RAG_EINVAL, "head %d", desc->head);
-    if (desc->dtype != RAG_DTYPE_BF16 && desc->dtype != RAG_DTYPE_FP16 && desc->dtype != RAG_DTYPE_FP16X3) return fail(RAG_EINVAL, "dtype %d", desc->dtype);
-    if (desc->dtype == RAG_DTYPE_FP16X3 && desc->resnet) return fail(RAG_EUNSUPPORTED, "split-operand precision is not available for residual networks");
+    if (desc->dtype < RAG_DTYPE_BF16 || desc->dtype > RAG_DTYPE_FP16C64) return fail(RAG_EINVAL, "dtype %d", desc->dtype);
+    if (desc->dtype >= RAG_DTYPE_FP16X3 && desc->resnet) return fail(RAG_EUNSUPPORTED, "split-operand precision is not available for residual networks");
     if (desc->dtype == RAG_DTYPE_FP16X3 && desc->in_planes > 64) return fail(RAG_EUNSUPPORTED, "split-operand precision takes at most 64 input planes (%d given)", desc->in_planes);
     if (desc->head == RAG_HEAD_VALUE && (desc->dense_units < 1 || desc->dense_units > 4096)) return fail(RAG_EINVAL, "dense_units %d", desc->dense_units);
     if (desc->resnet) {
@@ -782,6 +815,8 @@ int rag_net_create(const rag_net_desc* desc, rag_net** out)
     rag_net* net = new rag_net();
     net->desc = *desc;
     net->split = desc->dtype == RAG_DTYPE_FP16X3;
+    net->corr = desc->dtype == RAG_DTYPE_FP16C32 ? 32 : desc->dtype == RAG_DTYPE_FP16C64 ? 64 : 0;
+    net->in_density.assign(desc->in_planes, 0.25f);
     net->op_dtype = desc->dtype == RAG_DTYPE_BF16 ? RAG_DTYPE_BF16 : RAG_DTYPE_FP16;
     int cin = desc->in_planes;
     for (int l = 0; l < desc->layers; l++) {
@@ -790,9 +825,26 @@ int rag_net_create(const rag_net_desc* desc, rag_net** out)
         if (ly.width < 1 || ly.width > 7 || ly.width % 2 == 0) { delete net; return fail(RAG_EUNSUPPORTED, "filter_width_%d = %d (odd, <= 7 supported)", l + 1, ly.width); }
         if (ly.cout < 1 || ly.cout > 256) { delete net; return fail(RAG_EUNSUPPORTED, "filters_per_layer_%d = %d (<= 256 supported)", l + 1, ly.cout); }
         ly.cin_pad = round_up(cin, kChunkK); ly.n_pad = round_up(ly.cout, kChunkK); ly.taps = ly.width * ly.width;
-        ly.cin_store = net->split ? 2 * ly.cin_pad : ly.cin_pad; ly.kdim = net->split ? 3 * ly.cin_pad : ly.cin_pad;
+        // the network's input planes are taken as exact in fp16 (feature planes are 0/1), so the first
+        // layer of the FP16C modes has nothing to correct on its activation side
+        ly.lo_in = net->split ? ly.cin_pad : (l > 0 ? net->corr : 0);
+        const int nc = ly.cin_pad / kChunkK;
+        unsigned long long map = 0;
+        for (int c = 0; c < nc; c++) map |= (unsigned long long)c << (4 * c);
+        if (ly.lo_in == 0) { ly.cin_store = ly.cin_pad; ly.kdim = ly.cin_pad; }
+        else if (net->split) {
+            ly.cin_store = 2 * ly.cin_pad; ly.kdim = 3 * ly.cin_pad;
+            for (int c = 0; c < nc; c++) map |= (unsigned long long)(nc + c) << (4 * (nc + c)) | (unsigned long long)c << (4 * (2 * nc + c));
+        } else {
+            ly.cin_store = ly.cin_pad + 64; ly.kdim = ly.cin_pad + (ly.lo_in == 64 ? 128 : 64);
+            map |= (unsigned long long)nc << (4 * nc);            // [lo 0..63] or [lo 0..31 | hi 0..31]; then chunk 0 again
+        }
+        ly.a_map = map;
+        if (ly.kdim / kChunkK > 16 || ly.cin_store / kChunkK > 16) { delete net; return fail(RAG_EUNSUPPORTED, "layer %d has too many input channels for this precision mode", l + 1); }
         if (pick_stages(ly.n_pad) < 2) { delete net; return fail(RAG_EUNSUPPORTED, "layer %d does not fit shared memory", l + 1); }
         if (ly.n_pad > net->max_c) net->max_c = ly.n_pad;
+        if (l > 0 && ly.cin_store > net->max_pitch) net->max_pitch = ly.cin_store;
+        if (ly.n_pad > net->max_pitch) net->max_pitch = ly.n_pad;
         net->layers.push_back(ly);
         cin = ly.cout;
     }
@@ -833,6 +885,8 @@ int rag_net_load_weights(rag_net* net, const float* const* h_arrays, int n_array
     RAG_CUDA_CHECK(cudaSetDevice(net->device));
     const int dtype = net->op_dtype, L = (int)net->layers.size(), P = net->desc.board * net->desc.board;
     int ai = 0;
+    std::vector<float> mean_in = net->in_density;     // expected mean of every input channel, original order
+    std::vector<int> in_order;                        // input position -> the producing layer's filter (empty: identity)
     for (int l = 0; l < L; l++) {
         Layer& ly = net->layers[l];
         if (net->desc.resnet && l > 0) {
@@ -850,37 +904,61 @@ int rag_net_load_weights(rag_net* net, const float* const* h_arrays, int n_array
         const float* W = h_arrays[ai++];      // (cout, cin, kh, kw)  Keras 'th' kernel layout
         const float* bsrc = h_arrays[ai++];   // (cout,)
         const int k = ly.width;
+        // Which output channels will carry the most energy?  ReLU activations are non-negative, so a
+        // filter's mean response to the mean input tells: rank the filters by it and put the energetic
+        // ones first when the next layer corrects its leading input channels (FP16C32 / FP16C64).
+        std::vector<float> resp(ly.cout);
+        for (int co = 0; co < ly.cout; co++) {
+            double r = bsrc[co];
+            for (int ci = 0; ci < ly.cin; ci++) {
+                double sw = 0;
+                for (int t = 0; t < k * k; t++) sw += W[((size_t)co * ly.cin + ci) * k * k + t];
+                r += sw * mean_in[ci];
+            }
+            resp[co] = (float)r;
+        }
+        ly.out_order.resize(ly.cout);
+        for (int co = 0; co < ly.cout; co++) ly.out_order[co] = co;
+        if (l + 1 < L && net->corr)
+            std::stable_sort(ly.out_order.begin(), ly.out_order.end(), [&](int a, int b) { return resp[a] > resp[b]; });
         std::vector<uint16_t> w((size_t)ly.taps * ly.n_pad * ly.kdim, 0);
         for (int i = 0; i < k; i++)
             for (int j = 0; j < k; j++) {
                 // tap (i, j) reads in[x + i - pad, y + j - pad].  Theano's conv2d is a true
                 // convolution, i.e. a correlation with the kernel rotated by 180 degrees.
                 const int si = net->desc.kernel_flip ? k - 1 - i : i, sj = net->desc.kernel_flip ? k - 1 - j : j;
-                for (int co = 0; co < ly.cout; co++)
-                    for (int ci = 0; ci < ly.cin; ci++) {
+                for (int jo = 0; jo < ly.cout; jo++)
+                    for (int ji = 0; ji < ly.cin; ji++) {
+                        const int co = ly.out_order[jo], ci = in_order.empty() ? ji : in_order[ji];
                         const float v = W[(((size_t)co * ly.cin + ci) * k + si) * k + sj];
-                        uint16_t* row = &w[((size_t)(i * k + j) * ly.n_pad + co) * ly.kdim];
-                        row[ci] = to16(v, dtype);
-                        if (net->split) {
-                            // the K walk reads activations as [hi, lo, hi]: weights [W_hi, W_hi, W_lo]
-                            // give hi*W_hi + lo*W_hi + hi*W_lo; the lo*lo term (2^-22 relative) is dropped
-                            const __half h = __float2half_rn(v);
-                            row[ly.cin_pad + ci] = row[ci];
-                            row[2 * ly.cin_pad + ci] = to16(v - __half2float(h), dtype);
+                        uint16_t* row = &w[((size_t)(i * k + j) * ly.n_pad + jo) * ly.kdim];
+                        row[ji] = to16(v, dtype);
+                        if (ji < ly.lo_in) {
+                            // the extra K chunks pair lo(x) with W_hi and hi(x) with W_lo; the lo.lo term (2^-22 relative) is dropped
+                            const uint16_t lo = to16(v - __half2float(__float2half_rn(v)), dtype);
+                            if (net->split) { row[ly.cin_pad + ji] = row[ji]; row[2 * ly.cin_pad + ji] = lo; }
+                            else if (ly.lo_in == 64) { row[ly.cin_pad + ji] = row[ji]; row[ly.cin_pad + 64 + ji] = lo; }
+                            else { row[ly.cin_pad + ji] = row[ji]; row[ly.cin_pad + 32 + ji] = lo; }
                         }
                     }
             }
         std::vector<float> bias(ly.n_pad, 0.f);
-        for (int co = 0; co < ly.cout; co++) bias[co] = bsrc[co];
+        for (int jo = 0; jo < ly.cout; jo++) bias[jo] = bsrc[ly.out_order[jo]];
         if (int rc = upload(&ly.d_w, w)) return rc;
         if (int rc = upload(&ly.d_bias, bias)) return rc;
+        if (int rc = make_map(&ly.tmB, ly.d_w, (long long)ly.taps * ly.n_pad, ly.kdim, ly.n_pad, dtype)) return rc;
+        if (ly.n_pad % 32 == 0)
+            if (int rc = make_map(&ly.tmB_pair, ly.d_w, (long long)ly.taps * ly.n_pad, ly.kdim, ly.n_pad / 2, dtype)) return rc;
+        mean_in.assign(ly.cout, 0.f);
+        for (int co = 0; co < ly.cout; co++) mean_in[co] = resp[co] > 0.f ? resp[co] : 0.f;
+        in_order = ly.out_order;
     }
     {   // the 1x1 convolution to one plane (policy.py:125-130, value.py:23-25): W (1, cin, 1, 1), b (1,)
         const Layer& ly = net->layers[L - 1];
         const float* W = h_arrays[ai++];
         const float* bsrc = h_arrays[ai++];
         std::vector<float> hw(ly.n_pad, 0.f);
-        for (int c = 0; c < ly.cout; c++) hw[c] = W[c];
+        for (int c = 0; c < ly.cout; c++) hw[c] = W[ly.out_order[c]];
         if (int rc = upload(&net->d_head_w, hw)) return rc;
         net->head_b = bsrc[0];
     }
@@ -906,6 +984,27 @@ size_t rag_net_workspace_bytes(const rag_net* net, int n)
 {
     if (!net || n <= 0) return 0;
     return carve_net(net, n, nullptr, true).total;
+}
+
+// Mean of every canonical feature plane (include/rocalphago_b200.h numbering) over random-playout
+// 19x19 positions -- only used to rank channels by expected energy, never in the arithmetic.
+static const float kPlaneDensity[RAG_NUM_PLANES] = {
+    0.26f, 0.26f, 0.48f, 1.00f, 0.003f, 0.003f, 0.003f, 0.003f, 0.003f, 0.003f, 0.003f, 0.50f,
+    0.052f, 0.071f, 0.085f, 0.074f, 0.048f, 0.040f, 0.029f, 0.117f,
+    0.457f, 0.009f, 0.002f, 0.001f, 0.0005f, 0.0003f, 0.0002f, 0.0006f,
+    0.013f, 0.002f, 0.001f, 0.0006f, 0.0004f, 0.0003f, 0.0002f, 0.0007f,
+    0.018f, 0.047f, 0.107f, 0.155f, 0.041f, 0.041f, 0.020f, 0.041f,
+    0.014f, 0.007f, 0.466f, 0.0f, 0.471f, 0.50f};
+
+int rag_net_set_input_planes(rag_net* net, const int32_t* h_plane_src, int F)
+{
+    if (!net || !h_plane_src) return fail(RAG_EINVAL, "null argument");
+    if (F != net->desc.in_planes) return fail(RAG_EINVAL, "network takes %d planes, %d listed", net->desc.in_planes, F);
+    for (int f = 0; f < F; f++) {
+        if (h_plane_src[f] < 0 || h_plane_src[f] >= RAG_NUM_PLANES) return fail(RAG_EINVAL, "plane %d is not a canonical plane", h_plane_src[f]);
+        net->in_density[f] = kPlaneDensity[h_plane_src[f]];
+    }
+    return RAG_OK;
 }
 
 int rag_set_conv_pair(int enable) { int old = g_conv_pair; g_conv_pair = enable != 0; return old; }

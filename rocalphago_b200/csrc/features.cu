@@ -878,7 +878,7 @@ using namespace rag;
 extern "C" {
 
 const char* rag_last_error(void) { return last_error_buffer(); }
-int rag_abi_version(void) { return 5; }
+int rag_abi_version(void) { return 6; }
 
 int rag_pack_states(int n, int size, const int8_t* h_board, const int16_t* h_age, const int32_t* h_ko,
                     const int32_t* h_player, uint32_t* h_packed)

@@ -13,7 +13,7 @@ import numpy as np
 import torch
 
 from .. import _cabi, hdf5_lite
-from ..preprocessing import Preprocess, DTYPE_BF16, DTYPE_FP16, DTYPE_FP16X3, LAYOUT_CONV_IN, analyze_into
+from ..preprocessing import Preprocess, DTYPE_BF16, DTYPE_FP16, DTYPE_CODES, LAYOUT_CONV_IN, analyze_into
 from ..state import _ptr, _stream, _require_cuda
 
 HEAD_POLICY, HEAD_VALUE = 0, 1
@@ -52,9 +52,10 @@ class Network(object):
         if self.unit_end is not None and (len(self.unit_end) != len(self.specs) or not self.unit_end[0] or not self.unit_end[-1]):
             raise ValueError("unit_end needs one flag per convolution, set on the first and the last")
         self.head, self.dense_units = head, int(dense_units)
-        if dtype not in ("fp16", "bf16", "fp16x3"):
-            raise ValueError("dtype must be 'fp16', 'bf16' or 'fp16x3' (got %r)" % (dtype,))
+        if dtype not in DTYPE_CODES:
+            raise ValueError("dtype must be one of %s (got %r)" % (sorted(DTYPE_CODES), dtype))
         self.dtype, self.kernel_flip = dtype, bool(kernel_flip)
+        self.input_planes = None        # canonical plane of every input plane (set by NeuralNetBase): a ranking hint for 'fp16c32/64'
         self.input_shape = (None, self.input_dim, self.board, self.board)      # read by trainers
         self.output_shape = (None, self.board * self.board) if head == "policy" else (None, 1)
         self._weights = self._init_uniform(seed)
@@ -260,7 +261,7 @@ class Network(object):
                 d.filters[i], d.widths[i] = nb, k
             d.head = HEAD_POLICY if self.head == "policy" else HEAD_VALUE
             d.dense_units = self.dense_units
-            d.dtype = {"bf16": DTYPE_BF16, "fp16": DTYPE_FP16, "fp16x3": DTYPE_FP16X3}[self.dtype]
+            d.dtype = DTYPE_CODES[self.dtype]
             d.kernel_flip = int(self.kernel_flip)
             d.resnet = int(self.unit_end is not None)
             for i, u in enumerate(self.unit_end or []):
@@ -269,6 +270,9 @@ class Network(object):
             with torch.cuda.device(device):
                 _cabi.check(L.rag_net_create(ctypes.byref(d), ctypes.byref(h)))
             self._handle, self._handle_device, self._dirty = h, device, True
+            if self.input_planes is not None and len(self.input_planes) == self.input_dim:
+                src = np.ascontiguousarray(self.input_planes, np.int32)
+                _cabi.check(L.rag_net_set_input_planes(h, src.ctypes.data_as(ctypes.c_void_p), len(src)))
         if self._dirty:
             arr = (ctypes.c_void_p * len(self._weights))(*[w.ctypes.data_as(ctypes.c_void_p).value for w in self._weights])
             with torch.cuda.device(device):
@@ -362,6 +366,7 @@ class NeuralNetBase(object):
         kwargs["input_dim"] = self.preprocessor.output_dim
         if kwargs.get("init_network", True):
             self.model = self.__class__.create_network(**kwargs)
+            self.model.input_planes = list(self.preprocessor.plane_src)
             self.forward = self._model_forward()
 
     def _model_forward(self):
@@ -384,6 +389,7 @@ class NeuralNetBase(object):
                              "(was it registered with the @neuralnet decorator?)".format(class_name))
         new_net = network_class(object_specs["feature_list"], init_network=False)
         new_net.model = Network.from_json(object_specs["keras_model"])
+        new_net.model.input_planes = list(new_net.preprocessor.plane_src)
         if "weights_file" in object_specs:
             new_net.model.load_weights(_find_relative(object_specs["weights_file"], json_file))
         new_net.forward = new_net._model_forward()

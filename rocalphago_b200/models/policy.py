@@ -6,6 +6,13 @@ from ..state import BatchedGameState
 from .nn_util import NeuralNetBase, Network, neuralnet
 
 
+# What CNNPolicy computes in unless told otherwise: fp16 tensor-core operands with the 32 most energetic
+# input channels of every layer after the first corrected by their fp16 remainders (include/
+# rocalphago_b200.h RAG_DTYPE_FP16C32).  Plain 'fp16' is 1.3x faster but sits at north_star's 99.5 %
+# top-1 gate on random-init weights (99.4-99.8 % by seed); this mode holds it (99.6-99.9 %).
+DEFAULT_POLICY_DTYPE = "fp16c32"
+
+
 def flatten_idx(position, size):
     (x, y) = position
     return x * size + y            # AlphaGo/util.py:11-13
@@ -34,8 +41,8 @@ class CNNPolicy(NeuralNetBase):
         probs = self.model.eval_batch_device(batch, self.preprocessor.plane_src)
         which, flat, counts = self.preprocessor.legal_move_indices(self.model.features_workspace(), n, batch.size)
         picked = probs.cpu().numpy()[which, flat]
-        starts = np.concatenate([[0], np.cumsum(counts)[:-1]])
-        sums = np.add.reduceat(picked, np.minimum(starts, max(len(picked) - 1, 0))) if len(picked) else np.zeros(n, np.float32)
+        # per-state sums: states without a legal move (counts == 0) own no entry of `picked`
+        sums = np.bincount(which, weights=picked, minlength=n).astype(picked.dtype)
         return which, flat, counts, picked / np.repeat(sums, counts)
 
     def batch_eval_state(self, states, moves_lists=None):
@@ -82,8 +89,9 @@ class CNNPolicy(NeuralNetBase):
         Keyword Arguments (same names as the reference):
         - input_dim, board (19), filters_per_layer (128), filters_per_layer_K, layers (12),
           filter_width_K (3; first layer 5)
-        and, for this implementation: dtype ('fp16' (default) | 'bf16' operands of the convolutions, or 'fp16x3': fp16 operands
-        split into hi + lo parts, fp32-like results at a third of the speed),
+        and, for this implementation: dtype -- 'fp16c32' (default: fp16 operands, the 32 most energetic
+        input channels of layers 2.. corrected by their fp16 remainders), 'fp16c64', 'fp16', 'bf16', or
+        'fp16x3' (every operand split into hi + lo parts: fp32-like results at a third of fp16's speed),
         kernel_flip (True = Theano convolution semantics), seed (None = fresh random weights).
         """
         defaults = {
@@ -100,7 +108,7 @@ class CNNPolicy(NeuralNetBase):
             nb = params.get("filters_per_layer_%d" % i, params["filters_per_layer"])
             specs.append((nb, width))
         return Network(params["board"], params["input_dim"], specs, head="policy",
-                       dtype=params.get("dtype", "fp16"), kernel_flip=params.get("kernel_flip", True),
+                       dtype=params.get("dtype", DEFAULT_POLICY_DTYPE), kernel_flip=params.get("kernel_flip", True),
                        seed=params.get("seed"))
 
 
@@ -131,14 +139,3 @@ class ResnetPolicy(CNNPolicy):
             layer += n_skip
         return Network(params["board"], params["input_dim"], specs, head="policy", dtype=params.get("dtype", "fp16"),
                        kernel_flip=params.get("kernel_flip", True), seed=params.get("seed"), unit_end=unit_end)
-
-
-def _smoke(batch, board, age, ko, player):
-    """Used by __graft_entry__.smoke(): a 3-layer policy on the smoke batch vs the CPU oracle."""
-    from oracle import cnn_oracle, go_oracle
-    net = CNNPolicy(go_oracle.DEFAULT_FEATURES, layers=3, filters_per_layer=32, seed=5)
-    probs = net.model.eval_batch_device(batch, net.preprocessor.plane_src).cpu().numpy()
-    planes = go_oracle.features(board, age, ko, player, go_oracle.DEFAULT_FEATURES)
-    want = cnn_oracle.forward(net.model.get_weights(), planes, net.model.specs)
-    err = float(np.abs(probs - want).max())
-    assert err < 2e-3, "policy probabilities differ from the oracle by %g" % err

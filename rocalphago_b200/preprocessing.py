@@ -38,7 +38,8 @@ DEFAULT_FEATURES = [
     "sensibleness", "zeros"]
 
 LAYOUT_NCHW_U8, LAYOUT_NCHW_F32, LAYOUT_CONV_IN = 0, 1, 2
-DTYPE_BF16, DTYPE_FP16, DTYPE_FP16X3 = 0, 1, 2        # include/rocalphago_b200.h: RAG_DTYPE_*
+DTYPE_BF16, DTYPE_FP16, DTYPE_FP16X3, DTYPE_FP16C32, DTYPE_FP16C64 = 0, 1, 2, 3, 4        # include/rocalphago_b200.h: RAG_DTYPE_*
+DTYPE_CODES = {"bf16": DTYPE_BF16, "fp16": DTYPE_FP16, "fp16x3": DTYPE_FP16X3, "fp16c32": DTYPE_FP16C32, "fp16c64": DTYPE_FP16C64}
 _MOVE_PLANES = np.asarray([46, 48], np.int32)      # sensibleness, legal
 
 

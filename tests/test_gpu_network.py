@@ -63,35 +63,100 @@ def test_policy_forward_small_networks(dtype, arch, n):
     assert np.allclose(got.sum(1), 1.0, atol=1e-5)
 
 
-def test_policy_13x192_parity_and_top1():
-    """BASELINE config 2's network (12 conv + 1x1, 192 filters, 48 planes) with Keras-'uniform'
-    random weights on 1024 random-playout positions."""
+def _binomial(miss, n):
+    p = 1.0 - miss / float(n)
+    return p, 1.96 * (max(p * (1.0 - p), 1e-12) / n) ** 0.5
+
+
+def test_policy_13x192_top1_gate_for_the_default_precision():
+    """north_star's gates on BASELINE's network (12 conv + 1x1, 192 filters, 48 planes, Keras-'uniform'
+    random weights) for the precision CNNPolicy and bench.py use by default: probabilities within 2e-3
+    and >= 99.5 % top-1 agreement with the fp32 forward, on 8,192 random-playout positions x 3 weight
+    seeds (24,576 arg-max decisions; +-0.07 % at 95 %).  With random weights the 361 outputs are nearly
+    flat (top two logits ~3 % of the spread apart), so this measures the rounding noise of the
+    operands: plain fp16 sits AT the gate (99.4-99.8 % depending on the seed), bf16 at 96-98 % --
+    both are reported below with their own bounds, neither is what the bench runs."""
+    from rocalphago_b200.models.policy import DEFAULT_POLICY_DTYPE
     feats = go_oracle.DEFAULT_FEATURES
-    n = 1024
+    n = 8192
     b, a, ko, pl = _positions(n, seed=23)
     planes = go_oracle.features(b, a, ko, pl, feats)
     specs = cnn_oracle.layer_specs(input_dim=48, layers=12, filters_per_layer=192)
-    weights = cnn_oracle.uniform_weights(specs, 48, 19, seed=7)
+    batch = BatchedGameState.from_arrays(b, a, ko, pl)
+    chunks = [BatchedGameState(batch.packed[i:i + 4096].contiguous(), 19) for i in range(0, n, 4096)]
+    report, miss = {}, {}
+    for seed in (7, 8, 9):
+        weights = cnn_oracle.uniform_weights(specs, 48, 19, seed=seed)
+        want = cnn_oracle.forward(weights, planes, specs, threads=os.cpu_count())
+        for dtype in (DEFAULT_POLICY_DTYPE, "fp16", "bf16"):
+            net = CNNPolicy(feats, layers=12, filters_per_layer=192, dtype=dtype)
+            net.model.set_weights(weights)
+            got = np.concatenate([net.model.eval_batch_device(c, net.preprocessor.plane_src).cpu().numpy() for c in chunks])
+            st = _policy_stats(got, want)
+            report["%s/seed%d" % (dtype, seed)] = st
+            miss[dtype] = miss.get(dtype, 0) + int((got.argmax(1) != want.argmax(1)).sum())
+            assert st["max_abs"] <= PROB_TOL, report
+            if dtype == DEFAULT_POLICY_DTYPE:
+                assert st["top1"] >= TOP1_MIN, report          # every seed on its own
+    pooled = {d: dict(zip(("top1", "ci95"), _binomial(m, 3 * n)), miss=m, n=3 * n) for d, m in miss.items()}
+    print("policy 13x192 parity:", json.dumps({"pooled": pooled, "runs": report}))
+    assert pooled[DEFAULT_POLICY_DTYPE]["top1"] - pooled[DEFAULT_POLICY_DTYPE]["ci95"] >= TOP1_MIN, pooled
+    # the other operand types, bounded where they were measured (not the bench's precision):
+    assert pooled["fp16"]["top1"] >= 0.993, pooled
+    assert pooled["bf16"]["top1"] >= 0.95, pooled
+
+
+@pytest.mark.parametrize("dtype,noise", [("fp16c32", 0.75), ("fp16c64", 0.60)])
+def test_corrected_channel_modes_cut_the_rounding_noise(dtype, noise):
+    """fp16c32 / fp16c64: hi.W_hi + lo.W_hi + hi.W_lo for the 32 / 64 most energetic input channels of
+    layers 2.. only.  Their logit error must be the stated fraction of plain fp16's or less, the
+    filter reordering must not show in the result, and all entry points must agree."""
+    feats = go_oracle.DEFAULT_FEATURES
+    n = 512
+    b, a, ko, pl = _positions(n, seed=29)
+    planes = go_oracle.features(b, a, ko, pl, feats)
+    specs = cnn_oracle.layer_specs(input_dim=48, layers=12, filters_per_layer=192)
+    weights = cnn_oracle.uniform_weights(specs, 48, 19, seed=8)
     want = cnn_oracle.forward(weights, planes, specs, threads=os.cpu_count())
     batch = BatchedGameState.from_arrays(b, a, ko, pl)
-    report = {}
-    for dtype in ("fp16", "bf16"):
-        net = CNNPolicy(feats, layers=12, filters_per_layer=192, dtype=dtype)
+    err = {}
+    for dt in ("fp16", dtype):
+        net = CNNPolicy(feats, layers=12, filters_per_layer=192, dtype=dt)
         net.model.set_weights(weights)
         got = net.model.eval_batch_device(batch, net.preprocessor.plane_src).cpu().numpy()
-        report[dtype] = _policy_stats(got, want)
-    print("policy 13x192 parity:", json.dumps(report))
-    for dtype in report:
-        assert report[dtype]["max_abs"] <= PROB_TOL, report
-    # With Keras-'uniform' random weights the 361 outputs are nearly flat (the top two logits differ
-    # by about 1 % of the logit spread), so top-1 agreement measures rounding noise of the 16-bit
-    # operands: measured 99.4 % for fp16 and 96.0 % for bf16 (SURVEY F7 predicted 99.7 % / 96.3 %).
-    # These are bounded here, not hidden; with a trained-like output both pass the 99.5 % gate
-    # (test_policy_sharper_weights_bf16_top1).
-    assert report["fp16"]["top1"] >= 0.99, report
-    assert report["fp16"]["logit_rel"] <= 0.03, report
-    assert report["bf16"]["top1"] >= 0.93, report
-    assert report["bf16"]["logit_rel"] <= 0.25, report
+        err[dt] = float(np.sqrt(((_centered(got) - _centered(want)) ** 2).mean()))
+        assert np.abs(got - want).max() <= PROB_TOL
+    assert err[dtype] <= noise * err["fp16"], err
+    got2 = net.forward(planes[:64])                              # NCHW float entry
+    assert np.abs(got2 - got[:64]).max() <= 1e-6
+    from rocalphago_b200.pipeline import EvalPipeline
+    pipe = EvalPipeline(net, n, slots=2)
+    got3 = pipe.result(pipe.submit(batch.packed)).cpu().numpy()
+    assert np.array_equal(got3, got)
+
+
+@pytest.mark.parametrize("dtype", ["fp16c32", "fp16c64"])
+@pytest.mark.parametrize("arch,n", [
+    (dict(layers=3, filters_per_layer=32), 16),
+    (dict(layers=4, filters_per_layer=128, filter_width_2=1, filter_width_3=5, filters_per_layer_2=64), 9),
+    (dict(layers=3, filters_per_layer=152), 9),
+    (dict(layers=2, filters_per_layer=256, filter_width_2=7), 5),
+    (dict(layers=1, filters_per_layer=64, filter_width_1=3), 6),
+])
+def test_corrected_channel_modes_small_networks(dtype, arch, n):
+    feats = go_oracle.DEFAULT_FEATURES
+    b, a, ko, pl = _positions(n)
+    planes = go_oracle.features(b, a, ko, pl, feats)
+    net = CNNPolicy(feats, dtype=dtype, seed=3, **arch)
+    want = cnn_oracle.forward(net.model.get_weights(), planes, net.model.specs)
+    st = _policy_stats(net.forward(planes), want)
+    assert st["max_abs"] <= PROB_TOL and st["logit_rel"] <= 0.02, st
+    val = CNNValue(feats + ["color"], dtype=dtype, seed=5, dense_units=64, **arch)
+    bt = BatchedGameState.from_arrays(b, a, ko, pl)
+    vplanes = go_oracle.features(b, a, ko, pl, feats + ["color"])
+    vwant = cnn_oracle.forward(val.model.get_weights(), vplanes, val.model.specs, head="value")
+    vgot = np.array(val.batch_eval_state(bt))
+    assert np.abs(vgot - vwant).max() <= VALUE_TOL
 
 
 def test_split_operand_mode_meets_the_top1_gate_on_random_init_weights():
@@ -265,6 +330,32 @@ def test_batch_eval_state_matches_reference_api():
     with pytest.raises(ValueError, match="same size"):
         net.batch_eval_state([states[0], small])
     del sub
+
+
+def test_batch_eval_state_when_the_last_states_have_no_legal_move():
+    """A terminal position sorting last in a batch (an MCTS wave does this) must not disturb the
+    renormalisation of the states before it.  5x5: WHITE owns everything but two one-point eyes,
+    BLACK to move has no legal move at all (both points are suicide, go.py:267-285)."""
+    net = CNNPolicy(["board", "ones", "liberties"], board=5, layers=2, filters_per_layer=32, seed=9)
+    full = -np.ones((5, 5))
+    full[0, 0] = full[4, 4] = 0
+    ages = np.where(full != 0, 3, -1)
+    dead = PositionView(full, ages, None, 1)
+    open_ = PositionView(np.zeros((5, 5)), -np.ones((5, 5)), None, 1)
+    half = np.zeros((5, 5))
+    half[2, :] = 1
+    mid = PositionView(half, np.where(half != 0, 2, -1), None, -1)
+    for states in ([open_, mid, dead], [open_, mid, dead, dead], [dead, open_, dead, mid, dead]):
+        res = net.batch_eval_state(states)
+        assert len(res) == len(states)
+        for st, r in zip(states, res):
+            if st is dead:
+                assert r == []
+            else:
+                alone = net.eval_state(st)
+                assert [m for m, _ in r] == [m for m, _ in alone]
+                assert abs(sum(p for _, p in r) - 1.0) < 1e-5
+                assert np.allclose([p for _, p in r], [p for _, p in alone], atol=1e-6)
 
 
 def test_save_load_roundtrip_and_reference_model_json(tmp_path):
