@@ -132,7 +132,8 @@ def cpu_path(n_positions, cores, seed=99, pool=None, weights=None, keep=False):
     if own_pool:
         pool.close()
     if keep:
-        return t1 - t0, t3 - t2, (b, a, ko, pl, np.concatenate(probs))
+        order = np.concatenate([np.arange(len(b))[i::cores] for i in range(cores)])     # the order the chunks were joined in
+        return t1 - t0, t3 - t2, (b[order], a[order], ko[order], pl[order], np.concatenate(probs))
     return t1 - t0, t3 - t2
 
 
