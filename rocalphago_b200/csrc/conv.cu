@@ -41,6 +41,7 @@ constexpr int kMaxBoardPoints = 361;
 constexpr int kTmemCols = 512;
 constexpr int kConvThreads = 192;
 constexpr int kATileBytes = kTileM * kChunkK * 2;     // 16 KiB
+constexpr int kOutBoxBytes = 32 * kChunkK * 2;        // 4 KiB: what one epilogue warp hands to one TMA store
 
 struct ConvParams {
     int tiles, width, kchunks, N, stages, dtype;
@@ -67,6 +68,7 @@ struct ConvParams {
     int out_pitch;                // mode 0: channels per output row
     int lo_cols;                  // mode 0: leading channels whose lo half is written at column N + c
     int dup_hi;                   // mode 0: also copy hi of channels 0..31 to columns N + 32 .. N + 63
+    int debug;                    // timing experiments only (RAG_CONV_DEBUG): 1 skip weight loads, 2 skip activation loads, 8 skip stores
 };
 
 // ---- PTX wrappers ----------------------------------------------------------------------------
@@ -112,6 +114,15 @@ __device__ __forceinline__ void tma_load_im2col_pair(uint32_t dst, const CUtenso
         "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.im2col.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};"
         ::"r"(dst), "l"(map), "r"(leader_bar), "r"(c), "r"(w), "r"(h), "r"(n), "h"(w_off), "h"(h_off) : "memory");
 }
+// bulk tensor store smem -> global (rows past the tensor's extent are clipped by the TMA unit)
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, int c0, int c1, uint32_t src) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                 ::"l"(map), "r"(src), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_commit(uint32_t bar) {
@@ -193,7 +204,7 @@ constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;   // shared::cluster address of t
 template <bool kPair>
 __global__ void __launch_bounds__(kConvThreads, 1)
 conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                 const ConvParams p)
+                 const __grid_constant__ CUtensorMap tmO, const ConvParams p)
 {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
@@ -201,7 +212,8 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     uint8_t* smem = smem_raw + (base - raw);
     const uint32_t b_rows = kPair ? (uint32_t)p.N / 2u : (uint32_t)p.N;       // rows of B this CTA holds
     const uint32_t stage_bytes = kATileBytes + b_rows * 128u;
-    uint8_t* after = smem + (size_t)p.stages * stage_bytes;
+    uint8_t* out_stage = smem + (size_t)p.stages * stage_bytes;   // 4 epilogue warps x one 32-row x 64-channel store box
+    uint8_t* after = out_stage + 4 * kOutBoxBytes;
     uint64_t* bars = reinterpret_cast<uint64_t*>(after);          // full[stages], empty[stages], tfull[2], tempty[2]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * p.stages + 4);
     float* s_bias = reinterpret_cast<float*>(tmem_slot + 4);
@@ -269,6 +281,13 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                                 const uint32_t lb = full_bar(s) & kPeerBitMask;
                                 tma_load_im2col_pair(sa, &tmA, ca * kChunkK, y0 - pad, x0 - pad, b0, (uint16_t)j, (uint16_t)i, lb);
                                 tma_load_2d_pair(sa + kATileBytes, &tmB, c * kChunkK, t * p.N + (int)(rank * b_rows), lb);
+                            } else if (p.debug & 3) {
+                                // timing experiment: after the ring's first pass leave stale operands in place
+                                const bool la = !(p.debug & 2) || it < (uint32_t)p.stages, lb = !(p.debug & 1) || it < (uint32_t)p.stages;
+                                const uint32_t bytes = (la ? (uint32_t)kATileBytes : 0u) + (lb ? b_rows * 128u : 0u);
+                                if (bytes) mbar_expect_tx(full_bar(s), bytes); else mbar_arrive(full_bar(s));
+                                if (la) tma_load_im2col(sa, &tmA, ca * kChunkK, y0 - pad, x0 - pad, b0, (uint16_t)j, (uint16_t)i, full_bar(s));
+                                if (lb) tma_load_2d(sa + kATileBytes, &tmB, c * kChunkK, t * p.N, full_bar(s));
                             } else {
                                 mbar_expect_tx(full_bar(s), stage_bytes);
                                 tma_load_im2col(sa, &tmA, ca * kChunkK, y0 - pad, x0 - pad, b0, (uint16_t)j, (uint16_t)i, full_bar(s));
@@ -309,58 +328,87 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     } else {
         // ===== epilogue =====
         const int quarter = warp & 3;                              // TMEM lanes this warp may read
+        uint8_t* sbuf = out_stage + quarter * kOutBoxBytes;
+        const uint32_t sbuf_u32 = smem_u32(sbuf);
+        bool store_pending = false;
+        auto store_done = [&]() {                                  // the last box has been read out of sbuf
+            if (store_pending) { if (lane == 0) bulk_wait_read0(); __syncwarp(); store_pending = false; }
+        };
+        auto store_box = [&](int chan, int row0) {                 // every lane has written its row of the box
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0 && row0 < p.rows && !(p.debug & 8)) { tma_store_2d(&tmO, chan, row0, sbuf_u32); bulk_commit(); }
+            store_pending = true;
+        };
         uint32_t lt = 0;
         for (int tile = worker; tile < p.tiles; tile += n_workers, lt++) {
             const uint32_t a = lt & 1u, aph = (lt >> 1) & 1u;
             // my row of the tile = one point of one board; rows past the last board are not written
             const long long row = (long long)tile * rows_per_tile + (long long)rank * kTileM + quarter * 32 + lane;
-            const bool real = row < p.rows;
+            const bool real = row < p.rows && !(p.debug & 8);
             mbar_wait(tfull_bar((int)a), aph);
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + a * (uint32_t)p.N;
             if (p.mode == 0) {
-                uint16_t* orow = reinterpret_cast<uint16_t*>(p.out) + row * p.out_pitch;
-                for (int c0 = 0; c0 < p.N; c0 += 32) {
-                    uint32_t v[32];
-                    tc_ld32(taddr + (uint32_t)c0, v);
-                    tc_wait_ld();
-                    const bool with_lo = c0 < p.lo_cols;          // x = hi + lo, both fp16: the next layer multiplies both
-                    uint32_t packed[16], lo[16];
+                // 16-bit pixel rows for the next layer, 64 channels at a time: the warp assembles its 32 rows
+                // of the box in shared memory (128-byte rows, 16-byte chunks XOR-swizzled by row so that the
+                // 32 lanes' stores spread over all banks) and one lane hands the box to the TMA unit, which
+                // writes full lines and clips rows past the last board.  Per-thread global stores of 16 B at
+                // a 384-byte stride cost the SM's L1/shared-memory pipe 32 passes per instruction -- the
+                // pipe the tensor core's operands come through.
+                const int row0 = (int)((long long)tile * rows_per_tile + (long long)rank * kTileM + quarter * 32);
+                uint8_t* my_row = sbuf + lane * 128;
+                const int sw = lane & 7;
+                for (int bx = 0; bx < p.N; bx += kChunkK) {
+                    const bool with_lo = bx < p.lo_cols;          // x = hi + lo, both fp16: the next layer multiplies both
+                    uint32_t lo[32], dup[16];
                     #pragma unroll
-                    for (int j = 0; j < 16; j++) {
-                        float f0 = __uint_as_float(v[2 * j]) + s_bias[c0 + 2 * j];
-                        float f1 = __uint_as_float(v[2 * j + 1]) + s_bias[c0 + 2 * j + 1];
-                        if (p.relu) { f0 = fmaxf(f0, 0.f); f1 = fmaxf(f1, 0.f); }
-                        if (p.dtype == RAG_DTYPE_BF16) {
-                            __nv_bfloat162 h = __floats2bfloat162_rn(f0, f1);
-                            packed[j] = *reinterpret_cast<uint32_t*>(&h);
-                        } else {
-                            __half2 h = __floats2half2_rn(f0, f1);
-                            packed[j] = *reinterpret_cast<uint32_t*>(&h);
-                            if (with_lo) {
-                                const float2 back = __half22float2(h);
-                                __half2 l = __floats2half2_rn(f0 - back.x, f1 - back.y);
-                                lo[j] = *reinterpret_cast<uint32_t*>(&l);
+                    for (int half = 0; half < 2; half++) {
+                        const int c0 = bx + 32 * half;
+                        uint32_t v[32];
+                        tc_ld32(taddr + (uint32_t)c0, v);
+                        tc_wait_ld();
+                        uint32_t packed[16];
+                        #pragma unroll
+                        for (int j = 0; j < 16; j++) {
+                            float f0 = __uint_as_float(v[2 * j]) + s_bias[c0 + 2 * j];
+                            float f1 = __uint_as_float(v[2 * j + 1]) + s_bias[c0 + 2 * j + 1];
+                            if (p.relu) { f0 = fmaxf(f0, 0.f); f1 = fmaxf(f1, 0.f); }
+                            if (p.dtype == RAG_DTYPE_BF16) {
+                                __nv_bfloat162 h = __floats2bfloat162_rn(f0, f1);
+                                packed[j] = *reinterpret_cast<uint32_t*>(&h);
+                            } else {
+                                __half2 h = __floats2half2_rn(f0, f1);
+                                packed[j] = *reinterpret_cast<uint32_t*>(&h);
+                                if (with_lo) {
+                                    const float2 back = __half22float2(h);
+                                    __half2 l = __floats2half2_rn(f0 - back.x, f1 - back.y);
+                                    lo[16 * half + j] = *reinterpret_cast<uint32_t*>(&l);
+                                }
                             }
+                            if (half == 0) dup[j] = packed[j];
                         }
-                    }
-                    if (real) {
-                        uint4* dst = reinterpret_cast<uint4*>(orow + c0);
+                        if (half == 0) store_done();
                         #pragma unroll
                         for (int j = 0; j < 4; j++)
-                            dst[j] = make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
-                        if (with_lo) {
-                            uint4* dl = reinterpret_cast<uint4*>(orow + p.N + c0);
+                            *reinterpret_cast<uint4*>(my_row + (((4 * half + j) ^ sw) << 4)) =
+                                make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
+                    }
+                    store_box(bx, row0);
+                    if (with_lo) {
+                        store_done();
+                        if (p.dup_hi) {            // FP16C32: [lo 0..31 | hi 0..31]
                             #pragma unroll
-                            for (int j = 0; j < 4; j++)
-                                dl[j] = make_uint4(lo[4 * j], lo[4 * j + 1], lo[4 * j + 2], lo[4 * j + 3]);
-                            if (p.dup_hi) {
-                                uint4* dd = reinterpret_cast<uint4*>(orow + p.N + 32 + c0);
-                                #pragma unroll
-                                for (int j = 0; j < 4; j++)
-                                    dd[j] = make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
+                            for (int j = 0; j < 4; j++) {
+                                *reinterpret_cast<uint4*>(my_row + ((j ^ sw) << 4)) = make_uint4(lo[4 * j], lo[4 * j + 1], lo[4 * j + 2], lo[4 * j + 3]);
+                                *reinterpret_cast<uint4*>(my_row + (((4 + j) ^ sw) << 4)) = make_uint4(dup[4 * j], dup[4 * j + 1], dup[4 * j + 2], dup[4 * j + 3]);
                             }
+                        } else {
+                            #pragma unroll
+                            for (int j = 0; j < 8; j++)
+                                *reinterpret_cast<uint4*>(my_row + ((j ^ sw) << 4)) = make_uint4(lo[4 * j], lo[4 * j + 1], lo[4 * j + 2], lo[4 * j + 3]);
                         }
+                        store_box(p.N + bx, row0);
                     }
                 }
             } else if (p.mode == 1) {
@@ -437,6 +485,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             __syncwarp();
             if (lane == 0) { if (kPair) mbar_arrive_leader(tempty_bar((int)a)); else mbar_arrive(tempty_bar((int)a)); }
         }
+        if (lane == 0) bulk_wait0();                               // outstanding stores own sbuf until they are done
     }
     tc_fence_before();
     __syncthreads();
@@ -594,6 +643,8 @@ struct Layer {
     struct ACache { const void* ptr; int n; CUtensorMap map; };
     std::vector<ACache> a_maps;   // im2col views of recently used input buffers
     int a_next = 0;
+    std::vector<ACache> o_maps;   // store views of recently used output buffers
+    int o_next = 0;
     uint16_t* d_w = nullptr;      // [taps][n_pad][kdim]
     float* d_bias = nullptr;      // [n_pad]
     float* d_bn_scale = nullptr;  // residual nets: BatchNormalization applied to this layer's INPUT, [S] each
@@ -629,7 +680,7 @@ struct rag_net {
 namespace rag {
 
 static size_t conv_smem_bytes(int N, int stages) {
-    return 1024 + (size_t)stages * (kATileBytes + (size_t)N * 128) + (2 * stages + 4) * 8 + 16 + 2 * (size_t)N * 4;
+    return 1024 + (size_t)stages * (kATileBytes + (size_t)N * 128) + 4 * kOutBoxBytes + (2 * stages + 4) * 8 + 16 + 2 * (size_t)N * 4;
 }
 
 // rag_set_conv_pair: run layers on CTA pairs (cta_group::2) where they allow it.  Off by default:
@@ -694,6 +745,19 @@ static int input_map(rag_net* net, Layer& ly, const void* ptr, int n, const CUte
     return RAG_OK;
 }
 
+// the store view of an output buffer: [n*S*S rows][pitch channels] in boxes of 32 rows x 64 channels
+static int output_map(rag_net* net, Layer& ly, const void* ptr, int n, int pitch, const CUtensorMap** out) {
+    for (auto& e : ly.o_maps)
+        if (e.ptr == ptr && e.n == n) { *out = &e.map; return RAG_OK; }
+    Layer::ACache e;
+    e.ptr = ptr; e.n = n;
+    const int S = net->desc.board;
+    if (int rc = make_map(&e.map, ptr, (long long)n * S * S, pitch, 32, net->op_dtype)) return rc;
+    if (ly.o_maps.size() < 16) { ly.o_maps.push_back(e); *out = &ly.o_maps.back().map; }
+    else { ly.o_maps[ly.o_next] = e; *out = &ly.o_maps[ly.o_next].map; ly.o_next = (ly.o_next + 1) % 16; }
+    return RAG_OK;
+}
+
 static int conv_smem_limit(bool pair, size_t smem) {
     static size_t set[2] = {0, 0};      // largest dynamic shared memory size already granted to each kernel
     if (smem <= set[pair]) return RAG_OK;
@@ -719,6 +783,10 @@ static int run_layers(rag_net* net, const uint16_t* d_in, int n, float* d_out, c
         p.width = ly.width; p.kchunks = ly.kdim / kChunkK; p.N = ly.n_pad;
         p.stages = pick_stages(ly.n_pad); p.dtype = net->op_dtype;
         p.a_map = ly.a_map;
+        static const int dbg = getenv("RAG_CONV_DEBUG") ? atoi(getenv("RAG_CONV_DEBUG")) : 0;
+        static const int dbg_stages = getenv("RAG_CONV_STAGES") ? atoi(getenv("RAG_CONV_STAGES")) : 0;
+        p.debug = dbg;
+        if (dbg_stages >= 2 && dbg_stages < p.stages) p.stages = dbg_stages;
         if (!last) {
             const Layer& nx = net->layers[l + 1];
             p.out_pitch = nx.cin_store; p.lo_cols = nx.lo_in; p.dup_hi = nx.lo_in == 32;
@@ -744,6 +812,9 @@ static int run_layers(rag_net* net, const uint16_t* d_in, int n, float* d_out, c
         }
         const CUtensorMap* tmA = nullptr;
         if (int rc = input_map(net, ly, cur, n, &tmA)) return rc;
+        const CUtensorMap* tmO = tmA;                      // only read by layers that write plain pixel rows
+        if (p.mode == 0)
+            if (int rc = output_map(net, ly, dst, n, p.out_pitch, &tmO)) return rc;
         if (net->profiling) RAG_CUDA_CHECK(cudaEventRecord(net->events[l], s));
         if (pair) {
             const size_t smem = conv_smem_bytes(ly.n_pad / 2, p.stages) + (size_t)ly.n_pad * 4;      // bias/head tables are N wide
@@ -756,12 +827,12 @@ static int run_layers(rag_net* net, const uint16_t* d_in, int n, float* d_out, c
             attr[0].id = cudaLaunchAttributeClusterDimension;
             attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
             cfg.attrs = attr; cfg.numAttrs = 1;
-            RAG_CUDA_CHECK(cudaLaunchKernelEx(&cfg, conv_umma_kernel<true>, *tmA, ly.tmB_pair, p));
+            RAG_CUDA_CHECK(cudaLaunchKernelEx(&cfg, conv_umma_kernel<true>, *tmA, ly.tmB_pair, *tmO, p));
         } else {
             const size_t smem = conv_smem_bytes(ly.n_pad, p.stages);
             if (int rc = conv_smem_limit(false, smem)) return rc;
             const int grid = p.tiles < net->sms ? p.tiles : net->sms;
-            conv_umma_kernel<false><<<grid, kConvThreads, smem, s>>>(*tmA, ly.tmB, p);
+            conv_umma_kernel<false><<<grid, kConvThreads, smem, s>>>(*tmA, ly.tmB, *tmO, p);
         }
         RAG_CUDA_CHECK(cudaGetLastError());
         if (net->profiling && last) RAG_CUDA_CHECK(cudaEventRecord(net->events[L], s));

@@ -159,7 +159,9 @@ def test_command_line_converter(tmp_path):
 
 def test_references_minimodel_on_the_device():
     """The reference's minimodel (Keras 1.1.2 JSON, HDF5 weights; fixture tests/golden/minimodel.npz)
-    evaluated on the Lee Sedol positions: within north_star's tolerances of the CPU restatement."""
+    evaluated on the Lee Sedol positions: within north_star's tolerances of the CPU restatement, and
+    of the committed outputs tests/golden/minimodel_forward.npz (oracle/make_golden_minimodel_forward.py:
+    the scipy restatement, equal to the torch one to 5e-10) in every precision mode."""
     z = np.load(os.path.join(gu.GOLDEN, "minimodel.npz"))
     feats = [str(s) for s in z["feature_list"]]
     convs = [tuple(int(v) for v in c) for c in z["convs"]]
@@ -174,3 +176,14 @@ def test_references_minimodel_on_the_device():
     assert got.shape == want.shape == (len(x), 361)
     assert np.abs(got - want).max() <= 2e-3
     assert (got.argmax(1) == want.argmax(1)).mean() >= 0.995
+    gold = np.load(os.path.join(gu.GOLDEN, "minimodel_forward.npz"))
+    g = gu.load_features("features_sgf.npz")
+    idx = gold["index"]
+    planes = gu.select_planes(g["planes"], feats)[idx].astype(np.float32)
+    batch = BatchedGameState.from_arrays(g["board"][idx], g["age"][idx], g["ko"][idx], g["player"][idx])
+    for dtype in ("fp16c32", "fp16", "bf16", "fp16x3", "fp16c64"):
+        net = CNNPolicy(feats, board=19, layers=len(convs) - 1, filters_per_layer=convs[0][0], dtype=dtype, **kw)
+        net.model.set_weights(weights)
+        for got in (net.forward(planes), net.model.eval_batch_device(batch, net.preprocessor.plane_src).cpu().numpy()):
+            assert np.abs(got - gold["probs"]).max() <= (2e-3 if dtype == "bf16" else 2e-5), dtype
+            assert (got.argmax(1) == gold["probs"].argmax(1)).mean() >= (0.9 if dtype == "bf16" else 0.98), dtype

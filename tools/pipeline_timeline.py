@@ -11,7 +11,7 @@ from rocalphago_b200.preprocessing import DEFAULT_FEATURES
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
 if len(sys.argv) > 3:
     _cabi.lib().rag_set_ladder_helpers(int(sys.argv[3]))
-net = CNNPolicy(DEFAULT_FEATURES, layers=12, filters_per_layer=192, dtype="fp16", seed=1)
+net = CNNPolicy(DEFAULT_FEATURES, layers=12, filters_per_layer=192, dtype=os.environ.get("DTYPE", "fp16c32"), seed=1)
 batches = [BatchedGameState.random_playouts(n, seed=5 + i) for i in range(4)]
 pipe = EvalPipeline(net, n, slots=int(sys.argv[2]) if len(sys.argv) > 2 else None)
 for i in range(8):
