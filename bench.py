@@ -137,6 +137,73 @@ def cpu_path(n_positions, cores, seed=99, pool=None, weights=None, keep=False):
     return t1 - t0, t3 - t2
 
 
+
+def _ref_python_worker(args):
+    """Preprocess.state_to_tensor of the reference's own Python (oracle/_ref snapshot) on a few positions."""
+    os.environ["RAG_REFERENCE_ROOT"] = os.path.join(ROOT, "oracle", "_ref")
+    from oracle import ref_shim
+    ref_shim.REFERENCE_ROOT = os.environ["RAG_REFERENCE_ROOT"]
+    go, prep = ref_shim.load()
+    b, a, ko, pl = args
+    states = [ref_shim.state_from_arrays(go, b[i].astype(float), a[i], int(ko[i]), int(pl[i])) for i in range(len(b))]
+    pp = prep.Preprocess(prep.DEFAULT_FEATURES)
+    t0 = time.time()
+    out = [pp.state_to_tensor(st) for st in states]
+    return time.time() - t0, np.concatenate(out).astype(np.uint8)
+
+
+def reference_python_features(n_single, n_per_core, cores, seed=4242, size=19, positions=None):
+    """The reference's own feature code (AlphaGo/preprocessing/preprocessing.py:266-294 on AlphaGo/go.py),
+    unmodified, timed on this host: one process on `n_single` random-playout positions, then one process per
+    core on `n_per_core` positions each.  None where oracle/_ref is absent (python -m oracle.make_ref_snapshot
+    writes it in the build container; it travels to the GPU box with the snapshot)."""
+    from oracle import go_oracle, make_ref_snapshot
+    if not make_ref_snapshot.available():
+        return None
+    import multiprocessing as mp
+    if positions is None:
+        # a random subset of many games' positions (consecutive ones would all come from one or two games)
+        pool_b, pool_a, pool_ko, pool_pl = go_oracle.random_playouts(4096, size=size, seed=seed)
+        pick = np.random.RandomState(seed).permutation(4096)[:n_single + n_per_core * cores]
+        positions = pool_b[pick], pool_a[pick], pool_ko[pick], pool_pl[pick]
+    b, a, ko, pl = positions
+    t1, planes = _ref_python_worker((b[:n_single], a[:n_single], ko[:n_single], pl[:n_single]))
+    want = go_oracle.features(b[:n_single], a[:n_single], ko[:n_single], pl[:n_single], go_oracle.DEFAULT_FEATURES)
+    out = {"single": {"value": n_single / t1, "unit": "positions/s (features only)", "cores": 1,
+                      "sample": "%d positions, %.2f s" % (n_single, t1),
+                      "planes_equal_c_port": bool(np.array_equal(planes, want))}}
+    if n_per_core > 0:
+        chunks = [(b[n_single + i * n_per_core:n_single + (i + 1) * n_per_core], a[n_single + i * n_per_core:n_single + (i + 1) * n_per_core],
+                   ko[n_single + i * n_per_core:n_single + (i + 1) * n_per_core], pl[n_single + i * n_per_core:n_single + (i + 1) * n_per_core])
+                  for i in range(cores)]
+        with mp.get_context("fork").Pool(cores) as pool:
+            pool.map(_ref_python_worker, [(c[0][:1], c[1][:1], c[2][:1], c[3][:1]) for c in chunks])     # imports, spin-up
+            t0 = time.time()
+            pool.map(_ref_python_worker, chunks)
+            tall = time.time() - t0
+        out["all_cores"] = {"value": n_per_core * cores / tall, "unit": "positions/s (features only)", "cores": cores,
+                            "sample": "%d positions on %d processes, %.2f s" % (n_per_core * cores, cores, tall)}
+    return out
+
+
+def reference_entries(cores, forward_pos_per_s):
+    """cpu_baseline entries for the reference's own Python: its features (1 core / all cores) followed serially
+    by the fp32 forward (policy.py:42-45 runs them one after the other; Keras cannot run here, so the forward
+    is the torch restatement at `forward_pos_per_s`)."""
+    ref = reference_python_features(24, 4, cores)
+    if ref is None:
+        return {}
+    out = {}
+    for key, name in (("single", "reference"), ("all_cores", "reference_all_cores")):
+        f = ref[key]["value"]
+        out[name] = {"value": 1.0 / (1.0 / f + 1.0 / forward_pos_per_s), "unit": "positions/s", "cores": ref[key]["cores"],
+                     "kind": "reference", "features_only": f,
+                     "sample": "Preprocess.state_to_tensor of the unmodified reference (oracle/_ref): " + ref[key]["sample"]
+                               + "; then the torch fp32 forward at %.0f pos/s" % forward_pos_per_s}
+    out["reference"]["planes_equal_c_port"] = ref["single"]["planes_equal_c_port"]
+    return out
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -160,12 +227,14 @@ def run_reference(args):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * (tf + tn) / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": "13x192 policy + 48 planes, 19x19; CPU port of the reference path "
-                               "(C feature oracle on all cores, then torch fp32 forward), %d positions/step" % sample},
+                               "(C feature oracle on all cores, then torch fp32 forward), %d positions/step" % sample,
+                   "batch_per_gpu": sample},
         "cpu_baseline": {"value": value, "unit": "positions/s", "cores": cores, "kind": "port",
                          "sample": "%d steps x %d random-playout positions; features %.2fs + forward %.2fs; wall %.1fs"
                                    % (args.steps, sample, tf, tn, total)},
         "e2e": {"value": value, "unit": "positions/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
+    line["cpu_baseline"].update(reference_entries(cores, sample * args.steps / tn))
     print(json.dumps(line))
 
 
@@ -413,20 +482,25 @@ def run_gpu(args):
                                     "sample": "%d random-playout positions once: C feature oracle on %d processes %.2fs "
                                               "(%.0f pos/s) + torch fp32 13x192 forward on %d threads %.2fs (%.0f pos/s)"
                                               % (sample, cores, tf, sample / tf, cores, tn, sample / tn)}
+            line["cpu_baseline"].update(reference_entries(cores, sample / tn))
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
 
 
 def run_features(args):
-    """BASELINE config 4: feature extraction only (all 48 planes incl. ladders) -> uint8 NCHW.
+    """BASELINE config 4: feature extraction only (all 48 planes incl. ladders) -> uint8 NCHW, over
+    `steps` x `batch` DISTINCT device-generated random-playout positions per GPU (default 32 x 32,768 =
+    1,048,576; never recycled inside the timed region when steps <= 32).
     Roofline: the emit kernel, the HBM-bound kernel of the feature path (17,568 B per position)."""
     import torch
     import torch.distributed as dist
     from rocalphago_b200 import BatchedGameState, Preprocess, _cabi
     from rocalphago_b200 import preprocessing as P
-    from rocalphago_b200.state import _ptr, _stream
+    from rocalphago_b200.state import _ptr
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device; there is no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
@@ -434,7 +508,8 @@ def run_features(args):
     n, K, W = args.batch, args.steps, max(3, args.warmup)
     L = _cabi.lib()
     pp = Preprocess()
-    pool = [BatchedGameState.random_playouts(n, seed=20261106 + 7919 * (rank * 4 + i), device=dev) for i in range(4)]
+    npool = min(K, 32)
+    pool = [BatchedGameState.random_playouts(n, seed=20261106 + 7919 * (rank * 64 + i), device=dev) for i in range(npool)]
     # `lanes` batches in flight, each on its own stream with its own workspace and output buffer: the
     # tail of one batch's ladder search (a few warps) runs under the bulk of the next batch's
     lanes = max(1, args.slots or 4)
@@ -444,15 +519,15 @@ def run_features(args):
     src = np.ascontiguousarray(pp.plane_src, np.int32)
     vp = ctypes.c_void_p
 
-    def step(b, lane, ev=None):
+    def step(packed, lane, ev=None):
         st = vp(streams[lane].cuda_stream)
-        _cabi.check(L.rag_features_analyze(_ptr(b.packed), n, 19, 1, _ptr(wss[lane]), wss[lane].numel(), st))
+        _cabi.check(L.rag_features_analyze(_ptr(packed), n, 19, 1, _ptr(wss[lane]), wss[lane].numel(), st))
         if ev: ev[0].record(streams[lane])
         _cabi.check(L.rag_features_emit(_ptr(wss[lane]), n, 19, src.ctypes.data_as(vp), len(src), P.LAYOUT_NCHW_U8, 0, 0,
                                         _ptr(outs[lane]), st))
         if ev: ev[1].record(streams[lane])
     for i in range(max(W, lanes)):
-        step(pool[i % 4], i % lanes)
+        step(pool[i % npool].packed, i % lanes)
     torch.cuda.synchronize()
     if world > 1: dist.barrier()
     sampler = ClockSampler(local)
@@ -463,13 +538,39 @@ def run_features(args):
     t0.record()
     for s_ in streams: s_.wait_event(t0)
     for k in range(K):
-        step(pool[k % 4], k % lanes, evs[k])
+        step(pool[k % npool].packed, k % lanes, evs[k])
     for s_ in streams: torch.cuda.current_stream().wait_stream(s_)
     t1.record()
     torch.cuda.synchronize()
     if world > 1: dist.barrier()
-    clocks = sampler.stop() if rank == 0 else None
     tot = t0.elapsed_time(t1)
+
+    # ---- end to end with host buffers: pinned packed states -> H2D -> features -> D2H of the uint8 planes,
+    #      every step, two lanes; the planes are 17,328 B per position, so this leg is bound by the host link
+    e2e_steps = min(K, 8)
+    h_in = [pool[i % npool].packed.cpu().pin_memory() for i in range(2)]
+    h_out = [torch.empty((n, 48, 19, 19), dtype=torch.uint8).pin_memory() for _ in range(2)]
+    d_in = [torch.empty_like(pool[0].packed) for _ in range(2)]
+
+    def e2e_step(k):
+        lane = k % 2
+        with torch.cuda.stream(streams[lane]):
+            d_in[lane].copy_(h_in[lane], non_blocking=True)
+            step(d_in[lane], lane)
+            h_out[lane].copy_(outs[lane], non_blocking=True)
+    for k in range(2):
+        e2e_step(k)
+    torch.cuda.synchronize()
+    if world > 1: dist.barrier()
+    w0 = time.time()
+    for k in range(e2e_steps):
+        e2e_step(k)
+    torch.cuda.synchronize()
+    e2e_ms = (time.time() - w0) * 1e3
+    checksum = int(h_out[0][0].sum()) + int(h_out[1][0].sum())
+    if world > 1: dist.barrier()
+    clocks = sampler.stop() if rank == 0 else None
+
     # the emit kernel alone (nothing else on the GPU), 256 MiB written before each launch: its roofline figure
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     solo = [(E(), E()) for _ in range(5)]
@@ -482,30 +583,153 @@ def run_features(args):
             b.record(streams[0])
     torch.cuda.synchronize()
     emit = sum(a.elapsed_time(b) for a, b in solo) / len(solo)
-    t = torch.tensor([tot], dtype=torch.float64, device=dev)
+    # what a write-only kernel can reach on this part: a plain fill of the same buffer, timed the same way
+    fills = [(E(), E()) for _ in range(5)]
+    with torch.cuda.stream(streams[0]):
+        for a, b in fills:
+            flush.zero_()
+            a.record(streams[0])
+            outs[1 % lanes].zero_()
+            b.record(streams[0])
+    torch.cuda.synchronize()
+    fill = sum(a.elapsed_time(b) for a, b in fills) / len(fills)
+    t = torch.tensor([tot, e2e_ms], dtype=torch.float64, device=dev)
     if world > 1: dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    tot = float(t.cpu())
+    tot, e2e_ms = [float(v) for v in t.cpu()]
     if rank == 0:
         peaks = load_peaks()
         achieved = FEATURE_BYTES * n / (emit / 1e3) / 1e9
-        print(json.dumps({
+        line = {
             "metric": "positions/sec: 48-plane feature extraction only, 19x19", "value": n * K * world / (tot / 1e3),
             "unit": "positions/s", "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": tot / K, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
             "config": {"workload": "feature-extraction-only sweep (BASELINE config 4): 48 planes incl. ladders -> uint8 NCHW, "
-                                   "%d positions/GPU/step, device-generated random playouts" % n,
+                                   "%d steps x %d = %d positions per GPU, %d distinct device-generated random-playout batches"
+                                   % (K, n, K * n, npool),
+                       "batch_per_gpu": n, "positions_per_gpu": K * n,
                        "schedule": "%d batches in flight on their own streams" % lanes,
-                       "l2": "no flush needed: every step writes %.0f MB of planes (%.1fx the 126 MB L2) and the input batches rotate"
-                             % (n * 17328 / 1e6, n * 17328 / 126e6)},
+                       "l2": "no flush needed: every step writes %.0f MB of planes (%.1fx the 126 MB L2) and every batch is new"
+                             % (n * 17328 / 1e6, n * 17328 / 126e6),
+                       "parallelism": "dp%d (independent positions, no collective)" % world},
+            "e2e": {"value": n * e2e_steps * world / (e2e_ms / 1e3), "unit": "positions/s", "h2d_bytes_per_step": int(n * 768),
+                    "d2h_bytes_per_step": int(n * 17328), "ms_per_step": e2e_ms / e2e_steps, "steps": e2e_steps, "checksum": checksum,
+                    "note": "bound by the device-to-host copy of the planes (17,328 B per position over the host link)"},
             "gpu_launches": 3 * K, "clocks": clocks,
-            "roofline": {"bound": "hbm", "kernel": "emit_u8_kernel", "achieved": achieved, "peak": peaks["hbm"], "unit": "GB/s",
+            "roofline": {"bound": "hbm", "kernel": "emit_u8_flat_kernel", "achieved": achieved, "peak": peaks["hbm"], "unit": "GB/s",
                          "frac": achieved / peaks["hbm"], "ms_per_launch": emit, "traffic": None,
+                         "write_only": {"fill_gbs": n * 17328 / (fill / 1e3) / 1e9, "fill_ms": fill, "emit_over_fill": fill / emit,
+                                        "note": "the kernel only writes (planes in: 0.2 of the bytes out); a plain fill of the same "
+                                                "buffer is what this part's HBM takes for write-only traffic -- `peak` is a COPY rate "
+                                                "(read + write), which a write-only kernel cannot reach"},
                          "peak_source": peaks["src"], "note": "17,568 algorithmic bytes per position (SURVEY 8d); the kernel timed alone after "
                          "the timed region (inside it, it overlaps other batches' ladder searches); the step itself is bound by "
                          "the latency of the ladder searches, not by HBM"},
-            "stage_ms": {"step": tot / K, "emit_u8_alone": emit}}))
+            "stage_ms": {"step": tot / K, "emit_u8_alone": emit,
+                         "analysis_and_ladders_mean": float(np.mean([a.elapsed_time(b) for a, b in evs]))}}
+        if world == 1 and not args.no_cpu_baseline:
+            import multiprocessing as mp
+            from oracle import go_oracle
+            cores = os.cpu_count() or 1
+            sample = args.cpu_sample * 8
+            b, a, ko, pl = go_oracle.random_playouts(sample, size=19, seed=99)
+            chunks = [(b[i::cores], a[i::cores], ko[i::cores], pl[i::cores]) for i in range(cores)]
+            with mp.get_context("fork").Pool(cores) as cp:
+                cp.map(_cpu_features_worker, [(c[0][:1], c[1][:1], c[2][:1], c[3][:1]) for c in chunks])
+                c0 = time.time()
+                cp.map(_cpu_features_worker, chunks)
+                tf = time.time() - c0
+            line["cpu_baseline"] = {"value": sample / tf, "unit": "positions/s", "cores": cores, "kind": "port",
+                                    "sample": "%d random-playout positions once: C feature oracle on %d processes, %.2f s" % (sample, cores, tf)}
+            ref = reference_python_features(24, 4, cores)
+            if ref:
+                line["cpu_baseline"]["reference"] = dict(ref["single"], kind="reference")
+                line["cpu_baseline"]["reference_all_cores"] = dict(ref["all_cores"], kind="reference")
+        print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+def run_cfg1(args):
+    """BASELINE config 1 (the reference's own CPU-runnable case): Preprocess(48 default features) +
+    CNNPolicy(layers=3, filters_per_layer=32).batch_eval_state on 16 positions of the reference's SGFs (plies
+    20 / 41 / 101 / 161 of the Lee Sedol games; states recorded from the reference's replay in
+    tests/golden/features_sgf.npz), through the reference-facing Python call on GameState-like objects
+    (policy.py:27-52) -- lists of ((x, y), p) out.  One step = one such call."""
+    import torch
+    from rocalphago_b200 import PositionView
+    from rocalphago_b200.models import CNNPolicy
+    from rocalphago_b200.preprocessing import DEFAULT_FEATURES
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device; there is no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(0)
+    z = np.load(os.path.join(ROOT, "tests", "golden", "features_sgf.npz"))
+    names = [str(v) for v in z["names"]]
+    pick = [i for i in range(len(z["ply"])) if "Lee-Sedol" in names[int(z["game"][i])] and int(z["ply"][i]) in (20, 41, 101, 161)][:16]
+    b, a, ko, pl = z["board"][pick], z["age"][pick], z["ko"][pick], z["player"][pick]
+    states = [PositionView(b[i], a[i], None if ko[i] < 0 else (int(ko[i]) // 19, int(ko[i]) % 19), int(pl[i])) for i in range(len(pick))]
+    net = CNNPolicy(DEFAULT_FEATURES, layers=3, filters_per_layer=32, seed=16)
+    K, W = args.steps, max(3, args.warmup)
+    for _ in range(W):
+        res = net.batch_eval_state(states)
+    torch.cuda.synchronize()
+    sampler = ClockSampler(0)
+    sampler.start()
+    lat = []
+    for _ in range(K):
+        t0 = time.perf_counter()
+        res = net.batch_eval_state(states)
+        lat.append(time.perf_counter() - t0)
+    clocks = sampler.stop()
+    lat = np.asarray(lat)
+    n = len(states)
+    line = {"metric": METRIC, "value": n / float(lat.mean()), "unit": "positions/s", "n_gpus": 1, "steps": K, "warmup": W,
+            "ms_per_step": 1e3 * float(lat.mean()), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": net.model.dtype, "data": "16 positions of the reference's SGF fixtures, random-init weights",
+            "config": {"workload": "BASELINE config 1: 48 planes + CNNPolicy(layers=3, filters_per_layer=32).batch_eval_state, "
+                                   "16 SGF positions as GameState-like objects, lists of ((x, y), p) out", "batch_per_gpu": n,
+                       "l2": "not flushed: a 16-position step touches < 1 MB; this configuration measures call latency"},
+            "e2e": {"value": n / float(lat.mean()), "unit": "positions/s", "h2d_bytes_per_step": n * 768, "d2h_bytes_per_step": n * 361 * 4,
+                    "ms_per_step": 1e3 * float(lat.mean()), "ms_p50": 1e3 * float(np.median(lat)), "ms_p99": 1e3 * float(np.percentile(lat, 99)),
+                    "note": "host objects in, Python lists out, every step: value and e2e are the same measurement here"},
+            "gpu_launches": 7 * K, "clocks": clocks,
+            "roofline": {"bound": "tensor", "kernel": "conv_umma_kernel (3 launches per step)", "achieved": 41_055_808 * n / float(lat.mean()) / 1e12,
+                         "peak": load_peaks()["tf_sustained"], "unit": "TFLOP/s", "frac": 41_055_808 * n / float(lat.mean()) / 1e12 / load_peaks()["tf_sustained"],
+                         "traffic": None, "note": "41.06 MFLOP per position (SURVEY 8d); a 16-position call is bound by launch and "
+                         "host latency, not by the tensor pipe -- the fraction is reported for completeness"}}
+    if not args.no_cpu_baseline:
+        from oracle import cnn_oracle, go_oracle
+        cores = os.cpu_count() or 1
+        planes = go_oracle.features(b, a, ko, pl, go_oracle.DEFAULT_FEATURES)
+        want = cnn_oracle.forward(net.model.get_weights(), planes, net.model.specs, threads=cores)
+        got = np.zeros_like(want)
+        for i, r in enumerate(res):
+            for (x, y), p in r:
+                got[i, x * 19 + y] = p
+        legal = got > 0
+        ref_norm = np.where(legal, want, 0)
+        ref_norm = ref_norm / ref_norm.sum(1, keepdims=True)
+        line["parity"] = {"max_abs": float(np.abs(got - ref_norm).max()), "top1": float((got.argmax(1) == ref_norm.argmax(1)).mean()), "n": n,
+                          "against": "C feature oracle + fp32 CPU forward, renormalised over the returned moves"}
+        t0 = time.time()
+        for _ in range(20):
+            cnn_oracle.forward(net.model.get_weights(), planes, net.model.specs, threads=cores)
+        t_fwd = (time.time() - t0) / 20
+        ref = reference_python_features(n, 0, cores, positions=(b, a, ko, pl))
+        t0 = time.time()
+        for _ in range(20):
+            go_oracle.features(b, a, ko, pl, go_oracle.DEFAULT_FEATURES)
+        t_port = (time.time() - t0) / 20
+        line["cpu_baseline"] = {"value": n / (t_port + t_fwd), "unit": "positions/s", "cores": cores, "kind": "port",
+                                "sample": "the same 16 positions: C feature oracle (1 thread) %.2f ms + torch fp32 3x32 forward %.2f ms" % (1e3 * t_port, 1e3 * t_fwd)}
+        if ref:
+            f = ref["single"]["value"]
+            line["cpu_baseline"]["reference"] = {"value": 1.0 / (1.0 / f + t_fwd / n), "unit": "positions/s", "cores": 1, "kind": "reference",
+                                                 "features_only": f, "planes_equal_c_port": ref["single"]["planes_equal_c_port"],
+                                                 "sample": "Preprocess.state_to_tensor of the unmodified reference on the same 16 positions ("
+                                                           + ref["single"]["sample"] + ") + the torch fp32 forward"}
+    print(json.dumps(line))
 
 
 def main():
@@ -521,9 +745,9 @@ def main():
                          "operands, 1.3x faster, at / below the gate on random-init weights), fp16x3 (fp32-like, 3x the MMA work)")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--cpu-sample", type=int, default=8192, help="positions the CPU port is timed on (~15 s on 16 cores)")
-    ap.add_argument("--ref-sample", type=int, default=256)
+    ap.add_argument("--ref-sample", type=int, default=4096, help="positions per step of the --impl reference arm (the GPU arm's batch)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default="policy", choices=["policy", "features", "policy+value", "value"],
+    ap.add_argument("--workload", default="policy", choices=["policy", "features", "policy+value", "value", "cfg1"],
                     help="policy: the flagship (features + 13x192 policy forward); features: BASELINE config 4; "
                          "policy+value: BASELINE config 5 (adds the 49-plane 13x192 value forward to every step)")
     ap.add_argument("--serial", action="store_true", help="also time the single-stream rag_eval_batch step")
@@ -537,7 +761,11 @@ def main():
     elif args.workload == "features":
         if args.batch == 4096:
             args.batch = 32768
+        if args.steps == 100:
+            args.steps = 32                 # 32 x 32,768 = 1,048,576 distinct positions per GPU
         run_features(args)
+    elif args.workload == "cfg1":
+        run_cfg1(args)
     elif args.workload == "value":
         if args.batch == 4096:
             args.batch = 1024

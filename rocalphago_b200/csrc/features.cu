@@ -537,7 +537,59 @@ emit_nchw_kernel(const uint32_t* __restrict__ planes, long long total, int S, Pl
     }
 }
 
-// uint8 NCHW, the layout of Preprocess.state_to_tensor: one CTA per position.  The F x S*S bytes
+// uint8 NCHW for boards of 15 lines and more, the layout of Preprocess.state_to_tensor -- the HBM-bound
+// kernel of the feature path (17,328 B out per position at F = 48, S = 19).  The output of the whole batch
+// is one flat byte stream; a thread makes 16 consecutive bytes of it in registers and stores them with
+// one instruction, so a warp writes 512 contiguous bytes at a time.  16 bytes never span more than two
+// board rows (S >= 15): bits y.. of the row word the chunk starts in, then the low bits of the next row
+// word (next row, next plane, or the next position's first plane); four bits become four bytes with one
+// multiply (nibble * 0x00204081 & 0x01010101).  A CTA walks kEmitChunks consecutive chunks per thread, so
+// the position of its first byte costs one 64-bit division and everything after that is 32-bit.
+constexpr int kEmitChunks = 8;
+
+template <int kS>
+__global__ void __launch_bounds__(256)
+emit_u8_flat_kernel(const uint32_t* __restrict__ planes, long long total, int n, int S_rt, PlaneMap map, uint8_t* __restrict__ out)
+{
+    const int S = kS ? kS : S_rt;
+    const int S2 = S * S, per_pos = map.F * S2;
+    const long long cta_base = (long long)blockIdx.x * (256 * kEmitChunks * 16);
+    long long pos64 = cta_base / per_pos;
+    int pos = (int)pos64;
+    int off = (int)(cta_base - pos64 * per_pos) + (int)threadIdx.x * 16;          // byte offset inside position `pos`
+    long long e0 = cta_base + (long long)threadIdx.x * 16;
+    #pragma unroll 2
+    for (int k = 0; k < kEmitChunks; k++, off += 256 * 16, e0 += 256 * 16) {
+        if (e0 >= total) return;
+        while (off >= per_pos) { off -= per_pos; pos++; }
+        const int f = off / S2, r = off - f * S2;
+        const int x = r / S, y = r - x * S;
+        const uint32_t* pl = planes + (size_t)pos * kPlaneWords;
+        const uint32_t row_mask = (1u << S) - 1u;
+        const uint32_t w0 = __ldg(pl + map.src[f] * 32 + x) & row_mask;
+        uint32_t w1 = 0;
+        if (S - y < 16) {                                   // the chunk runs into the next row word
+            int x1 = x + 1, f1 = f;
+            const uint32_t* pl1 = pl;
+            if (x1 == S) { x1 = 0; if (++f1 == map.F) { f1 = 0; pl1 += kPlaneWords; } }
+            if (pl1 == pl || pos + 1 < n) w1 = __ldg(pl1 + map.src[f1] * 32 + x1);
+        }
+        const uint32_t bits = ((w0 >> y) | (w1 << (S - y))) & 0xFFFFu;
+        uint4 v;
+        v.x = ((bits & 15u) * 0x00204081u) & 0x01010101u;
+        v.y = (((bits >> 4) & 15u) * 0x00204081u) & 0x01010101u;
+        v.z = (((bits >> 8) & 15u) * 0x00204081u) & 0x01010101u;
+        v.w = ((bits >> 12) * 0x00204081u) & 0x01010101u;
+        if (e0 + 16 <= total) {
+            *reinterpret_cast<uint4*>(out + e0) = v;       // (streaming / write-through hints measured no faster)
+        } else {
+            const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+            for (int j = 0; e0 + j < total; j++) out[e0 + j] = (uint8_t)(w[j >> 2] >> (8 * (j & 3)));
+        }
+    }
+}
+
+// uint8 NCHW for small boards (and outputs that are not 16-byte aligned): one CTA per position.  The F x S*S bytes
 // of a position are assembled in shared memory (each thread expands (plane, row) words into S
 // bytes), then leave as one contiguous, 16-byte-vectorised stream -- the HBM-bound kernel of the
 // feature path (17,328 B out and 3.6 KB of row words in per position at F = 48).
@@ -1037,7 +1089,13 @@ int rag_features_emit(const void* d_workspace, int n, int size, const int32_t* h
     const long long total = (long long)n * F * size * size;
     if (layout == RAG_LAYOUT_NCHW_U8) {
         const size_t smem = (size_t)F * size * size + 16;
-        if (smem <= 48 * 1024) {
+        if (size >= 15 && ((size_t)d_out & 15) == 0) {
+            const long long per_cta = 256ll * kEmitChunks * 16;
+            const long long blocks = (total + per_cta - 1) / per_cta;
+            if (blocks > 0x7fffffffll) return fail(RAG_EUNSUPPORTED, "batch too large for one emit launch");
+            if (size == 19) emit_u8_flat_kernel<19><<<(int)blocks, 256, 0, s>>>(planes, total, n, size, map, (uint8_t*)d_out);
+            else emit_u8_flat_kernel<0><<<(int)blocks, 256, 0, s>>>(planes, total, n, size, map, (uint8_t*)d_out);
+        } else if (smem <= 48 * 1024) {
             int blocks = n < 148 * 8 ? n : 148 * 8;
             emit_u8_kernel<<<blocks, 256, smem, s>>>(planes, n, size, map, (uint8_t*)d_out);
         } else {

@@ -37,12 +37,28 @@ def test_planes_bit_exact_vs_reference_golden(name):
 
 
 @pytest.mark.parametrize("size,n,seed", [(19, 12000, 101), (13, 2000, 102), (9, 2000, 103), (7, 1000, 104),
-                                         (6, 500, 105), (5, 500, 106), (2, 20, 107)])
+                                         (6, 500, 105), (5, 500, 106), (2, 20, 107), (17, 600, 108), (15, 601, 109),
+                                         (16, 333, 110)])
 def test_planes_bit_exact_vs_oracle_on_playouts(size, n, seed):
     b, a, ko, pl = go_oracle.random_playouts(n, size=size, seed=seed, max_ply=size * size + 40, stride=5)
     want = go_oracle.features(b, a, ko, pl, ALL)
     got = _gpu_planes(b, a, ko, pl)
     assert np.array_equal(got, want), _explain(got, want)
+
+
+@pytest.mark.parametrize("size", [19, 16])
+def test_flat_u8_emit_with_plane_lists_that_break_16_byte_alignment(size):
+    """The uint8 emit for boards of 15+ lines treats the batch's output as one flat byte stream cut into
+    16-byte chunks: with F*S*S not a multiple of 16 the chunks straddle rows, planes AND positions, and
+    the stream ends in a partial chunk."""
+    n = 37
+    b, a, ko, pl = go_oracle.random_playouts(n, size=size, seed=211, max_ply=size * size, stride=9)
+    for fl in (["ones"], ["board"], ["ladder_capture", "board", "zeros", "sensibleness", "ones"],
+               ["liberties", "ones", "turns_since", "capture_size", "legal", "board", "board"]):
+        want = go_oracle.features(b, a, ko, pl, fl)
+        for k in (n, 1, 2, 5):
+            got = _gpu_planes(b[:k], a[:k], ko[:k], pl[:k], fl)
+            assert np.array_equal(got, want[:k]), (fl, k)
 
 
 def test_feature_subsets_orders_repeats_and_float_layout():
