@@ -476,6 +476,20 @@ def run_gpu(args):
                                   "max_abs": float(np.abs(got - want).max()), "gate": {"top1": 0.995, "max_abs": 2e-3},
                                   "against": "the fp32 CPU forward timed for cpu_baseline, same positions and weights; "
                                              "outside the timed region (the 3-seed, 24,576-position gate is tests/test_gpu_network.py)"}
+                # the reference-facing Python call on host objects: CNNPolicy.batch_eval_state(list of n GameState-likes)
+                from rocalphago_b200 import PositionView
+                views = [PositionView(pb[i].astype(np.float64), pa[i].astype(np.int64), int(pko[i]), int(ppl[i])) for i in range(min(n, sample))]
+                best = None
+                for _ in range(4):
+                    t_py = time.perf_counter()
+                    res = net.batch_eval_state(views)
+                    first_state = res[0]
+                    t_py = time.perf_counter() - t_py
+                    best = t_py if best is None else min(best, t_py)
+                line["e2e_python"] = {"value": len(views) / best, "unit": "positions/s", "ms_per_call": 1e3 * best, "states": len(views),
+                                      "note": "CNNPolicy.batch_eval_state(list of GameState-like objects with float64 boards) -> "
+                                              "MoveDistributions (the reference's list of lists of ((x, y), p), tuples built when a "
+                                              "state is looked at); one synchronous call, best of 4; first state has %d moves" % len(first_state)}
             else:
                 tf, tn = cpu_path(sample, cores)
             line["cpu_baseline"] = {"value": sample / (tf + tn), "unit": "positions/s", "cores": cores, "kind": "port",

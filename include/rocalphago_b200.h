@@ -194,6 +194,15 @@ long long rag_conv_rows(int n, int size);
 int rag_select_moves(const float* d_probs, const void* d_workspace, int n, int size, float temperature,
                      int greedy, uint64_t seed, int32_t* d_moves, void* stream);
 
+/* batch_eval_state's per-state host loop (policy.py:46-52) for a batch, on the device: for position i the
+ * moves of get_legal_moves() in the reference's order -- legal non-eye points x-major, then (include_eyes
+ * != 0) legal own eyes x-major (go.py:465-480) -- as flat points x*S+y in d_moves[i*S*S ..], with the
+ * probabilities of d_probs renormalised over exactly those moves (_select_moves_and_normalize,
+ * policy.py:15-25) in d_out[i*S*S ..]; d_counts[i] = how many.  Entries past the count are not written.
+ * d_workspace: the analysis of the same n states. */
+int rag_move_distributions(const float* d_probs, const void* d_workspace, int n, int size, int include_eyes,
+                           int16_t* d_moves, float* d_out, int32_t* d_counts, void* stream);
+
 /* ------------------------------------------------------------------ state updates
  *
  * GameState.do_move (go.py:521-581) on packed states, in place, one move per

@@ -61,6 +61,7 @@ def lib():
         "rag_features_static_max_positions": (i32, []),
         "rag_conv_rows": (i64, [i32, i32]),
         "rag_select_moves": (i32, [vp, vp, i32, i32, c.c_float, i32, u64, vp, vp]),
+        "rag_move_distributions": (i32, [vp, vp, i32, i32, i32, vp, vp, vp, vp]),
         "rag_do_move": (i32, [vp, i32, i32, vp, vp, vp]),
         "rag_random_playouts": (i32, [vp, i32, i32, u64, i32, i32, vp, i32, vp]),
         "rag_playout_quota": (i32, [i32, i32]),

@@ -42,7 +42,7 @@ def build_library(force=False, verbose=False):
         subprocess.check_call(cmd)
         objs.append(obj)
     subprocess.check_call([_nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", LIB_PATH]
-                          + objs + ["-lcuda"])
+                          + objs + ["-lcuda", "-lpthread"])
     return LIB_PATH
 
 

@@ -23,6 +23,8 @@
 #include <cuda_fp16.h>
 #include <string.h>
 #include <mutex>
+#include <thread>
+#include <vector>
 
 namespace rag {
 
@@ -829,6 +831,54 @@ static int static_scratch_address(void** out) {
     return RAG_OK;
 }
 
+// batch_eval_state's host loop (policy.py:46-52) on the device: for every position the moves of
+// get_legal_moves() in the reference's order -- legal non-eye points x-major, then legal own eyes
+// x-major (go.py:465-480) -- with the network's probabilities renormalised over them
+// (_select_moves_and_normalize, policy.py:15-25).  One warp per position, lane r = board row r.
+__global__ void __launch_bounds__(128)
+move_dist_kernel(const float* __restrict__ probs, const uint32_t* __restrict__ planes, int n, int S, int include_eyes,
+                 int16_t* __restrict__ moves, float* __restrict__ out, int32_t* __restrict__ counts)
+{
+    const int pos = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (pos >= n) return;
+    const int P = S * S;
+    const uint32_t* pl = planes + (size_t)pos * kPlaneWords;
+    const uint32_t row_mask = (1u << S) - 1u;
+    uint32_t first = 0, second = 0;
+    if (lane < S) {
+        first = __ldg(pl + kPlaneSensibleness * 32 + lane) & row_mask;
+        if (include_eyes) second = __ldg(pl + kPlaneLegal * 32 + lane) & row_mask & ~first;
+    }
+    const float* pr = probs + (size_t)pos * P;
+    int16_t* mv = moves + (size_t)pos * P;
+    float* po = out + (size_t)pos * P;
+    int base = 0;
+    float sum = 0.f;
+    #pragma unroll
+    for (int pass = 0; pass < 2; pass++) {
+        uint32_t w = pass == 0 ? first : second;
+        const int mine = __popc(w);
+        int incl = mine;
+        for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+        int idx = base + incl - mine;
+        while (w) {
+            const int y = __ffs(w) - 1;
+            w &= w - 1;
+            const int p = lane * S + y;
+            const float v = pr[p];
+            mv[idx] = (int16_t)p;
+            po[idx] = v;
+            sum += v;
+            idx++;
+        }
+        base += __shfl_sync(0xffffffffu, incl, 31);
+    }
+    for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    __syncwarp();
+    for (int i = lane; i < base; i += 32) po[i] = po[i] / sum;
+    if (lane == 0) counts[pos] = base;
+}
+
 // ---- move selection for batched players (ai.py:33-45, 84-133) ----------------------------------
 //
 // One warp per position: the network's probabilities restricted to the sensible moves (plane 46 of
@@ -932,36 +982,68 @@ extern "C" {
 const char* rag_last_error(void) { return last_error_buffer(); }
 int rag_abi_version(void) { return 6; }
 
+// packs positions [b0, b1); returns 0 or the index + 1 of the first bad position (reason in *why)
+static int pack_range(int b0, int b1, int size, const int8_t* h_board, const int16_t* h_age, const int32_t* h_ko,
+                      const int32_t* h_player, uint32_t* h_packed, int* why)
+{
+    const int np = size * size;
+    for (int b = b0; b < b1; b++) {
+        uint32_t* st = h_packed + (size_t)b * RAG_STATE_WORDS;
+        memset(st, 0, RAG_STATE_BYTES);
+        const int8_t* bd = h_board + (size_t)b * np;
+        const int16_t* ag = h_age + (size_t)b * np;
+        for (int x = 0; x < size; x++) {
+            uint32_t black = 0, white = 0, a0 = 0, a1 = 0, a2 = 0, ageless = 0;
+            for (int y = 0; y < size; y++) {
+                const int v = bd[x * size + y];
+                if (v == 0) continue;
+                if (v != 1 && v != -1) { *why = 1; return b + 1; }
+                const uint32_t bit = 1u << y;
+                if (v > 0) black |= bit; else white |= bit;
+                int a = ag[x * size + y];
+                if (a < 0) ageless |= bit;                       // a stone GameState.copy() left without an age
+                a = a < 0 ? 0 : (a > 7 ? 7 : a);
+                if (a & 1) a0 |= bit;
+                if (a & 2) a1 |= bit;
+                if (a & 4) a2 |= bit;
+            }
+            st[x] = black; st[32 + x] = white; st[64 + x] = a0; st[96 + x] = a1; st[128 + x] = a2; st[kAgelessWord + x] = ageless;
+        }
+        if (h_ko[b] >= np) { *why = 2; return b + 1; }
+        if (h_player[b] != 1 && h_player[b] != -1) { *why = 3; return b + 1; }
+        st[160] = (uint32_t)(h_ko[b] < 0 ? -1 : h_ko[b]);
+        st[161] = (uint32_t)h_player[b];
+        st[162] = (uint32_t)size;
+    }
+    return 0;
+}
+
 int rag_pack_states(int n, int size, const int8_t* h_board, const int16_t* h_age, const int32_t* h_ko,
                     const int32_t* h_player, uint32_t* h_packed)
 {
     if (n < 0 || !h_board || !h_age || !h_ko || !h_player || !h_packed) return fail(RAG_EINVAL, "null argument");
     if (int rc = check_size(size)) return rc;
-    const int np = size * size;
-    for (int b = 0; b < n; b++) {
-        uint32_t* st = h_packed + (size_t)b * RAG_STATE_WORDS;
-        memset(st, 0, RAG_STATE_BYTES);
-        const int8_t* bd = h_board + (size_t)b * np;
-        const int16_t* ag = h_age + (size_t)b * np;
-        for (int x = 0; x < size; x++)
-            for (int y = 0; y < size; y++) {
-                int v = bd[x * size + y];
-                if (v == 0) continue;
-                if (v != 1 && v != -1) return fail(RAG_EINVAL, "board[%d][%d][%d] = %d", b, x, y, v);
-                st[(v > 0 ? 0 : 32) + x] |= 1u << y;
-                int a = ag[x * size + y];
-                if (a < 0) st[kAgelessWord + x] |= 1u << y;       // a stone GameState.copy() left without an age
-                a = a < 0 ? 0 : (a > 7 ? 7 : a);
-                if (a & 1) st[64 + x] |= 1u << y;
-                if (a & 2) st[96 + x] |= 1u << y;
-                if (a & 4) st[128 + x] |= 1u << y;
-            }
-        if (h_ko[b] >= np) return fail(RAG_EINVAL, "ko[%d] = %d out of range", b, h_ko[b]);
-        if (h_player[b] != 1 && h_player[b] != -1) return fail(RAG_EINVAL, "player[%d] = %d", b, h_player[b]);
-        st[160] = (uint32_t)(h_ko[b] < 0 ? -1 : h_ko[b]);
-        st[161] = (uint32_t)h_player[b];
-        st[162] = (uint32_t)size;
+    // large batches (a 4,096-state batch_eval_state call) are split over a few host threads
+    int nt = n >= 1024 ? (int)std::thread::hardware_concurrency() : 1;
+    nt = nt < 1 ? 1 : (nt > 8 ? 8 : nt);
+    std::vector<int> bad(nt, 0), why(nt, 0);
+    if (nt == 1) bad[0] = pack_range(0, n, size, h_board, h_age, h_ko, h_player, h_packed, &why[0]);
+    else {
+        std::vector<std::thread> th;
+        const int per = (n + nt - 1) / nt;
+        for (int t = 0; t < nt; t++) {
+            const int b0 = t * per, b1 = b0 + per < n ? b0 + per : n;
+            th.emplace_back([=, &bad, &why]() { if (b0 < b1) bad[t] = pack_range(b0, b1, size, h_board, h_age, h_ko, h_player, h_packed, &why[t]); });
+        }
+        for (auto& t : th) t.join();
     }
+    for (int t = 0; t < nt; t++)
+        if (bad[t]) {
+            const int b = bad[t] - 1;
+            if (why[t] == 1) return fail(RAG_EINVAL, "board[%d] holds a value other than -1, 0, +1", b);
+            if (why[t] == 2) return fail(RAG_EINVAL, "ko[%d] = %d out of range", b, h_ko[b]);
+            return fail(RAG_EINVAL, "player[%d] = %d", b, h_player[b]);
+        }
     return RAG_OK;
 }
 
@@ -1155,6 +1237,18 @@ int rag_features_static(const uint32_t* d_states, int n, int size, const int32_t
 }
 
 long long rag_conv_rows(int n, int size) { return conv_rows(n, size); }
+
+int rag_move_distributions(const float* d_probs, const void* d_workspace, int n, int size, int include_eyes,
+                           int16_t* d_moves, float* d_out, int32_t* d_counts, void* stream)
+{
+    if (n < 0 || (n > 0 && (!d_probs || !d_workspace || !d_moves || !d_out || !d_counts))) return fail(RAG_EINVAL, "null argument");
+    if (int rc = check_size(size)) return rc;
+    if (n == 0) return RAG_OK;
+    const uint32_t* planes = (const uint32_t*)((const char*)d_workspace + kCounterBytes);
+    move_dist_kernel<<<(n + 3) / 4, 128, 0, (cudaStream_t)stream>>>(d_probs, planes, n, size, include_eyes, d_moves, d_out, d_counts);
+    RAG_CUDA_CHECK(cudaGetLastError());
+    return RAG_OK;
+}
 
 int rag_select_moves(const float* d_probs, const void* d_workspace, int n, int size, float temperature, int greedy,
                      uint64_t seed, int32_t* d_moves, void* stream)

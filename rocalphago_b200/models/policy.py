@@ -1,8 +1,13 @@
 """CNNPolicy on the B200 path (drop-in for AlphaGo/models/policy.py:9-138)."""
-import numpy as np
+import collections.abc
+import ctypes
 
+import numpy as np
+import torch
+
+from .. import _cabi
 from ..preprocessing import _points
-from ..state import BatchedGameState
+from ..state import BatchedGameState, _ptr, _stream
 from .nn_util import NeuralNetBase, Network, neuralnet
 
 
@@ -11,6 +16,60 @@ from .nn_util import NeuralNetBase, Network, neuralnet
 # rocalphago_b200.h RAG_DTYPE_FP16C32).  Plain 'fp16' is 1.3x faster but sits at north_star's 99.5 %
 # top-1 gate on random-init weights (99.4-99.8 % by seed); this mode holds it (99.6-99.9 %).
 DEFAULT_POLICY_DTYPE = "fp16c32"
+
+
+class MoveList(collections.abc.Sequence):
+    """One state's [((x, y), probability), ...] (policy.py:15-25), built from the batch's arrays the first
+    time it is looked at.  Behaves like the reference's list for what its callers do with it -- len(),
+    indexing, slicing, iteration, zip(*dist) (ai.py:118-124), == with a list -- without a million tuples
+    being made for a 4,096-state batch nobody reads in full."""
+    __slots__ = ("_dist", "_i", "_items")
+
+    def __init__(self, dist, i):
+        self._dist, self._i, self._items = dist, i, None
+
+    def to_list(self):
+        if self._items is None:
+            d, i = self._dist, self._i
+            c = int(d.counts[i])
+            pts = d.points
+            self._items = list(zip([pts[p] for p in d.moves[i, :c].tolist()], d.probs[i, :c].tolist()))
+        return self._items
+
+    def __len__(self):
+        return int(self._dist.counts[self._i])
+
+    def __getitem__(self, k):
+        return self.to_list()[k]
+
+    def __iter__(self):
+        return iter(self.to_list())
+
+    def __eq__(self, other):
+        if isinstance(other, MoveList):
+            other = other.to_list()
+        return self.to_list() == other if isinstance(other, list) else NotImplemented
+
+    __hash__ = None
+
+    def __repr__(self):
+        return repr(self.to_list())
+
+
+class MoveDistributions(object):
+    """The arrays behind a batch_eval_state result: `.moves` int16 (n, S*S) flat points x*S+y in
+    get_legal_moves() order, `.probs` float32 (n, S*S) renormalised over them, `.counts` int32 (n,);
+    entries past a state's count are undefined.  `as_list()` gives the reference-shaped view."""
+
+    def __init__(self, moves, probs, counts, size):
+        self.moves, self.probs, self.counts, self.size = moves, probs, counts, int(size)
+        self.points = _points(self.size)
+
+    def __len__(self):
+        return int(self.counts.shape[0])
+
+    def as_list(self):
+        return [MoveList(self, i) for i in range(len(self))]
 
 
 def flatten_idx(position, size):
@@ -37,13 +96,25 @@ class CNNPolicy(NeuralNetBase):
         """batch_eval_state of a BatchedGameState as flat arrays: (state index, flat move x*S+y,
         moves per state, probability renormalised over each state's legal moves), moves in
         get_legal_moves() order.  What batched callers (players, tree search) consume."""
-        n = len(batch)
+        dist = self.eval_distributions(batch)
+        inside = np.arange(batch.size * batch.size)[None, :] < dist.counts[:, None]
+        which = np.nonzero(inside)[0]
+        return which, dist.moves[inside].astype(np.int64), dist.counts.astype(np.int64), dist.probs[inside]
+
+    def eval_distributions(self, batch):
+        """batch_eval_state of a BatchedGameState with the move lists left on the device path: features,
+        forward, then rag_move_distributions (get_legal_moves() order and renormalisation per state) and
+        one copy of three arrays to the host.  Returns a MoveDistributions."""
+        n, P = len(batch), batch.size * batch.size
         probs = self.model.eval_batch_device(batch, self.preprocessor.plane_src)
-        which, flat, counts = self.preprocessor.legal_move_indices(self.model.features_workspace(), n, batch.size)
-        picked = probs.cpu().numpy()[which, flat]
-        # per-state sums: states without a legal move (counts == 0) own no entry of `picked`
-        sums = np.bincount(which, weights=picked, minlength=n).astype(picked.dtype)
-        return which, flat, counts, picked / np.repeat(sums, counts)
+        dev = batch.device
+        moves = torch.empty((n, P), dtype=torch.int16, device=dev)
+        out = torch.empty((n, P), dtype=torch.float32, device=dev)
+        counts = torch.empty((n,), dtype=torch.int32, device=dev)
+        with torch.cuda.device(dev):
+            _cabi.check(_cabi.lib().rag_move_distributions(_ptr(probs), _ptr(self.model.features_workspace()), n, batch.size, 1,
+                                                           _ptr(moves), _ptr(out), _ptr(counts), _stream()))
+        return MoveDistributions(moves.cpu().numpy(), out.cpu().numpy(), counts.cpu().numpy(), batch.size)
 
     def batch_eval_state(self, states, moves_lists=None):
         """Given a list of states (or a BatchedGameState), evaluates them all at once.
@@ -63,13 +134,9 @@ class CNNPolicy(NeuralNetBase):
                 raise ValueError("all states must have the same size")
             batch = BatchedGameState.from_states(states)
         if not moves_lists:
-            # all legal moves of every state: select and renormalise in one vectorised pass
-            _, flat, counts, picked = self.eval_arrays(batch)
-            picked = picked.tolist()
-            points = _points(state_size)
-            moves = [points[p] for p in flat.tolist()]
-            ends = np.cumsum(counts).tolist()
-            return [list(zip(moves[e - c:e], picked[e - c:e])) for e, c in zip(ends, counts.tolist())]
+            # all legal moves of every state, selected and renormalised on the device; a list with one
+            # MoveList per state, whose tuples are made when the caller looks at that state
+            return self.eval_distributions(batch).as_list()
         probs = self.model.eval_batch_device(batch, self.preprocessor.plane_src)
         network_output = probs.cpu().numpy()
         results = [None] * n_states
@@ -80,7 +147,8 @@ class CNNPolicy(NeuralNetBase):
     def eval_state(self, state, moves=None):
         """Given a GameState object, returns a list of (action, probability) pairs
         according to the network outputs (policy.py:54-64)"""
-        return self.batch_eval_state([state], [moves] if moves else None)[0]
+        dist = self.batch_eval_state([state], [moves] if moves else None)[0]
+        return dist.to_list() if isinstance(dist, MoveList) else dist
 
     @staticmethod
     def create_network(**kwargs):

@@ -332,6 +332,35 @@ def test_batch_eval_state_matches_reference_api():
     del sub
 
 
+def test_move_distributions_follow_the_references_move_order_and_behave_like_its_lists():
+    """batch_eval_state without move lists: moves in get_legal_moves() order as recorded from the reference
+    (tests/golden/features_sgf.npz), probabilities renormalised over them, and the lazy result object
+    indistinguishable from the reference's list of lists for the ways its callers use it (ai.py:107-133)."""
+    g = gu.load_features("features_sgf.npz")
+    n = 60
+    batch = BatchedGameState.from_arrays(g["board"][:n], g["age"][:n], g["ko"][:n], g["player"][:n])
+    net = CNNPolicy(go_oracle.DEFAULT_FEATURES, layers=2, filters_per_layer=32, seed=33)
+    res = net.batch_eval_state(batch)
+    raw = net.model.eval_batch_device(batch, net.preprocessor.plane_src).cpu().numpy()
+    assert len(res) == n
+    for i in range(n):
+        want_moves = g["legal_moves"][i, :g["n_legal"][i]].tolist()
+        assert [x * 19 + y for (x, y), _ in res[i]] == want_moves
+        ref = raw[i, want_moves] / raw[i, want_moves].sum()
+        assert np.abs(np.array([p for _, p in res[i]]) - ref).max() <= 1e-6
+        assert all(isinstance(m, tuple) and isinstance(p, float) for m, p in res[i][:3])
+    as_list = [list(r) for r in res]
+    assert isinstance(res, list) and res == as_list and res[-1] == as_list[-1] and res[2:5] == as_list[2:5]
+    assert res[3].to_list() == as_list[3] and res[3][1:4] == as_list[3][1:4] and res[3][-1] == as_list[3][-1]
+    moves, probs = zip(*res[0])                                   # ai.py:121
+    assert len(moves) == len(probs) == len(res[0]) == g["n_legal"][0]
+    with pytest.raises(IndexError):
+        res[0][len(res[0])]
+    which, flat, counts, pr = net.eval_arrays(batch)
+    assert counts.tolist() == g["n_legal"][:n].tolist() and len(which) == len(flat) == len(pr) == counts.sum()
+    assert flat[:counts[0]].tolist() == g["legal_moves"][0, :counts[0]].tolist()
+
+
 def test_batch_eval_state_when_the_last_states_have_no_legal_move():
     """A terminal position sorting last in a batch (an MCTS wave does this) must not disturb the
     renormalisation of the states before it.  5x5: WHITE owns everything but two one-point eyes,
