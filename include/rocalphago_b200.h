@@ -117,6 +117,16 @@ int rag_set_ladder_handover(int moves);
  * previous value. */
 int rag_set_ladder_helpers(int ctas);
 
+/* The ladder kernel never spins without bound: a warp that has waited longer than the watchdog (SM clock
+ * cycles, default 2e10 ~ 10 s; rag_set_ladder_watchdog returns the previous value, <= 0 only reads it)
+ * for work it handed to another warp gives the search up and marks the workspace.
+ * rag_features_status waits for `stream` and returns RAG_ECUDA with a message if a ladder kernel that
+ * wrote this workspace did so (its ladder planes are then incomplete), RAG_OK otherwise.  The Python
+ * layer calls it wherever it synchronises anyway.  No reference counterpart (go.py:329-463 recurses on
+ * one thread); the liveness argument is in DESIGN.md. */
+long long rag_set_ladder_watchdog(long long cycles);
+int rag_features_status(const void* d_workspace, void* stream);
+
 /* Positional superko (go.py:242-265, 282-283) for states created with enforce_superko=True: what
  * is_positional_superko reads, per position, in device memory.  q = x*32 + y.
  *   d_zobrist  uint64 [2][1024]: hash_lookup by q, [0] BLACK, [1] WHITE           (go.py:58-62)

@@ -46,7 +46,7 @@ struct StealTask {
 };
 static_assert(sizeof(StealTask) == 512, "StealTask layout");
 enum { kTaskFree = 0, kTaskPosted = 1, kTaskTaken = 2, kTaskDone0 = 3, kTaskDone1 = 4, kTaskCancelled = 5 };
-enum { kCtlQueued = 0, kCtlTaken = 1, kCtlPosted = 2, kCtlBusy = 4, kCtlAllocCursor = 5 };
+enum { kCtlQueued = 0, kCtlTaken = 1, kCtlPosted = 2, kCtlBusy = 4, kCtlAllocCursor = 5, kCtlTimeout = 6 };
 
 struct Workspace {
     unsigned* counters;      // kCtl* slots
@@ -264,7 +264,7 @@ struct TaskCancelled {                    // "has the task I am working on been 
 // ladder_dfs (go_bb.cuh) with hand-over of replies.  `nodes` = moves tried so far by this search.
 __device__ __noinline__ int ladder_dfs_steal(const Workspace& ws, const Geo& g, BB H, BB P, BB G, int ko, BB pending,
                                              bool frame_is_capture, int remaining_children, int nodes, int steal_after,
-                                             LadderStack& st, StealFrames& sf, const int* own_status, long long t_start)
+                                             LadderStack& st, StealFrames& sf, const int* own_status, long long t_deadline)
 {
     TaskCancelled cancelled{own_status};
     int d = 0;
@@ -325,7 +325,13 @@ __device__ __noinline__ int ladder_dfs_steal(const Workspace& ws, const Geo& g, 
                 if (stt == kTaskDone0 || stt == kTaskDone1) break;
                 if (cancelled()) { stt = -1; break; }
                 __nanosleep(200);
-                if (clock64() - t_start > 20000000000ll) __trap();   // never hang the device
+                // never hang the device: past the deadline the wait is given up, the search unwinds as
+                // aborted, and the workspace is marked (rag_features_status reports it)
+                if (LANE0_INT(clock64() > t_deadline || ld_vol(&ws.counters[kCtlTimeout]) != 0u)) {
+                    if (g.lane == 0) atomicExch(&ws.counters[kCtlTimeout], 1u);
+                    stt = -1;
+                    break;
+                }
             }
             if (stt < 0) v = kLadderAborted;
             else {
@@ -352,11 +358,11 @@ __device__ __noinline__ int ladder_dfs_steal(const Workspace& ws, const Geo& g, 
 // is_ladder_capture / is_ladder_escape of one move on one prey group, with hand-over.
 __device__ __forceinline__ int ladder_search_steal(const Workspace& ws, const Geo& g, BB H, BB P, BB G, int ko, int move,
                                                    bool is_capture, int remaining, int nodes, int steal_after, LadderStack& st,
-                                                   StealFrames& sf, const int* own_status, long long t_start) {
+                                                   StealFrames& sf, const int* own_status, long long t_deadline) {
     BB pending = bb_zero();
     const int res = ladder_expand(g, is_capture, H, P, G, ko, move, remaining, pending);
     if (res != kLadderPush) return res;
-    return ladder_dfs_steal(ws, g, H, P, G, ko, pending, is_capture, remaining - 1, nodes + 1, steal_after, st, sf, own_status, t_start);
+    return ladder_dfs_steal(ws, g, H, P, G, ko, pending, is_capture, remaining - 1, nodes + 1, steal_after, st, sf, own_status, t_deadline);
 }
 
 // kBesideConv only makes two copies of the kernel, so that each can have its own shared-memory / L1
@@ -365,12 +371,12 @@ __device__ __forceinline__ int ladder_search_steal(const Workspace& ws, const Ge
 // stage, which runs underneath the convolutions of another stream.
 template <int kBesideConv>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
-ladder_kernel(const uint32_t* __restrict__ states, int S, int steal_after, int helper_ctas, Workspace ws)
+ladder_kernel(const uint32_t* __restrict__ states, int S, int steal_after, int helper_ctas, long long watchdog, Workspace ws)
 {
     const Geo g = make_geo(S);
     LadderStack st;
     StealFrames sf;
-    const long long t_start = clock64();
+    const long long t_deadline = clock64() + watchdog;
     const unsigned total = min((unsigned)ws.queue_cap, ws.counters[kCtlQueued]);
 
     // ---- work items
@@ -395,8 +401,8 @@ ladder_kernel(const uint32_t* __restrict__ states, int S, int steal_after, int h
         const int np = ladder_root_preys(g, own, opp, q, is_escape, preys);
         int r = kLadderValue0;
         for (int i = 0; i < np && r == kLadderValue0; i++)
-            r = is_escape ? ladder_search_steal(ws, g, opp, own, preys[i], ko, q, false, kLadderDepth, 0, steal_after, st, sf, nullptr, t_start)
-                          : ladder_search_steal(ws, g, own, opp, preys[i], ko, q, true, kLadderDepth, 0, steal_after, st, sf, nullptr, t_start);
+            r = is_escape ? ladder_search_steal(ws, g, opp, own, preys[i], ko, q, false, kLadderDepth, 0, steal_after, st, sf, nullptr, t_deadline)
+                          : ladder_search_steal(ws, g, own, opp, preys[i], ko, q, true, kLadderDepth, 0, steal_after, st, sf, nullptr, t_deadline);
 #ifdef RAG_LADDER_TIMING
         if (g.lane == 0) ws.queue[idx] = (uint32_t)((clock64() - t_item) >> 4);     // tools/ladder_profile.py
 #endif
@@ -444,7 +450,10 @@ ladder_kernel(const uint32_t* __restrict__ states, int S, int steal_after, int h
             if (done) break;
             __nanosleep(nap);
             if (nap < 8000) nap += nap / 2;
-            if (clock64() - t_start > 20000000000ll) __trap();        // never hang the device
+            if (LANE0_INT(clock64() > t_deadline || ld_vol(&ws.counters[kCtlTimeout]) != 0u)) {   // never hang the device
+                if (g.lane == 0) atomicExch(&ws.counters[kCtlTimeout], 1u);
+                break;
+            }
         }
         if (slot < 0) break;
         nap = 500;
@@ -454,7 +463,7 @@ ladder_kernel(const uint32_t* __restrict__ states, int S, int steal_after, int h
         const BB H{__ldcg(&t->H[g.lane])}, P{__ldcg(&t->P[g.lane])}, G{__ldcg(&t->G[g.lane])};
         const int ko = LANE0_INT(ld_vol(&t->ko)), move = LANE0_INT(ld_vol(&t->move));
         const int is_capture = LANE0_INT(ld_vol(&t->is_capture)), remaining = LANE0_INT(ld_vol(&t->remaining));
-        const int r = ladder_search_steal(ws, g, H, P, G, ko, move, is_capture != 0, remaining, 0, steal_after, st, sf, tstat, t_start);
+        const int r = ladder_search_steal(ws, g, H, P, G, ko, move, is_capture != 0, remaining, 0, steal_after, st, sf, tstat, t_deadline);
         if (g.lane == 0) {
             __threadfence();
             if (r == kLadderAborted) atomicExch(tstat, kTaskFree);
@@ -954,6 +963,7 @@ select_moves_kernel(const float* __restrict__ probs, const uint32_t* __restrict_
 }
 
 static int g_steal_after = kStealAfterDefault;      // rag_set_ladder_handover
+static long long g_ladder_watchdog = 20000000000ll; // rag_set_ladder_watchdog: SM clock cycles a ladder kernel may wait for handed-over work
 static int g_helper_ctas = 32;                      // rag_set_ladder_helpers
 
 static int check_size(int size) {
@@ -1098,7 +1108,7 @@ int rag_features_analyze(const uint32_t* d_states, int n, int size, int with_lad
         const int cap = 8;
         long long want = ((long long)n * 16 + kWarpsPerBlock - 1) / kWarpsPerBlock;
         int blocks = (int)(want < (long long)sms * cap ? (want < 1 ? 1 : want) : (long long)sms * cap);
-        ladder_kernel<0><<<blocks, kWarpsPerBlock * 32, 0, s>>>(d_states, size, g_steal_after, g_helper_ctas, ws);
+        ladder_kernel<0><<<blocks, kWarpsPerBlock * 32, 0, s>>>(d_states, size, g_steal_after, g_helper_ctas, g_ladder_watchdog, ws);
         RAG_CUDA_CHECK(cudaGetLastError());
     }
     return RAG_OK;
@@ -1120,7 +1130,7 @@ int rag_features_ladders(const uint32_t* d_states, int n, int size, void* d_work
     RAG_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     long long want = ((long long)n * 16 + kWarpsPerBlock - 1) / kWarpsPerBlock;
     int blocks = (int)(want < (long long)sms * 4 ? (want < 1 ? 1 : want) : (long long)sms * 4);
-    ladder_kernel<1><<<blocks, kWarpsPerBlock * 32, 0, (cudaStream_t)stream>>>(d_states, size, g_steal_after, g_helper_ctas, ws);
+    ladder_kernel<1><<<blocks, kWarpsPerBlock * 32, 0, (cudaStream_t)stream>>>(d_states, size, g_steal_after, g_helper_ctas, g_ladder_watchdog, ws);
     RAG_CUDA_CHECK(cudaGetLastError());
     return RAG_OK;
 }
@@ -1214,6 +1224,19 @@ int rag_features(const uint32_t* d_states, int n, int size, const int32_t* h_pla
 }
 
 int rag_set_ladder_helpers(int ctas) { int old = g_helper_ctas; g_helper_ctas = ctas < 0 ? 1 << 30 : ctas; return old; }
+long long rag_set_ladder_watchdog(long long cycles) { long long old = g_ladder_watchdog; if (cycles > 0) g_ladder_watchdog = cycles; return old; }
+
+int rag_features_status(const void* d_workspace, void* stream)
+{
+    if (!d_workspace) return fail(RAG_EINVAL, "null argument");
+    unsigned flag = 0;
+    RAG_CUDA_CHECK(cudaMemcpyAsync(&flag, (const char*)d_workspace + kCtlTimeout * sizeof(unsigned), sizeof flag, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    RAG_CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream));
+    if (flag) return fail(RAG_ECUDA, "the ladder reader gave up waiting for handed-over work (watchdog of %lld cycles): the ladder planes of this "
+                                     "workspace are incomplete; run the batch again", g_ladder_watchdog);
+    return RAG_OK;
+}
+
 int rag_set_ladder_handover(int moves) { int old = g_steal_after; g_steal_after = moves < 0 ? 1 << 30 : moves; return old; }
 
 int rag_features_static_max_positions(void) { return kStaticMaxPositions; }

@@ -6,7 +6,7 @@ import numpy as np
 import torch
 
 from .. import _cabi
-from ..preprocessing import _points
+from ..preprocessing import _points, check_workspace
 from ..state import BatchedGameState, _ptr, _stream
 from .nn_util import NeuralNetBase, Network, neuralnet
 
@@ -114,6 +114,7 @@ class CNNPolicy(NeuralNetBase):
         with torch.cuda.device(dev):
             _cabi.check(_cabi.lib().rag_move_distributions(_ptr(probs), _ptr(self.model.features_workspace()), n, batch.size, 1,
                                                            _ptr(moves), _ptr(out), _ptr(counts), _stream()))
+        check_workspace(self.model.features_workspace())
         return MoveDistributions(moves.cpu().numpy(), out.cpu().numpy(), counts.cpu().numpy(), batch.size)
 
     def batch_eval_state(self, states, moves_lists=None):

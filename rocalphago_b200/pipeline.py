@@ -100,7 +100,7 @@ class EvalPipeline(object):
             # attractive, but with the CTA-pair convolution kernel -- a cluster launch -- and the
             # persistent ladder kernel in flight together, prioritised streams stopped making
             # progress on B200 / driver 580; equal priorities never did in any run.)
-            self.s_net, self.s_copy = torch.cuda.Stream(), torch.cuda.Stream()
+            self.s_net, self.s_copy, self.s_stat = torch.cuda.Stream(), torch.cuda.Stream(), torch.cuda.Stream()
         self.channels = int(self.L.rag_net_input_channels(self.handle))
         self.dtype_code = 0 if self.model.dtype == "bf16" else 1
         self.count = 0
@@ -199,6 +199,8 @@ class EvalPipeline(object):
             raise ValueError("ticket %d is no longer (or not yet) in flight" % ticket)
         slot = self.slots[ticket % self.nslots]
         slot.out_copied.synchronize()
+        with torch.cuda.device(self.device):       # did this batch's ladder kernel give up (watchdog)?  4 bytes on a stream of its own
+            _cabi.check(self.L.rag_features_status(_ptr(slot.fws), ctypes.c_void_p(self.s_stat.cuda_stream)))
         out = slot.host_out if slot.to_host else slot.out
         if self.vhandle is not None:
             return out, (slot.host_vout if slot.to_host else slot.vout)

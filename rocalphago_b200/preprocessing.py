@@ -80,6 +80,13 @@ def analyze_into(batch, ws, with_ladders=True):
                                                _ptr(ws), ws.numel(), _stream()))
 
 
+def check_workspace(ws):
+    """rag_features_status: waits for the current stream and raises if a ladder kernel gave up on `ws`
+    (its watchdog, include/rocalphago_b200.h).  Called where results are about to be read on the host."""
+    with torch.cuda.device(ws.device):
+        _cabi.check(_cabi.lib().rag_features_status(_ptr(ws), _stream()))
+
+
 class Preprocess(object):
     """a class to convert from AlphaGo GameState objects to tensors of one-hot
     features for NN inputs (preprocessing.py:266-294)"""
@@ -159,7 +166,10 @@ class Preprocess(object):
         if len(states) == 0:
             return np.zeros((0, self.output_dim, 0, 0), np.uint8)
         batch = states if isinstance(states, BatchedGameState) else BatchedGameState.from_states(states)
-        return self.to_device(batch, LAYOUT_NCHW_U8).cpu().numpy()
+        ws = self.analyze(batch)
+        out = self.emit(ws, len(batch), batch.size, layout=LAYOUT_NCHW_U8)
+        check_workspace(ws)
+        return out.cpu().numpy()
 
     def state_to_tensor(self, state):
         """Convert a GameState to a Theano-compatible tensor: (1, F, S, S) float64 of 0/1

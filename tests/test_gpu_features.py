@@ -7,7 +7,7 @@ import pytest
 import torch
 
 from oracle import go_oracle
-from rocalphago_b200 import BatchedGameState, Preprocess, PositionView
+from rocalphago_b200 import BatchedGameState, Preprocess, PositionView, _cabi
 from rocalphago_b200 import preprocessing as P
 from tests import golden_util as gu
 
@@ -252,3 +252,44 @@ def test_copied_states_without_ages_and_forget_ages():
         orig.do_move(np.where(mv >= 0, mv, -1))
         orig.packed = torch.where(torch.as_tensor(mv >= 0, device=orig.device)[:, None], orig.packed, keep)
     assert np.array_equal(Preprocess(feats).to_device(orig).cpu().numpy(), want)
+
+
+def test_ladder_kernel_stress_all_replies_handed_over_with_one_helper():
+    """Liveness of the reply hand-over under its worst settings -- every search hands its replies over from
+    the first move (rag_set_ladder_handover(0)) and a single CTA keeps a helper warp -- on 100,000
+    positions: the kernel finishes, the watchdog does not fire, and the planes equal those of the default
+    settings (hand-over never changes results)."""
+    L = _cabi.lib()
+    n = 100000
+    batch = BatchedGameState.random_playouts(n, seed=7007)
+    pp = Preprocess(["ladder_capture", "ladder_escape"])
+    want = pp.to_device(batch).clone()
+    P.check_workspace(pp._ws.get(n, batch.device))
+    old_h, old_c = L.rag_set_ladder_handover(0), L.rag_set_ladder_helpers(1)
+    try:
+        got = pp.to_device(batch)
+        P.check_workspace(pp._ws.get(n, batch.device))
+    finally:
+        L.rag_set_ladder_handover(old_h if old_h < (1 << 29) else -1)
+        L.rag_set_ladder_helpers(old_c)
+    assert int(want.sum()) > 1000
+    assert torch.equal(got, want)
+
+
+def test_ladder_watchdog_reports_instead_of_killing_the_context():
+    """With an absurdly short watchdog, warps that wait for handed-over replies give up: the kernel still
+    ends, rag_features_status (raised by the Python layer where it synchronises) says so, and the next
+    call with the normal watchdog is clean and exact again."""
+    L = _cabi.lib()
+    b, a, ko, pl = go_oracle.random_playouts(3000, size=19, seed=808, max_ply=380, stride=3)
+    batch = BatchedGameState.from_arrays(b, a, ko, pl)
+    pp = Preprocess(["ladder_capture", "ladder_escape"])
+    old_w, old_h = L.rag_set_ladder_watchdog(1), L.rag_set_ladder_handover(0)
+    try:
+        with pytest.raises(_cabi.RagError, match="watchdog"):
+            pp.states_to_tensor(batch)
+    finally:
+        L.rag_set_ladder_watchdog(old_w)
+        L.rag_set_ladder_handover(old_h if old_h < (1 << 29) else -1)
+    got = pp.states_to_tensor(batch)                         # the context is alive, the flag was per call
+    assert np.array_equal(got, go_oracle.features(b, a, ko, pl, ["ladder_capture", "ladder_escape"]))

@@ -14,6 +14,7 @@ import numpy as np
 import pytest
 import torch
 
+from oracle import go_oracle
 from rocalphago_b200 import BatchedGameState, Preprocess, _cabi
 from rocalphago_b200.state import _ptr, _stream
 
@@ -49,6 +50,27 @@ def test_static_scratch_matches_workspace_entry_point_twice():
     small = BatchedGameState.random_playouts(40, size=9, seed=5, max_ply=90, stride=3)
     got, want = _both(small, Preprocess(["ladder_escape", "legal", "liberties"]).plane_src)
     assert np.array_equal(got, want)
+
+
+def test_static_scratch_against_the_oracle_and_without_touching_the_allocator():
+    """The same entry point checked on its own: planes equal to the CPU oracle's on oracle-made positions,
+    and the device's free memory the same before and after the calls (nothing is allocated or freed)."""
+    L = _cabi.lib()
+    b, a, ko, pl = go_oracle.random_playouts(200, size=19, seed=606, max_ply=380, stride=7)
+    want = go_oracle.features(b, a, ko, pl, go_oracle.DEFAULT_FEATURES)
+    batch = BatchedGameState.from_arrays(b, a, ko, pl)
+    pp = Preprocess()
+    src = pp.plane_src.ctypes.data_as(ctypes.c_void_p)
+    got = torch.zeros((200, 48, 19, 19), dtype=torch.uint8, device="cuda")
+    _cabi.check(L.rag_features_static(_ptr(batch.packed), 200, 19, src, 48, 0, 0, 64, _ptr(got), _stream()))   # set-up call
+    torch.cuda.synchronize()
+    free_before = torch.cuda.mem_get_info()[0]
+    for _ in range(3):
+        got.fill_(5)
+        _cabi.check(L.rag_features_static(_ptr(batch.packed), 200, 19, src, 48, 0, 0, 64, _ptr(got), _stream()))
+        torch.cuda.synchronize()
+        assert np.array_equal(got.cpu().numpy(), want)
+    assert torch.cuda.mem_get_info()[0] == free_before
 
 
 def test_static_scratch_refuses_oversized_batches():
