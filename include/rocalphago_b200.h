@@ -126,6 +126,13 @@ int rag_set_ladder_helpers(int ctas);
  * one thread); the liveness argument is in DESIGN.md. */
 long long rag_set_ladder_watchdog(long long cycles);
 int rag_features_status(const void* d_workspace, void* stream);
+/* The reference's ladder recursion (go.py:329-463) is bounded in depth (80) but not in size; on a rare
+ * position (one in ~4 million random-playout positions so far) it does not return in any practical time.
+ * The device search gives up -- the move is then "not a ladder" -- once one line of it has tried 65,536
+ * moves (the longest search of the parity sets tries a few thousand).  Returns, after waiting for
+ * `stream`, how many of the (position, move) searches of the ladder kernel that last wrote this workspace
+ * were cut off that way (>= 0), or a negative RAG_E* code. */
+int rag_features_ladder_cutoffs(const void* d_workspace, void* stream);
 
 /* Positional superko (go.py:242-265, 282-283) for states created with enforce_superko=True: what
  * is_positional_superko reads, per position, in device memory.  q = x*32 + y.

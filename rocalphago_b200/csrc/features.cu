@@ -42,11 +42,12 @@ constexpr int kMaxPositionsPerLaunch = 1 << 21;        // queue item = pos<<11 |
 struct StealTask {
     uint32_t H[32], P[32], G[32];    // hunter stones, prey-side stones, prey group: the position the reply is played in
     int ko, move, is_capture, remaining;
-    int pad[28];
+    int nodes;                       // moves the posting line of the search had tried (counts against its budget)
+    int pad[27];
 };
 static_assert(sizeof(StealTask) == 512, "StealTask layout");
-enum { kTaskFree = 0, kTaskPosted = 1, kTaskTaken = 2, kTaskDone0 = 3, kTaskDone1 = 4, kTaskCancelled = 5 };
-enum { kCtlQueued = 0, kCtlTaken = 1, kCtlPosted = 2, kCtlBusy = 4, kCtlAllocCursor = 5, kCtlTimeout = 6 };
+enum { kTaskFree = 0, kTaskPosted = 1, kTaskTaken = 2, kTaskDone0 = 3, kTaskDone1 = 4, kTaskCancelled = 5, kTaskBudget = 6 };
+enum { kCtlQueued = 0, kCtlTaken = 1, kCtlPosted = 2, kCtlBusy = 4, kCtlAllocCursor = 5, kCtlTimeout = 6, kCtlCutoffs = 7 };
 
 struct Workspace {
     unsigned* counters;      // kCtl* slots
@@ -197,6 +198,13 @@ analyze_kernel(const uint32_t* __restrict__ states, int n, int S, int with_ladde
 
 constexpr int kStealAfterDefault = 96;   // moves tried before a search starts handing over replies
 constexpr int kMaxPosted = 3;            // replies handed over per node
+// The reference's recursion (go.py:329-463) is bounded in depth (80) but not in size: on a rare position
+// (one in ~4 million random-playout positions met so far) the tree of replies is astronomically large and
+// the reference itself does not return in any practical time.  Here a search gives up -- "not a ladder" --
+// once one line of it (counted through hand-overs) has tried this many moves; the longest search of the
+// golden and oracle sets tries a few thousand.  rag_features_ladder_cutoffs counts the searches cut off.
+constexpr int kLadderNodeBudget = 1 << 16;
+constexpr int kLadderBudget = 3;         // return value of a search that ran out of budget
 
 __device__ __forceinline__ int ld_vol(const int* p) { return *(const volatile int*)p; }
 __device__ __forceinline__ unsigned ld_vol(const unsigned* p) { return *(const volatile unsigned*)p; }
@@ -211,7 +219,7 @@ struct StealFrames {                     // which tasks each stack frame has out
 #define LANE0_INT(expr) __shfl_sync(kFullMask, (g.lane == 0) ? (int)(expr) : 0, 0)
 
 __device__ __forceinline__ int steal_post(const Workspace& ws, const Geo& g, BB H, BB P, BB G, int ko, int move,
-                                          bool is_capture, int remaining) {
+                                          bool is_capture, int remaining, int nodes) {
     int slot = -1;
     if (g.lane == 0) {
         for (int probe = 0; probe < 8 && slot < 0; probe++) {
@@ -223,7 +231,7 @@ __device__ __forceinline__ int steal_post(const Workspace& ws, const Geo& g, BB 
     if (slot < 0) return -1;
     StealTask* t = ws.tasks + slot;
     t->H[g.lane] = H.w; t->P[g.lane] = P.w; t->G[g.lane] = G.w;
-    if (g.lane == 0) { t->ko = ko; t->move = move; t->is_capture = is_capture ? 1 : 0; t->remaining = remaining; }
+    if (g.lane == 0) { t->ko = ko; t->move = move; t->is_capture = is_capture ? 1 : 0; t->remaining = remaining; t->nodes = nodes; }
     __threadfence();
     __syncwarp();
     if (g.lane == 0) {
@@ -283,7 +291,7 @@ __device__ __noinline__ int ladder_dfs_steal(const Workspace& ws, const Geo& g, 
                 const int m = bb_first(rest);
                 if (m < 0) break;
                 const int slot = steal_post(ws, g, st.hunter[d], st.prey[d], st.group[d], st.ko[d], m, !node_is_capture,
-                                            remaining_children - d);
+                                            remaining_children - d, nodes);
                 if (slot < 0) break;
                 rest = andnot(rest, bb_single(m, g));
                 st.pending[d] = andnot(st.pending[d], bb_single(m, g));
@@ -293,6 +301,7 @@ __device__ __noinline__ int ladder_dfs_steal(const Workspace& ws, const Geo& g, 
         const int m = bb_first(st.pending[d]);
         if (m >= 0) {
             if ((nodes & 15) == 15 && cancelled()) { v = kLadderAborted; }
+            else if (nodes >= kLadderNodeBudget) { v = kLadderBudget; }
             else {
                 nodes++;
                 st.pending[d] = andnot(st.pending[d], bb_single(m, g));
@@ -322,7 +331,7 @@ __device__ __noinline__ int ladder_dfs_steal(const Workspace& ws, const Geo& g, 
             int stt;
             for (;;) {                                                // somebody is on it: wait for the value
                 stt = LANE0_INT(ld_vol(tstat));
-                if (stt == kTaskDone0 || stt == kTaskDone1) break;
+                if (stt == kTaskDone0 || stt == kTaskDone1 || stt == kTaskBudget) break;
                 if (cancelled()) { stt = -1; break; }
                 __nanosleep(200);
                 // never hang the device: past the deadline the wait is given up, the search unwinds as
@@ -338,7 +347,7 @@ __device__ __noinline__ int ladder_dfs_steal(const Workspace& ws, const Geo& g, 
                 if (g.lane == 0) atomicExch(tstat, kTaskFree);
                 sf.count[d]--;
                 if (stt == kTaskDone0) continue;
-                v = 0;                                                // that reply has value 1
+                v = stt == kTaskBudget ? kLadderBudget : 0;           // 0: that reply has value 1
             }
         } else v = 1;                                                 // every reply failed
 
@@ -348,7 +357,7 @@ __device__ __noinline__ int ladder_dfs_steal(const Workspace& ws, const Geo& g, 
             sf.count[d] = 0;
             if (d == 0) return v;
             d--;
-            if (v == kLadderAborted) continue;
+            if (v == kLadderAborted || v == kLadderBudget) continue;
             if (v == 0) break;                                        // parent keeps looking
             v = 0;                                                    // a child of value 1 refutes the parent
         }
@@ -409,6 +418,7 @@ ladder_kernel(const uint32_t* __restrict__ states, int S, int steal_after, int h
         if (g.lane == 0) {
             if (r == kLadderValue1)
                 atomicOr(ws.planes + (size_t)pos * kPlaneWords + (kPlaneLadderCapture + kind) * 32 + (q >> 5), 1u << (q & 31));
+            if (r == kLadderBudget) atomicAdd(&ws.counters[kCtlCutoffs], 1u);
             __threadfence();
             atomicSub(&ws.counters[kCtlBusy], 1u);
         }
@@ -463,11 +473,12 @@ ladder_kernel(const uint32_t* __restrict__ states, int S, int steal_after, int h
         const BB H{__ldcg(&t->H[g.lane])}, P{__ldcg(&t->P[g.lane])}, G{__ldcg(&t->G[g.lane])};
         const int ko = LANE0_INT(ld_vol(&t->ko)), move = LANE0_INT(ld_vol(&t->move));
         const int is_capture = LANE0_INT(ld_vol(&t->is_capture)), remaining = LANE0_INT(ld_vol(&t->remaining));
-        const int r = ladder_search_steal(ws, g, H, P, G, ko, move, is_capture != 0, remaining, 0, steal_after, st, sf, tstat, t_deadline);
+        const int nodes0 = LANE0_INT(ld_vol(&t->nodes));
+        const int r = ladder_search_steal(ws, g, H, P, G, ko, move, is_capture != 0, remaining, nodes0, steal_after, st, sf, tstat, t_deadline);
         if (g.lane == 0) {
             __threadfence();
             if (r == kLadderAborted) atomicExch(tstat, kTaskFree);
-            else if (atomicCAS(tstat, kTaskTaken, r == kLadderValue1 ? kTaskDone1 : kTaskDone0) != kTaskTaken)
+            else if (atomicCAS(tstat, kTaskTaken, r == kLadderBudget ? kTaskBudget : r == kLadderValue1 ? kTaskDone1 : kTaskDone0) != kTaskTaken)
                 atomicExch(tstat, kTaskFree);                         // cancelled while it ran: nobody waits for it
             atomicSub(&ws.counters[kCtlBusy], 1u);
         }
@@ -1235,6 +1246,15 @@ int rag_features_status(const void* d_workspace, void* stream)
     if (flag) return fail(RAG_ECUDA, "the ladder reader gave up waiting for handed-over work (watchdog of %lld cycles): the ladder planes of this "
                                      "workspace are incomplete; run the batch again", g_ladder_watchdog);
     return RAG_OK;
+}
+
+int rag_features_ladder_cutoffs(const void* d_workspace, void* stream)
+{
+    if (!d_workspace) return fail(RAG_EINVAL, "null argument");
+    unsigned count = 0;
+    RAG_CUDA_CHECK(cudaMemcpyAsync(&count, (const char*)d_workspace + kCtlCutoffs * sizeof(unsigned), sizeof count, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    RAG_CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream));
+    return (int)(count > 0x7fffffffu ? 0x7fffffffu : count);
 }
 
 int rag_set_ladder_handover(int moves) { int old = g_steal_after; g_steal_after = moves < 0 ? 1 << 30 : moves; return old; }

@@ -293,3 +293,30 @@ def test_ladder_watchdog_reports_instead_of_killing_the_context():
         L.rag_set_ladder_handover(old_h if old_h < (1 << 29) else -1)
     got = pp.states_to_tensor(batch)                         # the context is alive, the flag was per call
     assert np.array_equal(got, go_oracle.features(b, a, ko, pl, ["ladder_capture", "ladder_escape"]))
+
+
+def test_a_ladder_search_the_reference_cannot_finish_is_cut_off():
+    """Device-generated batch 21805311 (found by the 4-GPU feature sweep) holds a position whose ladder
+    recursion is astronomically large: the reference's unbounded recursion (go.py:329-463) and the C
+    oracle do not return on it.  The device search gives up after 65,536 tried moves along one line,
+    says so (rag_features_ladder_cutoffs), and the batch still finishes in well under a second."""
+    import time
+    L = _cabi.lib()
+    n = 32768
+    batch = BatchedGameState.random_playouts(n, seed=21805311)
+    pp = Preprocess(["ladder_capture", "ladder_escape"])
+    torch.cuda.synchronize()
+    t0 = time.time()
+    planes = pp.to_device(batch)
+    torch.cuda.synchronize()
+    took = time.time() - t0
+    ws = pp._ws.get(n, batch.device)
+    P.check_workspace(ws)                                     # the watchdog did not fire
+    cut = L.rag_features_ladder_cutoffs(ws.data_ptr(), None)
+    assert 1 <= cut <= 8, cut
+    assert took < 5.0, took
+    assert int(planes.sum()) > 1000
+    # an ordinary batch cuts nothing off
+    other = BatchedGameState.random_playouts(4096, seed=5)
+    pp.to_device(other)
+    assert L.rag_features_ladder_cutoffs(pp._ws.get(4096, other.device).data_ptr(), None) == 0
