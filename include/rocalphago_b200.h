@@ -302,10 +302,9 @@ size_t rag_net_workspace_bytes(const rag_net* net, int n);
 long long rag_net_input_rows(const rag_net* net, int n);
 int rag_net_input_channels(const rag_net* net);
 
-/* Tuning/test knob (process-wide): 0 = one CTA per tile (default); 1 = convolutions run on CTA
- * pairs (tcgen05 cta_group::2: half the weight tile per CTA, one M=256 UMMA per pair).  Results
- * are identical.  Only use 1 when no other kernel shares the GPU with the forward (see conv.cu).
- * Returns the previous setting. */
+/* Tuning/test knob (process-wide): 1 = convolutions run on CTA pairs (tcgen05 cta_group::2: half the
+ * weight tile per CTA, one M=256 UMMA per pair; the default, also RAG_CONV_PAIR=0/1 in the environment);
+ * 0 = one CTA per tile.  Results are identical.  Returns the previous setting. */
 int rag_set_conv_pair(int enable);
 
 /* Measurement aid: with profiling on, every forward records a CUDA event on its stream before

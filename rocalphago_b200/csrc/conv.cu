@@ -683,12 +683,16 @@ static size_t conv_smem_bytes(int N, int stages) {
     return 1024 + (size_t)stages * (kATileBytes + (size_t)N * 128) + 4 * kOutBoxBytes + (2 * stages + 4) * 8 + 16 + 2 * (size_t)N * 4;
 }
 
-// rag_set_conv_pair: run layers on CTA pairs (cta_group::2) where they allow it.  Off by default:
-// live, under the 1 kW power cap, the pair kernel is no faster than the single-CTA one (same
-// 0.88-0.91 ms per 3x3 layer at batch 4096), and a cluster launch sharing the GPU with the
-// persistent ladder kernel of the next batch (pipeline.py) stopped making progress in a few long
-// runs on B200 / driver 580 -- never when run on its own stream alone.
-static int g_conv_pair = 0;
+// rag_set_conv_pair: layers whose filter count allows it run on CTA pairs (cta_group::2): each CTA
+// loads its own 128 rows of activations and HALF of the weight tile, one M=256 UMMA per pair reads both
+// halves -- 30 % less operand traffic into shared memory per flop.  Under the 1 kW cap that is
+// 5 % of the step (fp16c32: 14.85 -> 14.09 ms per 4,096 positions; fp16: 350 -> 368 k positions/s).
+// On by default since round 2 (RAG_CONV_PAIR=0 in the environment or rag_set_conv_pair(0) turns it
+// off): round 1 kept it off because a few long pipelined runs had stopped making progress; this round
+// 1,000-4,000-step pipelined runs at batch 64 / 256 / 1,024 / 4,096, with and without a value network,
+// all completed, and the one reproducible "no progress" event found was an unbounded ladder search
+// (features.cu, kLadderNodeBudget), not the cluster launch.
+static int g_conv_pair = getenv("RAG_CONV_PAIR") ? atoi(getenv("RAG_CONV_PAIR")) != 0 : 1;
 
 static int pick_stages(int N) {
     for (int st = 6; st >= 2; st--)

@@ -456,12 +456,17 @@ def test_two_stream_pipeline_gives_the_same_results():
         pipe.submit(batches[0].packed[:10])
 
 
-def test_cta_pair_convolution_kernel_matches_single_cta_kernel():
-    """rag_set_conv_pair(1) switches the layers to the cta_group::2 kernel; outputs are bit-identical."""
+@pytest.mark.parametrize("dtype,arch,n", [("fp16", dict(layers=3, filters_per_layer=192), 700),
+                                          ("fp16c32", dict(layers=4, filters_per_layer=192), 700),
+                                          ("fp16c64", dict(layers=3, filters_per_layer=152), 130),
+                                          ("fp16x3", dict(layers=3, filters_per_layer=64), 33),
+                                          ("bf16", dict(layers=2, filters_per_layer=256, filter_width_2=5), 1)])
+def test_cta_pair_convolution_kernel_matches_single_cta_kernel(dtype, arch, n):
+    """rag_set_conv_pair(1) (the default) runs the layers on the cta_group::2 kernel, (0) on one CTA per
+    tile; outputs are bit-identical in every precision mode, also when the last pair of tiles is ragged."""
     from rocalphago_b200 import _cabi
     L = _cabi.lib()
-    n = 700                                                     # several 256-row tiles per CTA pair
-    net = CNNPolicy(go_oracle.DEFAULT_FEATURES, layers=3, filters_per_layer=192, dtype="fp16", seed=41)
+    net = CNNPolicy(go_oracle.DEFAULT_FEATURES, dtype=dtype, seed=41, **arch)
     batch = BatchedGameState.random_playouts(n, seed=77)
     old = L.rag_set_conv_pair(0)
     try:
