@@ -41,6 +41,18 @@ ISSUED = {"fp16": 1.0, "bf16": 1.0, "fp16c32": 4.0 / 3.0, "fp16c64": 5.0 / 3.0, 
 FEATURE_BYTES = 17_568                         # per position, packed state in + 48x361 u8 out
 
 
+def ncu_traffic(key, n, algorithmic_bytes):
+    """roofline.traffic: dram__bytes_read.sum + dram__bytes_write.sum per launch of the kernel, from the
+    `ncu --set full` capture tools/ncu_extract.py summarised into profiles/ncu_traffic.json, scaled to n."""
+    path = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    try:
+        e = json.load(open(path))[key]
+    except (OSError, KeyError, ValueError):
+        return None
+    return {"bytes": int(e["bytes"] * n / e["positions_per_launch"]), "algorithmic_bytes": int(algorithmic_bytes),
+            "source": e["source"] + " via profiles/ncu_traffic.json"}
+
+
 def load_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -446,9 +458,7 @@ def run_gpu(args):
                          "ms_per_launch": k3,
                          # dram__bytes_read.sum + dram__bytes_write.sum per launch from the ncu --set full capture
                          # of this kernel at batch 4096 (profiles/r1_final_ncu_summary.md); scales with the batch
-                         "traffic": None if args.dtype not in ("fp16", "bf16") else
-                                    {"bytes": int(1.0892e9 * n / 4096), "algorithmic_bytes": int(n * 361 * 192 * 2 * 2),
-                                     "source": "profiles/r1_final_ncu_summary.md"},
+                         "traffic": ncu_traffic("conv_umma/" + args.dtype, n, n * 361 * 2 * 2 * {"fp16c32": 256, "fp16c64": 256, "fp16x3": 384}.get(args.dtype, 192)),
                          "issued_over_algorithmic": ISSUED[args.dtype],
                          "issued_tflops": achieved * ISSUED[args.dtype],
                          "note": "CUDA events recorded by the library on the launching stream, sampled %d time(s) inside "
@@ -630,7 +640,7 @@ def run_features(args):
                     "note": "bound by the device-to-host copy of the planes (17,328 B per position over the host link)"},
             "gpu_launches": 3 * K, "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": "emit_u8_flat_kernel", "achieved": achieved, "peak": peaks["hbm"], "unit": "GB/s",
-                         "frac": achieved / peaks["hbm"], "ms_per_launch": emit, "traffic": None,
+                         "frac": achieved / peaks["hbm"], "ms_per_launch": emit, "traffic": ncu_traffic("emit_u8_flat/u8", n, FEATURE_BYTES * n),
                          "write_only": {"fill_gbs": n * 17328 / (fill / 1e3) / 1e9, "fill_ms": fill, "emit_over_fill": fill / emit,
                                         "note": "the kernel only writes (planes in: 0.2 of the bytes out); a plain fill of the same "
                                                 "buffer is what this part's HBM takes for write-only traffic -- `peak` is a COPY rate "

@@ -34,12 +34,15 @@ def lib():
     if _lib is not None:
         return _lib
     path = _build.LIB_PATH
-    if not os.path.exists(path):
+    if _build._stale():                 # missing, or built from other sources than the tree holds now (content hash)
         try:
             _build.build_library()
         except Exception as e:  # noqa: BLE001
-            raise RagError("librocalphago_b200.so is not built and nvcc could not build it (%s); "
-                           "run `python -c 'import __graft_entry__ as g; g.build()'`" % e)
+            if not os.path.exists(path):
+                raise RagError("librocalphago_b200.so is not built and nvcc could not build it (%s); "
+                               "run `python -c 'import __graft_entry__ as g; g.build()'`" % e)
+            import warnings
+            warnings.warn("librocalphago_b200.so is older than csrc/ and could not be rebuilt (%s); using it as it is" % e)
     L = ctypes.CDLL(path)
     c = ctypes
     vp, i32, i64, u64, sz = c.c_void_p, c.c_int, c.c_longlong, c.c_uint64, c.c_size_t

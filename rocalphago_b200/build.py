@@ -17,12 +17,28 @@ def _nvcc():
     return shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
 
 
+STAMP_PATH = os.path.join(LIB_DIR, "sources.sha1")
+
+
+def _source_digest():
+    """Content hash of everything the library is built from (modification times do not survive a copy
+    of the tree to another machine; contents do)."""
+    import hashlib
+    h = hashlib.sha1(" ".join(NVCC_FLAGS).encode())
+    for rel in SOURCES + HEADERS:
+        path = os.path.join(CSRC, rel)
+        if os.path.exists(path):
+            with open(path, "rb") as f:
+                h.update(rel.encode() + b"\0" + f.read())
+    return h.hexdigest()
+
+
 def _stale():
-    if not os.path.exists(LIB_PATH):
+    """True if the shared library is missing or was built from other sources than the ones in the tree."""
+    if not os.path.exists(LIB_PATH) or not os.path.exists(STAMP_PATH):
         return True
-    t = os.path.getmtime(LIB_PATH)
-    files = [os.path.join(CSRC, s) for s in SOURCES + HEADERS]
-    return any(os.path.exists(f) and os.path.getmtime(f) > t for f in files)
+    with open(STAMP_PATH) as f:
+        return f.read().strip() != _source_digest()
 
 
 def build_library(force=False, verbose=False):
@@ -43,6 +59,8 @@ def build_library(force=False, verbose=False):
         objs.append(obj)
     subprocess.check_call([_nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", LIB_PATH]
                           + objs + ["-lcuda", "-lpthread"])
+    with open(STAMP_PATH, "w") as f:
+        f.write(_source_digest() + "\n")
     return LIB_PATH
 
 

@@ -34,7 +34,7 @@ char* last_error_buffer() {
 }
 
 constexpr int kWarpsPerBlock = 4;
-constexpr int kPlaneWords = kNumPlanes * 32;           // 1568 words = 6272 B per position
+constexpr int kPlaneWords = kNumPlanes * 32;           // 1600 words = 6400 B per position
 constexpr int kCounterBytes = 256;
 constexpr int kMaxPositionsPerLaunch = 1 << 21;        // queue item = pos<<11 | kind<<10 | q
 

@@ -38,7 +38,12 @@ class IllegalMove(Exception):            # go.py:584
 
 
 def _flat(pt, size):
-    return -1 if pt is None else pt[0] * size + pt[1]
+    """Flat point x*S+y; a coordinate off the board (an SGF letter past the board size) becomes S*S,
+    which no kernel accepts: the move is reported illegal, as GameState.is_legal does (go.py:267-270)."""
+    if pt is None:
+        return -1
+    x, y = pt
+    return x * size + y if 0 <= x < size and 0 <= y < size else size * size
 
 
 def replay_games(games, size, device=None):
@@ -47,8 +52,9 @@ def replay_games(games, size, device=None):
     Returns (packed, game_index, ply, moves, illegal_at): `packed` (m, 192) int32 on the device
     holds the position before every main-line move that was reached (m = sum of usable plies),
     `game_index`/`ply` say where each row comes from, `moves` the flat move played there (-1 =
-    pass), and `illegal_at[g]` is the ply at which game g hit an illegal move (its later plies are
-    dropped, game_converter.py:117-119) or -1."""
+    pass), and `illegal_at[g]` is the ply at which game g hit an illegal move (that ply's pair is kept, as
+    the reference's generator yields it before do_move raises; later plies are dropped,
+    game_converter.py:117-119) or -1."""
     dev = torch.device(device or "cuda")
     G = len(games)
     if G == 0:
@@ -102,7 +108,9 @@ def replay_games(games, size, device=None):
     if (bad < T0).any():
         i = int(np.argmax(bad < T0))
         raise IllegalMove("set-up stone of game %d cannot be placed" % i)
-    usable = np.minimum(n_moves, bad - T0)
+    # sgf_iter_states (util.py:124-126) yields (state, move) BEFORE do_move raises, so the reference stores the
+    # pair whose move is illegal and drops only what follows
+    usable = np.minimum(n_moves, bad - T0 + 1)
     game_index = np.repeat(np.arange(G), usable)
     ply = np.concatenate([np.arange(u) for u in usable]) if G else np.zeros(0, np.int64)
     rows = torch.as_tensor(ply * G + game_index, device=dev)
@@ -145,7 +153,7 @@ class GameConverter(object):
         keep = np.flatnonzero(moves >= 0)
         planes = self._planes(packed[torch.as_tensor(keep, device=packed.device)], bd_size)
         for k, i in enumerate(keep):
-            yield planes[k:k + 1], (int(moves[i]) // bd_size, int(moves[i]) % bd_size)
+            yield planes[k:k + 1], tuple(game.moves[i][1])       # the point as the file gives it (also when it is off the board)
         if illegal_at[0] >= 0:
             raise IllegalMove("move %d of %s" % (illegal_at[0], file_name))
 
@@ -168,13 +176,16 @@ class GameConverter(object):
                         return
                     names, games = zip(*pending)
                     del pending[:]
-                    packed, gi, _, moves, illegal_at = replay_games(list(games), bd_size)
+                    packed, gi, ply, moves, illegal_at = replay_games(list(games), bd_size)
                     keep = moves >= 0
                     rows = torch.as_tensor(np.flatnonzero(keep), device=packed.device)
                     planes = self._planes(packed[rows], bd_size)
                     raw.write(planes.tobytes())
                     mk, gk = moves[keep], gi[keep]
-                    actions.append(np.stack([mk // bd_size, mk % bd_size], axis=1).astype(np.uint8))
+                    act = np.stack([mk // bd_size, mk % bd_size], axis=1)
+                    for k in np.flatnonzero(mk >= bd_size * bd_size):          # an off-board point: stored as the file gives it
+                        act[k] = games[gk[k]].moves[ply[keep][k]][1]
+                    actions.append(act.astype(np.uint8))
                     counts = np.bincount(gk, minlength=len(games))
                     for g, name in enumerate(names):
                         if illegal_at[g] >= 0:

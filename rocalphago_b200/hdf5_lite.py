@@ -538,10 +538,12 @@ class Writer(WGroup):
                 if isinstance(c, WGroup):
                     scan(c)
         scan(self)
-        leaf_k = max(4, (biggest[0] + 1) // 2)
-        if leaf_k > 32767:
-            raise Hdf5Error("too many objects in one group (%d)" % biggest[0])
+        # one symbol-table node holds 2 * leaf_k entries (leaf_k is a 16-bit field of the superblock); a group
+        # with more children gets several nodes under its B-tree node, which has room for 2 * internal_k of them
+        leaf_k = min(32767, max(4, (biggest[0] + 1) // 2))
         internal_k = 16
+        if biggest[0] > 2 * leaf_k * 2 * internal_k:
+            raise Hdf5Error("too many objects in one group (%d; at most %d)" % (biggest[0], 2 * leaf_k * 2 * internal_k))
         fh.write(b"\0" * 96)                                  # superblock, filled in at the end
 
         def alloc(data):
@@ -606,16 +608,20 @@ class Writer(WGroup):
             heap_data += struct.pack("<QQ", 1, 16)             # one free block; 1 = end of the free list
             data_addr = alloc(bytes(heap_data))
             heap_addr = alloc(b"HEAP" + struct.pack("<B3xQQQ", 0, len(heap_data), free, data_addr))
-            snod = b"SNOD" + struct.pack("<BBH", 1, 0, len(entries))
-            for (nm, addr), off in zip(entries, offsets):
-                snod += struct.pack("<QQII16x", off, addr, 0, 0)
-            snod += b"\0" * (8 + 2 * leaf_k * 40 - len(snod))
             node_size = 24 + (2 * internal_k + 1) * 8 + 2 * internal_k * 8
-            if entries:
-                snod_addr = alloc(snod)
-                tree = b"TREE" + struct.pack("<BBHQQ", 0, 0, 1, UNDEF, UNDEF) + struct.pack("<QQQ", 0, snod_addr, offsets[-1])
-            else:
-                tree = b"TREE" + struct.pack("<BBHQQ", 0, 0, 0, UNDEF, UNDEF) + struct.pack("<Q", 0)
+            per = 2 * leaf_k
+            tree_body = struct.pack("<Q", 0)                   # key 0: the empty name, below every child
+            n_nodes = 0
+            for i in range(0, len(entries), per):
+                chunk, offs = entries[i:i + per], offsets[i:i + per]
+                snod = [b"SNOD" + struct.pack("<BBH", 1, 0, len(chunk))]
+                for (nm, addr), off in zip(chunk, offs):
+                    snod.append(struct.pack("<QQII16x", off, addr, 0, 0))
+                snod = b"".join(snod)
+                snod_addr = alloc(snod + b"\0" * (8 + per * 40 - len(snod)))
+                tree_body += struct.pack("<QQ", snod_addr, offs[-1])       # child, then the key of its largest name
+                n_nodes += 1
+            tree = b"TREE" + struct.pack("<BBHQQ", 0, 0, n_nodes, UNDEF, UNDEF) + tree_body
             tree_addr = alloc(tree + b"\0" * (node_size - len(tree)))
             hdr = alloc(header([(0x11, struct.pack("<QQ", tree_addr, heap_addr))] + attribute_messages(g)))
             return hdr, tree_addr, heap_addr

@@ -217,3 +217,30 @@ class BatchedMCTS(object):
                 self._root = child
                 return
         self._root = TreeNode(None, 0)
+
+
+def _network_of(fn, what):
+    """The CNNPolicy / CNNValue behind a reference-style callable (the object itself, or its bound
+    eval_state / __call__)."""
+    net = getattr(fn, "__self__", fn)
+    if not hasattr(net, "model") or not hasattr(net, "preprocessor"):
+        raise TypeError("%s must be a network of this package (or its eval_state method): the device search cannot "
+                        "call back into arbitrary Python functions" % what)
+    return net
+
+
+class MCTS(BatchedMCTS):
+    """AlphaGo/mcts.py:109-217 under its own name and constructor:
+        MCTS(value_fn, policy_fn, rollout_policy_fn, lmbda=0.5, c_puct=5, rollout_limit=500, playout_depth=20, n_playout=10000)
+    `value_fn` / `policy_fn` are this package's CNNValue / CNNPolicy (or their bound `eval_state`);
+    `rollout_policy_fn` is accepted for the signature and not called -- rollouts (lmbda > 0) are uniformly
+    random sensible-move playouts on the device.  Playouts run one at a time, as in the reference
+    (`batch=1`: the same visit counts, playout for playout); pass batch=64 or more for throughput."""
+
+    def __init__(self, value_fn, policy_fn, rollout_policy_fn=None, lmbda=0.5, c_puct=5, rollout_limit=500,
+                 playout_depth=20, n_playout=10000, batch=1, **kw):
+        value = None if value_fn is None else _network_of(value_fn, "value_fn")
+        BatchedMCTS.__init__(self, _network_of(policy_fn, "policy_fn"), value, lmbda=lmbda, c_puct=c_puct,
+                             rollout_limit=rollout_limit, playout_depth=playout_depth, n_playout=n_playout,
+                             batch=batch, **kw)
+        self._rollout_policy_fn = rollout_policy_fn

@@ -173,11 +173,101 @@ class Network(object):
         self.set_weights(arrays)
 
     # -- (de)serialisation in Keras-1 Sequential JSON -------------------------------------------
+    def _functional_json(self):
+        """Keras 1.2.0 `Model.to_json()` of ResnetPolicy.create_network's graph (policy.py:196-271): an
+        InputLayer, then layers with `inbound_nodes`, Merge(mode='sum') closing every residual unit."""
+        layers, counter = [], {}
+
+        def add(cls, cfg, inbound):
+            counter[cls] = counter.get(cls, 0) + 1
+            name = "%s_%d" % ({"InputLayer": "input", "Convolution2D": "convolution2d", "BatchNormalization": "batchnormalization",
+                               "Activation": "activation", "Merge": "merge", "Flatten": "flatten", "Bias": "bias"}[cls], counter[cls])
+            cfg = dict(cfg, name=name)
+            layers.append({"class_name": cls, "config": cfg, "name": name,
+                           "inbound_nodes": [[[src, 0, 0] for src in inbound]] if inbound else []})
+            return name
+
+        def conv(nb, k, inbound):
+            return add("Convolution2D", {"nb_filter": nb, "nb_row": k, "nb_col": k, "init": "uniform", "activation": "linear",
+                                         "border_mode": "same", "dim_ordering": "th", "subsample": [1, 1], "bias": True,
+                                         "trainable": True}, [inbound])
+        inp = add("InputLayer", {"batch_input_shape": [None, self.input_dim, self.board, self.board], "input_dtype": "float32",
+                                 "sparse": False}, [])
+        path = conv(self.specs[0][0], self.specs[0][1], inp)
+        block_input = path
+        for i in range(1, len(self.specs)):
+            path = add("BatchNormalization", {"epsilon": 0.001, "mode": 0, "axis": -1, "momentum": 0.99, "trainable": True}, [path])
+            path = add("Activation", {"activation": "relu", "trainable": True}, [path])
+            path = conv(self.specs[i][0], self.specs[i][1], path)
+            if self.unit_end[i]:
+                counter["Merge"] = counter.get("Merge", 0) + 1
+                name = "merge_%d" % counter["Merge"]
+                layers.append({"class_name": "Merge", "name": name, "inbound_nodes": [[[block_input, 0, 0], [path, 0, 0]]],
+                               "config": {"name": name, "mode": "sum", "concat_axis": -1, "dot_axes": -1, "mode_type": "raw",
+                                          "output_shape": None, "output_shape_type": "raw", "output_mask": None,
+                                          "output_mask_type": "raw", "arguments": {}}})
+                path = block_input = name
+        path = add("Activation", {"activation": "relu", "trainable": True}, [path])
+        path = add("Convolution2D", {"nb_filter": 1, "nb_row": 1, "nb_col": 1, "init": "uniform", "activation": "linear",
+                                     "border_mode": "same", "dim_ordering": "th", "subsample": [1, 1], "bias": True,
+                                     "trainable": True}, [path])
+        path = add("Flatten", {"trainable": True}, [path])
+        path = add("Bias", {"trainable": True}, [path])
+        path = add("Activation", {"activation": "softmax", "trainable": True}, [path])
+        return {"class_name": "Model", "keras_version": "1.2.0",
+                "config": {"name": "model_1", "layers": layers, "input_layers": [[inp, 0, 0]], "output_layers": [[path, 0, 0]]},
+                "rocalphago_b200": {"dtype": self.dtype, "kernel_flip": self.kernel_flip}}
+
+    @staticmethod
+    def _from_functional(km):
+        """Parses the functional-model JSON Keras 1.x writes for a reference-built ResnetPolicy
+        (policy.py:271 `Model(input=..., output=...)`, saved by nn_util.py:96-101): layers come in
+        topological order; a Merge(mode='sum') after a convolution marks the end of a residual unit."""
+        cfg = km["config"]
+        by_name = {l["name"]: l for l in cfg["layers"]}
+        convs, unit_end, board, input_dim, saw_softmax = [], [], None, None, False
+        pending_bn = False
+        for layer in cfg["layers"]:
+            cls, c = layer["class_name"], layer["config"]
+            if cls == "InputLayer":
+                _, input_dim, board, _ = c["batch_input_shape"]
+            elif cls == "Convolution2D":
+                if c.get("border_mode", "same") != "same" or tuple(c.get("subsample", (1, 1))) != (1, 1) or c["nb_row"] != c["nb_col"]:
+                    raise ValueError("only square stride-1 'same' convolutions are supported")
+                if c.get("activation", "linear") != "linear":
+                    raise ValueError("convolutions of a residual network are linear (policy.py:207,239)")
+                if convs and not (c["nb_filter"] == 1 and c["nb_row"] == 1) and not pending_bn:
+                    raise ValueError("expected BatchNormalization -> ReLU in front of %s" % layer["name"])
+                convs.append((c["nb_filter"], c["nb_row"]))
+                unit_end.append(1 if len(convs) == 1 else 0)
+                pending_bn = False
+            elif cls == "BatchNormalization":
+                if c.get("mode", 0) != 0 or c.get("axis", -1) not in (-1, 3):
+                    raise ValueError("BatchNormalization(mode=%r, axis=%r) is not what ResnetPolicy builds" % (c.get("mode"), c.get("axis")))
+                pending_bn = True
+            elif cls == "Merge":
+                srcs = [s[0] for s in layer["inbound_nodes"][0]]
+                if c.get("mode") != "sum" or len(srcs) != 2 or not all(s in by_name for s in srcs):
+                    raise ValueError("only Merge(mode='sum') of a unit's input and its path is supported")
+                unit_end[-1] = 1
+            elif cls == "Activation":
+                if c.get("activation") == "softmax":
+                    saw_softmax = True
+                elif c.get("activation") != "relu":
+                    raise ValueError("activation %r is not supported on this path" % c.get("activation"))
+            elif cls in ("Flatten", "Bias"):
+                pass
+            else:
+                raise ValueError("layer %s is not supported on this path" % cls)
+        if len(convs) < 2 or convs[-1] != (1, 1) or not saw_softmax:
+            raise ValueError("expected the graph to end in a 1x1 convolution, Flatten, Bias and softmax")
+        ext = km.get("rocalphago_b200", {})
+        return Network(board, input_dim, convs[:-1], head="policy", dtype=ext.get("dtype", "fp16"),
+                       kernel_flip=ext.get("kernel_flip", True), unit_end=unit_end[:-1])
+
     def to_json(self):
         if self.unit_end is not None:
-            return json.dumps({"class_name": "Model", "keras_version": "1.2.0", "rocalphago_b200": {
-                "arch": "resnet", "board": self.board, "input_dim": self.input_dim, "specs": self.specs,
-                "unit_end": self.unit_end, "dtype": self.dtype, "kernel_flip": self.kernel_flip}})
+            return json.dumps(self._functional_json())
         layers = []
         for i, (nb, k) in enumerate(self.specs):
             cfg = {"name": "convolution2d_%d" % (i + 1), "nb_filter": nb, "nb_row": k, "nb_col": k,
@@ -212,8 +302,10 @@ class Network(object):
             return Network(ext["board"], ext["input_dim"], [tuple(x) for x in ext["specs"]], head="policy",
                            dtype=ext.get("dtype", "fp16"), kernel_flip=ext.get("kernel_flip", True),
                            unit_end=ext["unit_end"])
+        if km.get("class_name") == "Model":
+            return Network._from_functional(km)
         if km.get("class_name") != "Sequential":
-            raise ValueError("only Sequential models are supported on this path (got %s)" % km.get("class_name"))
+            raise ValueError("only Sequential and functional (Model) JSON is supported on this path (got %s)" % km.get("class_name"))
         convs, head, dense, board, input_dim = [], None, [], None, None
         for layer in km["config"]:
             name, cfg = layer["class_name"], layer["config"]

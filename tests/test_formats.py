@@ -188,3 +188,47 @@ def test_load_model_reads_the_references_minimodel(tmp_path):
     again = NeuralNetBase.load_model(js)
     assert all(np.array_equal(a, b) for a, b in zip(ws, again.model.get_weights()))
     assert json.load(open(js))["class"] == "CNNPolicy"
+
+
+def test_writer_handles_groups_with_more_children_than_one_symbol_table_node(tmp_path):
+    """sgfs_to_hdf5 makes one `file_offsets` entry per game; a KGS-sized corpus has more games than the
+    65,534 entries one symbol-table node can hold.  The writer then spreads the group over several nodes
+    under its B-tree node; the reader (which also reads h5py's files) finds every entry."""
+    w = hdf5_lite.Writer()
+    g = w.create_group("file_offsets")
+    n = 70000
+    for i in range(n):
+        g["game_%06d.sgf" % i] = np.array([i, i % 7], np.int64)
+    w["features"] = np.bytes_("board,ones")
+    path = str(tmp_path / "many.h5")
+    w.save(path)
+    f = hdf5_lite.File(path)
+    assert len(f["file_offsets"]) == n
+    for i in (0, 1, 65533, 65534, 65535, n - 1):
+        assert f["file_offsets"]["game_%06d.sgf" % i][...].tolist() == [i, i % 7]
+    assert sorted(f["file_offsets"])[:2] == ["game_000000.sgf", "game_000001.sgf"]
+
+
+def test_functional_model_json_of_a_resnet_policy_round_trips():
+    """A reference-built ResnetPolicy is a Keras functional `Model` (policy.py:271); nn_util.py:96-101 saves
+    `model.to_json()`: InputLayer, layers with inbound_nodes, Merge(mode='sum') closing each residual unit.
+    Network.from_json reads that form (and to_json writes it), including uneven n_skip_K."""
+    import json
+    from rocalphago_b200.models.nn_util import Network
+    from rocalphago_b200.models.policy import ResnetPolicy
+    net = ResnetPolicy.create_network(input_dim=12, board=9, layers=7, filters_per_layer=16, n_skip_1=2, n_skip_3=1,
+                                      n_skip_4=3, seed=1)
+    text = net.to_json()
+    km = json.loads(text)
+    assert km["class_name"] == "Model" and km["config"]["input_layers"] == [["input_1", 0, 0]]
+    classes = [l["class_name"] for l in km["config"]["layers"]]
+    assert classes.count("Merge") == sum(net.unit_end) - 1 and classes.count("BatchNormalization") == len(net.specs) - 1
+    merge = [l for l in km["config"]["layers"] if l["class_name"] == "Merge"][0]
+    assert [s[0] for s in merge["inbound_nodes"][0]] == ["convolution2d_1", "convolution2d_3"] and merge["config"]["mode"] == "sum"
+    back = Network.from_json(text)
+    assert back.specs == net.specs and back.unit_end == net.unit_end and (back.board, back.input_dim) == (9, 12)
+    assert [w.shape for w in back.get_weights()] == [w.shape for w in net.get_weights()]
+    # a graph this path does not run is refused with a reason
+    km["config"]["layers"][2]["config"]["axis"] = 1
+    with pytest.raises(ValueError, match="BatchNormalization"):
+        Network.from_json(json.dumps(km))

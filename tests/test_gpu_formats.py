@@ -121,8 +121,8 @@ def test_convert_game_semantics(tmp_path):
     with pytest.raises(IllegalMove):
         for pair in conv.convert_game(str(bad), 9):
             got.append(pair[1])
-    assert got == [(0, 0), (1, 1)]
-    # the file-level converter keeps the pairs before the illegal move, warns, and skips broken files
+    assert got == [(0, 0), (1, 1), (1, 1)]       # the pair at the illegal ply is yielded before do_move raises (util.py:124-126)
+    # the file-level converter keeps the pairs up to the illegal move, warns, and skips broken files
     broken = tmp_path / "broken.sgf"
     broken.write_text("(;SZ[9];B[aa")
     small = tmp_path / "small.sgf"
@@ -134,9 +134,17 @@ def test_convert_game_semantics(tmp_path):
     text = " | ".join(str(w.message) for w in caught)
     assert "Illegal Move encountered" in text and "Could not parse" in text and "wrong board size" in text
     f = hdf5_lite.File(out)
-    assert f["states"].shape == (5, 4, 9, 9) and f["actions"][...].tolist() == [[0, 0], [1, 1], [2, 2], [0, 0], [1, 1]]
+    assert f["states"].shape == (6, 4, 9, 9) and f["actions"][...].tolist() == [[0, 0], [1, 1], [2, 2], [0, 0], [1, 1], [1, 1]]
     assert f["file_offsets"][str(ok).replace("/", ":")][...].tolist() == [0, 3]
-    assert f["file_offsets"][str(bad).replace("/", ":")][...].tolist() == [3, 2]
+    assert f["file_offsets"][str(bad).replace("/", ":")][...].tolist() == [3, 3]
+    # a coordinate past the board ("fz" on 9x9 would alias another point if flattened blindly) is an illegal move
+    off = tmp_path / "off.sgf"
+    off.write_text("(;SZ[9];B[aa];W[az];B[cc])")
+    got = []
+    with pytest.raises(IllegalMove):
+        for pair in conv.convert_game(str(off), 9):
+            got.append(pair[1])
+    assert got[0] == (0, 0) and len(got) == 2
     assert len(f["file_offsets"]) == 2
 
 

@@ -76,3 +76,50 @@ def test_device_self_play_replays_on_the_oracle():
         assert np.array_equal(rb[0], gb[gme]) and rko[0] == gko[gme] and rpl[0] == gpl[gme]
         assert np.array_equal(np.minimum(ra[0], 7), ga[gme])
     assert (gb != 0).sum() > 64 * 80
+
+
+def test_reference_named_players_and_search():
+    """ai.py's class names and constructor arguments: GreedyPolicyPlayer / ProbabilisticPolicyPlayer /
+    MCTSPlayer, and mcts.MCTS(value_fn, policy_fn, rollout_policy_fn, ...) taking bound eval_state methods."""
+    from rocalphago_b200 import PositionView
+    from rocalphago_b200.ai import GreedyPolicyPlayer, MCTSPlayer, PASS_MOVE, ProbabilisticPolicyPlayer
+    from rocalphago_b200.mcts import MCTS
+    from rocalphago_b200.models import CNNValue
+    net, batch, probs, sensible = _setup(n=40)
+    b, a, ko, pl = batch.to_arrays()
+
+    class State(PositionView):                                   # a GameState look-alike with a move history
+        def __init__(self, i, plies):
+            PositionView.__init__(self, b[i], a[i], int(ko[i]), int(pl[i]))
+            self.history = [(0, 0)] * plies
+
+    states = [State(i, plies=10 * i) for i in range(40)]
+    greedy = GreedyPolicyPlayer(net, move_limit=300)
+    for i in (0, 7, 31, 39):
+        mv = greedy.get_move(states[i])
+        if 10 * i > 300 or len(sensible[i]) == 0:
+            assert mv is PASS_MOVE
+        else:
+            s = sensible[i]
+            assert mv == (int(s[np.argmax(probs[i][s])]) // 19, int(s[np.argmax(probs[i][s])]) % 19)
+    prob = ProbabilisticPolicyPlayer(net, temperature=0.7, move_limit=350, greedy_start=200, seed=3)
+    moves = prob.get_moves(states)
+    assert len(moves) == 40
+    for i, mv in enumerate(moves):
+        s = sensible[i]
+        if 10 * i > 350 or len(s) == 0:
+            assert mv is PASS_MOVE
+        elif 10 * i >= 200:
+            assert mv == (int(s[np.argmax(probs[i][s])]) // 19, int(s[np.argmax(probs[i][s])]) % 19)
+        else:
+            assert mv[0] * 19 + mv[1] in set(s.tolist())
+    assert prob.get_move(states[25]) == moves[25]                # greedy past greedy_start
+    assert abs(prob.apply_temperature(np.array([0.2, 0.3, 0.5])).sum() - 1.0) < 1e-12
+    value = CNNValue(go_oracle.DEFAULT_FEATURES + ["color"], layers=2, filters_per_layer=32, dense_units=16, seed=4)
+    search = MCTS(value.eval_state, net.eval_state, net.eval_state, lmbda=0.0, c_puct=5, playout_depth=4, n_playout=12)
+    mv = search.get_move(states[3])
+    assert mv is None or mv[0] * 19 + mv[1] in set(go_oracle.legal_moves(b[3:4], ko[3:4], pl[3:4])[0][0].tolist())
+    player = MCTSPlayer(value.eval_state, net.eval_state, net.eval_state, lmbda=0.0, playout_depth=3, n_playout=8)
+    assert player.get_move(states[5]) is not None
+    with pytest.raises(TypeError):
+        MCTS(lambda st: 0.0, net.eval_state, None)
