@@ -65,6 +65,7 @@ struct ConvParams {
     // chunks against extra weight columns so that those channels contribute hi.W_hi + lo.W_hi + hi.W_lo
     // (layouts in rag_net_create / rag_net_load_weights)
     unsigned long long a_map;     // 4 bits per K chunk: which 64-channel chunk of the A row it reads
+    unsigned long long k_map;     // 4 bits per K chunk: how many K=16 steps of it hold real channels (1..4)
     int out_pitch;                // mode 0: channels per output row
     int lo_cols;                  // mode 0: leading channels whose lo half is written at column N + c
     int dup_hi;                   // mode 0: also copy hi of channels 0..31 to columns N + 32 .. N + 63
@@ -123,6 +124,13 @@ __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.comm
 __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+// one lane of a converged warp (elect.sync): unlike `lane == 0`, the compiler knows exactly one thread is
+// inside the branch and issues the TMA / MMA instructions straight from uniform registers
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_commit(uint32_t bar) {
@@ -256,9 +264,12 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int kblocks = p.width * p.width * p.kchunks;
 
     if (warp == 0) {
-        // ===== TMA producer =====
-        if (lane == 0) {
-            uint32_t it = 0;
+        // ===== TMA producer: the whole warp walks the ring, one elected lane issues =====
+        {
+            // (ring position and phase are carried along, never divided out: this lane's and the MMA lane's
+            // instruction count per stage is on the kernel's critical path)
+            uint32_t it = 0, ph = 0;
+            int s = 0;
             const int pad = p.width / 2, S2 = p.S * p.S;
             for (int tile = worker; tile < p.tiles; tile += n_workers) {
                 // first output point of my 128 rows -> base point of the im2col walk (shifted by -pad)
@@ -269,13 +280,13 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     for (int j = 0; j < p.width; j++) {
                         const int t = i * p.width + j;
                         for (int c = 0; c < p.kchunks; c++, it++) {
-                            const int s = (int)(it % (uint32_t)p.stages);
-                            const uint32_t ph = (it / (uint32_t)p.stages) & 1u;
                             mbar_wait(empty_bar(s), ph ^ 1u);
                             const uint32_t sa = base + (uint32_t)s * stage_bytes;
                             const int ca = (int)((p.a_map >> (4 * c)) & 15ull);
                             // tensor dims are (C, y, x, board): y is the fast spatial index
-                            if (kPair) {
+                            if (!elect_one()) {
+                                // nothing to issue on this lane
+                            } else if (kPair) {
                                 // both CTAs' bytes are counted on the leader's barrier
                                 if (rank == 0) mbar_expect_tx(full_bar(s), 2u * stage_bytes);
                                 const uint32_t lb = full_bar(s) & kPeerBitMask;
@@ -293,36 +304,53 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                                 tma_load_im2col(sa, &tmA, ca * kChunkK, y0 - pad, x0 - pad, b0, (uint16_t)j, (uint16_t)i, full_bar(s));
                                 tma_load_2d(sa + kATileBytes, &tmB, c * kChunkK, t * p.N, full_bar(s));
                             }
+                            __syncwarp();
+                            if (++s == p.stages) { s = 0; ph ^= 1u; }
                         }
                     }
                 }
             }
         }
     } else if (warp == 1) {
-        // ===== MMA issuer (the leader CTA's, for a pair) =====
-        if (lane == 0 && rank == 0) {
+        // ===== MMA issuer (the leader CTA's, for a pair): the warp walks, one elected lane issues =====
+        if (rank == 0) {
             const uint32_t idesc = umma_idesc(p.dtype, p.N, rows_per_tile);
-            uint32_t it = 0, lt = 0;
+            uint32_t lt = 0, ph = 0;
+            int s = 0;
+            const uint64_t desc0 = umma_desc_sw128(base), desc_stage = (uint64_t)(stage_bytes >> 4), desc_b = (uint64_t)(kATileBytes >> 4);
             for (int tile = worker; tile < p.tiles; tile += n_workers, lt++) {
                 const uint32_t a = lt & 1u, aph = (lt >> 1) & 1u;
                 mbar_wait(tempty_bar((int)a), aph ^ 1u);
                 tc_fence_after();
                 const uint32_t tmem_d = tmem_base + a * (uint32_t)p.N;
-                for (int kb = 0; kb < kblocks; kb++, it++) {
-                    const int s = (int)(it % (uint32_t)p.stages);
-                    const uint32_t ph = (it / (uint32_t)p.stages) & 1u;
+                uint32_t accumulate = 0u;                         // the tile's first MMA overwrites the accumulator
+                unsigned long long km = p.k_map;
+                int c = 0;
+                for (int kb = 0; kb < kblocks; kb++) {
                     mbar_wait(full_bar(s), ph);
                     tc_fence_after();
-                    const uint32_t sa = base + (uint32_t)s * stage_bytes;
-                    const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + kATileBytes);
-                    #pragma unroll
-                    for (int k = 0; k < kChunkK / 16; k++) {      // +32 bytes along K inside the swizzled row
-                        if (kPair) tc_mma_f16_pair(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((kb | k) != 0));
-                        else tc_mma_f16(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((kb | k) != 0));
+                    // the stage's descriptors: the start-address field advances by stage_bytes / 16 per stage
+                    // (the ring stays far below the 14-bit field's 256 KiB reach)
+                    const uint64_t da = desc0 + (uint64_t)s * desc_stage, db = da + desc_b;
+                    const int ksteps = (int)(km & 15ull);         // K=16 steps of this chunk that hold real channels
+                    if (elect_one()) {
+                        #pragma unroll
+                        for (int k = 0; k < kChunkK / 16; k++) {  // +32 bytes along K inside the swizzled row
+                            if (k < ksteps) {
+                                if (kPair) tc_mma_f16_pair(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, k == 0 ? accumulate : 1u);
+                                else tc_mma_f16(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, k == 0 ? accumulate : 1u);
+                            }
+                        }
+                        if (kPair) tc_commit_pair(empty_bar(s)); else tc_commit(empty_bar(s));   // frees the stage (in both CTAs)
                     }
-                    if (kPair) tc_commit_pair(empty_bar(s)); else tc_commit(empty_bar(s));   // frees the stage (in both CTAs)
+                    __syncwarp();
+                    accumulate = 1u;
+                    if (++s == p.stages) { s = 0; ph ^= 1u; }
+                    km >>= 4;
+                    if (++c == p.kchunks) { c = 0; km = p.k_map; }
                 }
-                if (kPair) tc_commit_pair(tfull_bar((int)a)); else tc_commit(tfull_bar((int)a));   // accumulator complete
+                if (elect_one()) { if (kPair) tc_commit_pair(tfull_bar((int)a)); else tc_commit(tfull_bar((int)a)); }   // accumulator complete
+                __syncwarp();
             }
         }
     } else {
@@ -638,6 +666,7 @@ struct Layer {
     int cin_store = 0;            // channels of this layer's input rows
     int kdim = 0;                 // K extent of the weights per tap
     unsigned long long a_map = 0; // K chunk -> chunk of the input row, 4 bits each
+    unsigned long long k_map = 0; // K chunk -> K=16 steps that hold real channels, 4 bits each
     std::vector<int> out_order;   // position j of this layer's output holds filter out_order[j] (energetic first)
     CUtensorMap tmB, tmB_pair;    // weight tiles, encoded by rag_net_load_weights
     struct ACache { const void* ptr; int n; CUtensorMap map; };
@@ -786,7 +815,7 @@ static int run_layers(rag_net* net, const uint16_t* d_in, int n, float* d_out, c
         p.tiles = (int)((p.rows + kTileM - 1) / kTileM);
         p.width = ly.width; p.kchunks = ly.kdim / kChunkK; p.N = ly.n_pad;
         p.stages = pick_stages(ly.n_pad); p.dtype = net->op_dtype;
-        p.a_map = ly.a_map;
+        p.a_map = ly.a_map; p.k_map = ly.k_map;
         static const int dbg = getenv("RAG_CONV_DEBUG") ? atoi(getenv("RAG_CONV_DEBUG")) : 0;
         static const int dbg_stages = getenv("RAG_CONV_STAGES") ? atoi(getenv("RAG_CONV_STAGES")) : 0;
         p.debug = dbg;
@@ -915,6 +944,19 @@ int rag_net_create(const rag_net_desc* desc, rag_net** out)
             map |= (unsigned long long)nc << (4 * nc);            // [lo 0..63] or [lo 0..31 | hi 0..31]; then chunk 0 again
         }
         ly.a_map = map;
+        // K=16 steps per chunk: a chunk of plain channels holds min(64, cin - 64 c) real ones; the
+        // corrected-channel chunks hold lo_in (and, for FP16C32, the copied hi channels after them)
+        auto steps = [](int channels) { return (unsigned long long)((channels < 1 ? 1 : channels > 64 ? 64 : channels) + 15) / 16; };
+        unsigned long long km = 0;
+        const int total_chunks = ly.kdim / kChunkK;
+        for (int c = 0; c < total_chunks; c++) {
+            int real;
+            if (net->split || ly.lo_in == 0 || c < nc) real = cin - 64 * (c % nc);
+            else if (ly.lo_in == 64) real = cin < 64 ? cin : 64;
+            else real = 64;                                            // [lo 0..31 | hi 0..31]: the hi half sits at 32..63
+            km |= steps(real) << (4 * c);
+        }
+        ly.k_map = km;
         if (ly.kdim / kChunkK > 16 || ly.cin_store / kChunkK > 16) { delete net; return fail(RAG_EUNSUPPORTED, "layer %d has too many input channels for this precision mode", l + 1); }
         if (pick_stages(ly.n_pad) < 2) { delete net; return fail(RAG_EUNSUPPORTED, "layer %d does not fit shared memory", l + 1); }
         if (ly.n_pad > net->max_c) net->max_c = ly.n_pad;
