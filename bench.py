@@ -775,7 +775,8 @@ def main():
                     help="policy: the flagship (features + 13x192 policy forward); features: BASELINE config 4; "
                          "policy+value: BASELINE config 5 (adds the 49-plane 13x192 value forward to every step)")
     ap.add_argument("--serial", action="store_true", help="also time the single-stream rag_eval_batch step")
-    ap.add_argument("--conv-pair", type=int, default=1, help="1: convolutions on CTA pairs (cta_group::2, the default); 0: one CTA per tile")
+    ap.add_argument("--conv-pair", type=int, default=0, help="0: one CTA per tile (default); 1: convolutions on CTA pairs (cta_group::2; faster, but "
+                                                               "sporadically stalls beside the pipeline's ladder kernels -- see csrc/conv.cu)")
     ap.add_argument("--no-pipeline", action="store_true", help="debug: skip the pipelined passes")
     ap.add_argument("--e2e-graphs", type=int, default=1, help="1: the end-to-end pass replays each pipeline stage as a CUDA graph")
     ap.add_argument("--slots", type=int, default=None, help="batches in flight in the pipeline (default: 2, or 4 below 2048 positions)")

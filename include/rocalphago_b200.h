@@ -302,10 +302,17 @@ size_t rag_net_workspace_bytes(const rag_net* net, int n);
 long long rag_net_input_rows(const rag_net* net, int n);
 int rag_net_input_channels(const rag_net* net);
 
-/* Tuning/test knob (process-wide): 1 = convolutions run on CTA pairs (tcgen05 cta_group::2: half the
- * weight tile per CTA, one M=256 UMMA per pair; the default, also RAG_CONV_PAIR=0/1 in the environment);
- * 0 = one CTA per tile.  Results are identical.  Returns the previous setting. */
+/* Tuning/test knob (process-wide): 0 = one CTA per tile (default); 1 = convolutions run on CTA pairs
+ * (tcgen05 cta_group::2: half the weight tile per CTA, one M=256 UMMA per pair; also RAG_CONV_PAIR=1 in the
+ * environment).  Results are identical and the pair kernel is ~13 % faster, but beside the pipeline's persistent
+ * ladder kernels its cluster launch sporadically never finishes on B200 / driver 580 (csrc/conv.cu): use 1
+ * only when nothing else shares the GPU with the forward.  Returns the previous setting. */
 int rag_set_conv_pair(int enable);
+/* No wait inside the convolution kernel is unbounded: a barrier that has not moved for ~4 s (a layer takes
+ * 1 ms) makes the kernel record where it stood in host-mapped memory and trap, so that a stall surfaces as
+ * a CUDA error instead of a hang.  After such an error this writes the record as text into buf and returns
+ * 1; 0 if there is none.  Needs no working CUDA context. */
+int rag_conv_stall_report(char* buf, int size);
 
 /* Measurement aid: with profiling on, every forward records a CUDA event on its stream before
  * each convolution launch and after the last; rag_net_layer_times then gives the device time

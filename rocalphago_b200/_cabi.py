@@ -79,6 +79,7 @@ def lib():
         "rag_net_workspace_bytes": (sz, [vp, i32]),
         "rag_net_logits_offset": (sz, [vp, i32]),
         "rag_set_conv_pair": (i32, [i32]),
+        "rag_conv_stall_report": (i32, [c.c_char_p, i32]),
         "rag_net_set_profiling": (i32, [vp, i32]),
         "rag_net_layer_times": (i32, [vp, vp, i32]),
         "rag_net_input_rows": (i64, [vp, i32]),

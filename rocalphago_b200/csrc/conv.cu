@@ -85,16 +85,41 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+// Where a wait that never ended was standing: written to host-mapped memory just before the kernel traps
+// (rag_conv_stall_report reads it after the context is gone).  A correct run never touches it.
+struct StallRecord { unsigned magic, code, block, thread, tile, stage, parity, pad; };
+__device__ StallRecord* g_stall_record = nullptr;
+constexpr long long kStallCycles = 6000000000ll;      // ~4 s at 1.5 GHz: a 3x3 layer takes 1 ms
+
+__device__ __noinline__ void stall_trap(uint32_t code, uint32_t a, uint32_t b, uint32_t c) {
+    StallRecord* r = g_stall_record;
+    if (r && atomicCAS(&r->magic, 0u, 0x57A11u) == 0u) {
+        r->code = code; r->block = blockIdx.x; r->thread = threadIdx.x; r->tile = a; r->stage = b; r->parity = c;
+        __threadfence_system();
+    }
+    __trap();
+}
+
+__device__ __forceinline__ bool mbar_try(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
     asm volatile(
         "{\n\t"
         ".reg .pred p;\n\t"
-        "WAIT_%=:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-        "@p bra DONE_%=;\n\t"
-        "bra WAIT_%=;\n\t"
-        "DONE_%=:\n\t"
-        "}" ::"r"(bar), "r"(parity) : "memory");
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}" : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    return ok != 0;
+}
+// `code` says which wait this is (1 producer/empty, 2 MMA/accumulator free, 3 MMA/stage full, 4 epilogue/accumulator full)
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, uint32_t code = 0, uint32_t a = 0, uint32_t b = 0) {
+    if (mbar_try(bar, parity)) return;
+    const long long t0 = clock64();
+    for (;;) {
+        #pragma unroll 1
+        for (int i = 0; i < 1024; i++)
+            if (mbar_try(bar, parity)) return;
+        if (clock64() - t0 > kStallCycles) stall_trap(code, a, b, parity);
+    }
 }
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar) {
     asm volatile(
@@ -280,7 +305,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     for (int j = 0; j < p.width; j++) {
                         const int t = i * p.width + j;
                         for (int c = 0; c < p.kchunks; c++, it++) {
-                            mbar_wait(empty_bar(s), ph ^ 1u);
+                            mbar_wait(empty_bar(s), ph ^ 1u, 1u, (uint32_t)tile, (uint32_t)s);
                             const uint32_t sa = base + (uint32_t)s * stage_bytes;
                             const int ca = (int)((p.a_map >> (4 * c)) & 15ull);
                             // tensor dims are (C, y, x, board): y is the fast spatial index
@@ -320,14 +345,14 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const uint64_t desc0 = umma_desc_sw128(base), desc_stage = (uint64_t)(stage_bytes >> 4), desc_b = (uint64_t)(kATileBytes >> 4);
             for (int tile = worker; tile < p.tiles; tile += n_workers, lt++) {
                 const uint32_t a = lt & 1u, aph = (lt >> 1) & 1u;
-                mbar_wait(tempty_bar((int)a), aph ^ 1u);
+                mbar_wait(tempty_bar((int)a), aph ^ 1u, 2u, (uint32_t)tile, a);
                 tc_fence_after();
                 const uint32_t tmem_d = tmem_base + a * (uint32_t)p.N;
                 uint32_t accumulate = 0u;                         // the tile's first MMA overwrites the accumulator
                 unsigned long long km = p.k_map;
                 int c = 0;
                 for (int kb = 0; kb < kblocks; kb++) {
-                    mbar_wait(full_bar(s), ph);
+                    mbar_wait(full_bar(s), ph, 3u, (uint32_t)tile, (uint32_t)s);
                     tc_fence_after();
                     // the stage's descriptors: the start-address field advances by stage_bytes / 16 per stage
                     // (the ring stays far below the 14-bit field's 256 KiB reach)
@@ -374,7 +399,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             // my row of the tile = one point of one board; rows past the last board are not written
             const long long row = (long long)tile * rows_per_tile + (long long)rank * kTileM + quarter * 32 + lane;
             const bool real = row < p.rows && !(p.debug & 8);
-            mbar_wait(tfull_bar((int)a), aph);
+            mbar_wait(tfull_bar((int)a), aph, 4u, (uint32_t)tile, a);
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + a * (uint32_t)p.N;
             if (p.mode == 0) {
@@ -712,16 +737,17 @@ static size_t conv_smem_bytes(int N, int stages) {
     return 1024 + (size_t)stages * (kATileBytes + (size_t)N * 128) + 4 * kOutBoxBytes + (2 * stages + 4) * 8 + 16 + 2 * (size_t)N * 4;
 }
 
-// rag_set_conv_pair: layers whose filter count allows it run on CTA pairs (cta_group::2): each CTA
+// rag_set_conv_pair: layers whose filter count allows it can run on CTA pairs (cta_group::2): each CTA
 // loads its own 128 rows of activations and HALF of the weight tile, one M=256 UMMA per pair reads both
-// halves -- 30 % less operand traffic into shared memory per flop.  Under the 1 kW cap that is
-// 5 % of the step (fp16c32: 14.85 -> 14.09 ms per 4,096 positions; fp16: 350 -> 368 k positions/s).
-// On by default since round 2 (RAG_CONV_PAIR=0 in the environment or rag_set_conv_pair(0) turns it
-// off): round 1 kept it off because a few long pipelined runs had stopped making progress; this round
-// 1,000-4,000-step pipelined runs at batch 64 / 256 / 1,024 / 4,096, with and without a value network,
-// all completed, and the one reproducible "no progress" event found was an unbounded ladder search
-// (features.cu, kLadderNodeBudget), not the cluster launch.
-static int g_conv_pair = getenv("RAG_CONV_PAIR") ? atoi(getenv("RAG_CONV_PAIR")) != 0 : 1;
+// halves -- 30 % less operand traffic into shared memory per flop, 0.735 instead of 0.843 ms per fp16
+// 3x3 layer.  OFF by default (RAG_CONV_PAIR=1 in the environment or rag_set_conv_pair(1) turns it on):
+// beside the persistent ladder kernels of the pipeline the cluster launch sporadically never finishes
+// on B200 / driver 580 -- about one process in eleven in this round's soak (tools/pair_soak.py: ten runs
+// of 1,200 pipelined steps completed, the next two hung), after 1,000-4,000-step runs at every batch
+// size had all completed.  The stall is not in any mbarrier wait of this kernel (those now record where
+// they stand and trap after ~4 s, rag_conv_stall_report; nothing was recorded), which leaves the
+// co-scheduling of the CTA pair itself or tcgen05.alloc.  Alone on the GPU the pair kernel never stalled.
+static int g_conv_pair = getenv("RAG_CONV_PAIR") ? atoi(getenv("RAG_CONV_PAIR")) != 0 : 0;
 
 static int pick_stages(int N) {
     for (int st = 6; st >= 2; st--)
@@ -791,16 +817,35 @@ static int output_map(rag_net* net, Layer& ly, const void* ptr, int n, int pitch
     return RAG_OK;
 }
 
+static StallRecord* g_stall_host = nullptr;
+
+static int stall_record_ready() {
+    static bool done = false;
+    if (done) return RAG_OK;
+    StallRecord* dev_view = nullptr;
+    RAG_CUDA_CHECK(cudaHostAlloc((void**)&g_stall_host, sizeof(StallRecord), cudaHostAllocMapped | cudaHostAllocPortable));
+    memset(g_stall_host, 0, sizeof(StallRecord));
+    RAG_CUDA_CHECK(cudaHostGetDevicePointer((void**)&dev_view, g_stall_host, 0));
+    RAG_CUDA_CHECK(cudaMemcpyToSymbol(g_stall_record, &dev_view, sizeof dev_view));
+    done = true;
+    return RAG_OK;
+}
+
 static int conv_smem_limit(bool pair, size_t smem) {
     static size_t set[2] = {0, 0};      // largest dynamic shared memory size already granted to each kernel
     if (smem <= set[pair]) return RAG_OK;
-    if (pair) RAG_CUDA_CHECK(cudaFuncSetAttribute(conv_umma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (pair) {
+        RAG_CUDA_CHECK(cudaFuncSetAttribute(conv_umma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        if (getenv("RAG_CONV_CARVEOUT"))      // experiment only: an explicit shared-memory / L1 preference on the cluster kernel
+            RAG_CUDA_CHECK(cudaFuncSetAttribute(conv_umma_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(getenv("RAG_CONV_CARVEOUT"))));
+    }
     else RAG_CUDA_CHECK(cudaFuncSetAttribute(conv_umma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     set[pair] = smem;
     return RAG_OK;
 }
 
 static int run_layers(rag_net* net, const uint16_t* d_in, int n, float* d_out, const NetBuffers& b, cudaStream_t s) {
+    if (int rc = stall_record_ready()) return rc;
     const int S = net->desc.board, L = (int)net->layers.size();
     int lin_cur = 0;
     const uint16_t* cur = d_in;
@@ -1122,6 +1167,19 @@ int rag_net_set_input_planes(rag_net* net, const int32_t* h_plane_src, int F)
         net->in_density[f] = kPlaneDensity[h_plane_src[f]];
     }
     return RAG_OK;
+}
+
+int rag_conv_stall_report(char* buf, int size)
+{
+    if (!buf || size < 1) return fail(RAG_EINVAL, "null argument");
+    buf[0] = 0;
+    if (!g_stall_host || g_stall_host->magic != 0x57A11u) return 0;
+    static const char* what[] = {"?", "TMA producer waiting for a free stage", "MMA lane waiting for a drained accumulator",
+                                 "MMA lane waiting for a loaded stage", "epilogue waiting for a finished accumulator"};
+    const StallRecord& r = *g_stall_host;
+    snprintf(buf, (size_t)size, "convolution kernel gave up after %lld cycles: %s (block %u, thread %u, tile %u, slot %u, parity %u)",
+             kStallCycles, what[r.code < 5 ? r.code : 0], r.block, r.thread, r.tile, r.stage, r.parity);
+    return 1;
 }
 
 int rag_set_conv_pair(int enable) { int old = g_conv_pair; g_conv_pair = enable != 0; return old; }
