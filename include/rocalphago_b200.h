@@ -133,6 +133,9 @@ int rag_features_status(const void* d_workspace, void* stream);
  * `stream`, how many of the (position, move) searches of the ladder kernel that last wrote this workspace
  * were cut off that way (>= 0), or a negative RAG_E* code. */
 int rag_features_ladder_cutoffs(const void* d_workspace, void* stream);
+/* Measurement aid: the largest number of moves any one line of a ladder search had tried in the ladder kernel
+ * that last wrote this workspace (what the budget above is compared with). */
+int rag_features_ladder_longest(const void* d_workspace, void* stream);
 
 /* Positional superko (go.py:242-265, 282-283) for states created with enforce_superko=True: what
  * is_positional_superko reads, per position, in device memory.  q = x*32 + y.

@@ -58,6 +58,7 @@ def lib():
         "rag_set_ladder_watchdog": (i64, [i64]),
         "rag_features_status": (i32, [vp, vp]),
         "rag_features_ladder_cutoffs": (i32, [vp, vp]),
+        "rag_features_ladder_longest": (i32, [vp, vp]),
         "rag_features_ladders": (i32, [vp, i32, i32, vp, sz, vp]),
         "rag_rollout_winners": (i32, [vp, i32, i32, i32, c.c_uint64, c.c_float, vp, vp]),
         "rag_features_analyze_superko": (i32, [vp, i32, i32, i32, vp, vp, sz, vp]),

@@ -42,12 +42,12 @@ constexpr int kMaxPositionsPerLaunch = 1 << 21;        // queue item = pos<<11 |
 struct StealTask {
     uint32_t H[32], P[32], G[32];    // hunter stones, prey-side stones, prey group: the position the reply is played in
     int ko, move, is_capture, remaining;
-    int nodes;                       // moves the posting line of the search had tried (counts against its budget)
+    int root;                        // queue index of the (position, move) item this reply belongs to: its slot counts the item's moves
     int pad[27];
 };
 static_assert(sizeof(StealTask) == 512, "StealTask layout");
 enum { kTaskFree = 0, kTaskPosted = 1, kTaskTaken = 2, kTaskDone0 = 3, kTaskDone1 = 4, kTaskCancelled = 5, kTaskBudget = 6 };
-enum { kCtlQueued = 0, kCtlTaken = 1, kCtlPosted = 2, kCtlBusy = 4, kCtlAllocCursor = 5, kCtlTimeout = 6, kCtlCutoffs = 7 };
+enum { kCtlQueued = 0, kCtlTaken = 1, kCtlPosted = 2, kCtlBusy = 4, kCtlAllocCursor = 5, kCtlTimeout = 6, kCtlCutoffs = 7, kCtlMaxNodes = 8 };
 
 struct Workspace {
     unsigned* counters;      // kCtl* slots
@@ -200,10 +200,12 @@ constexpr int kStealAfterDefault = 96;   // moves tried before a search starts h
 constexpr int kMaxPosted = 3;            // replies handed over per node
 // The reference's recursion (go.py:329-463) is bounded in depth (80) but not in size: on a rare position
 // (one in ~4 million random-playout positions met so far) the tree of replies is astronomically large and
-// the reference itself does not return in any practical time.  Here a search gives up -- "not a ladder" --
-// once one line of it (counted through hand-overs) has tried this many moves; the longest search of the
-// golden and oracle sets tries a few thousand.  rag_features_ladder_cutoffs counts the searches cut off.
-constexpr int kLadderNodeBudget = 1 << 16;
+// the reference itself does not return in any practical time.  Here the search for one (position, move) item
+// gives up -- "not a ladder" -- once it has tried this many moves in total, over all the warps that work on
+// it (they count in steps of 16 on the item's queue slot, which is free once the item has been read).  The
+// largest search met in 8.4 million random-playout positions (tools/ladder_longest.py) tried 46,544 moves.
+// rag_features_ladder_cutoffs counts the items cut off.
+constexpr int kLadderNodeBudget = 1 << 18;
 constexpr int kLadderBudget = 3;         // return value of a search that ran out of budget
 
 __device__ __forceinline__ int ld_vol(const int* p) { return *(const volatile int*)p; }
@@ -219,7 +221,7 @@ struct StealFrames {                     // which tasks each stack frame has out
 #define LANE0_INT(expr) __shfl_sync(kFullMask, (g.lane == 0) ? (int)(expr) : 0, 0)
 
 __device__ __forceinline__ int steal_post(const Workspace& ws, const Geo& g, BB H, BB P, BB G, int ko, int move,
-                                          bool is_capture, int remaining, int nodes) {
+                                          bool is_capture, int remaining, int root) {
     int slot = -1;
     if (g.lane == 0) {
         for (int probe = 0; probe < 8 && slot < 0; probe++) {
@@ -231,7 +233,7 @@ __device__ __forceinline__ int steal_post(const Workspace& ws, const Geo& g, BB 
     if (slot < 0) return -1;
     StealTask* t = ws.tasks + slot;
     t->H[g.lane] = H.w; t->P[g.lane] = P.w; t->G[g.lane] = G.w;
-    if (g.lane == 0) { t->ko = ko; t->move = move; t->is_capture = is_capture ? 1 : 0; t->remaining = remaining; t->nodes = nodes; }
+    if (g.lane == 0) { t->ko = ko; t->move = move; t->is_capture = is_capture ? 1 : 0; t->remaining = remaining; t->root = root; }
     __threadfence();
     __syncwarp();
     if (g.lane == 0) {
@@ -272,7 +274,7 @@ struct TaskCancelled {                    // "has the task I am working on been 
 // ladder_dfs (go_bb.cuh) with hand-over of replies.  `nodes` = moves tried so far by this search.
 __device__ __noinline__ int ladder_dfs_steal(const Workspace& ws, const Geo& g, BB H, BB P, BB G, int ko, BB pending,
                                              bool frame_is_capture, int remaining_children, int nodes, int steal_after,
-                                             LadderStack& st, StealFrames& sf, const int* own_status, long long t_deadline)
+                                             LadderStack& st, StealFrames& sf, const int* own_status, long long t_deadline, int root)
 {
     TaskCancelled cancelled{own_status};
     int d = 0;
@@ -291,7 +293,7 @@ __device__ __noinline__ int ladder_dfs_steal(const Workspace& ws, const Geo& g, 
                 const int m = bb_first(rest);
                 if (m < 0) break;
                 const int slot = steal_post(ws, g, st.hunter[d], st.prey[d], st.group[d], st.ko[d], m, !node_is_capture,
-                                            remaining_children - d, nodes);
+                                            remaining_children - d, root);
                 if (slot < 0) break;
                 rest = andnot(rest, bb_single(m, g));
                 st.pending[d] = andnot(st.pending[d], bb_single(m, g));
@@ -300,8 +302,10 @@ __device__ __noinline__ int ladder_dfs_steal(const Workspace& ws, const Geo& g, 
         }
         const int m = bb_first(st.pending[d]);
         if (m >= 0) {
+            int spent = 0;
+            if ((nodes & 15) == 15) spent = LANE0_INT(atomicAdd(&ws.queue[root], 16u) + 16u);     // the item's total so far
             if ((nodes & 15) == 15 && cancelled()) { v = kLadderAborted; }
-            else if (nodes >= kLadderNodeBudget) { v = kLadderBudget; }
+            else if (spent >= kLadderNodeBudget) { v = kLadderBudget; }
             else {
                 nodes++;
                 st.pending[d] = andnot(st.pending[d], bb_single(m, g));
@@ -367,11 +371,11 @@ __device__ __noinline__ int ladder_dfs_steal(const Workspace& ws, const Geo& g, 
 // is_ladder_capture / is_ladder_escape of one move on one prey group, with hand-over.
 __device__ __forceinline__ int ladder_search_steal(const Workspace& ws, const Geo& g, BB H, BB P, BB G, int ko, int move,
                                                    bool is_capture, int remaining, int nodes, int steal_after, LadderStack& st,
-                                                   StealFrames& sf, const int* own_status, long long t_deadline) {
+                                                   StealFrames& sf, const int* own_status, long long t_deadline, int root) {
     BB pending = bb_zero();
     const int res = ladder_expand(g, is_capture, H, P, G, ko, move, remaining, pending);
     if (res != kLadderPush) return res;
-    return ladder_dfs_steal(ws, g, H, P, G, ko, pending, is_capture, remaining - 1, nodes + 1, steal_after, st, sf, own_status, t_deadline);
+    return ladder_dfs_steal(ws, g, H, P, G, ko, pending, is_capture, remaining - 1, nodes + 1, steal_after, st, sf, own_status, t_deadline, root);
 }
 
 // kBesideConv only makes two copies of the kernel, so that each can have its own shared-memory / L1
@@ -395,7 +399,8 @@ ladder_kernel(const uint32_t* __restrict__ states, int S, int steal_after, int h
         idx = __shfl_sync(kFullMask, idx, 0);
         if (idx >= total) break;
         if (g.lane == 0) atomicAdd(&ws.counters[kCtlBusy], 1u);
-        const uint32_t item = ws.queue[idx];
+        const uint32_t item = LANE0_INT(ld_vol(&ws.queue[idx]));
+        if (g.lane == 0) ws.queue[idx] = 0u;                       // from here on the slot counts the moves this item's search tries
         const int pos = (int)(item >> 11), kind = (int)((item >> 10) & 1u), q = (int)(item & 1023u);
         const LoadedState s = load_state(states + (size_t)pos * RAG_STATE_WORDS, g);
         const BB own = s.player > 0 ? s.black : s.white;
@@ -410,8 +415,8 @@ ladder_kernel(const uint32_t* __restrict__ states, int S, int steal_after, int h
         const int np = ladder_root_preys(g, own, opp, q, is_escape, preys);
         int r = kLadderValue0;
         for (int i = 0; i < np && r == kLadderValue0; i++)
-            r = is_escape ? ladder_search_steal(ws, g, opp, own, preys[i], ko, q, false, kLadderDepth, 0, steal_after, st, sf, nullptr, t_deadline)
-                          : ladder_search_steal(ws, g, own, opp, preys[i], ko, q, true, kLadderDepth, 0, steal_after, st, sf, nullptr, t_deadline);
+            r = is_escape ? ladder_search_steal(ws, g, opp, own, preys[i], ko, q, false, kLadderDepth, 0, steal_after, st, sf, nullptr, t_deadline, (int)idx)
+                          : ladder_search_steal(ws, g, own, opp, preys[i], ko, q, true, kLadderDepth, 0, steal_after, st, sf, nullptr, t_deadline, (int)idx);
 #ifdef RAG_LADDER_TIMING
         if (g.lane == 0) ws.queue[idx] = (uint32_t)((clock64() - t_item) >> 4);     // tools/ladder_profile.py
 #endif
@@ -419,6 +424,8 @@ ladder_kernel(const uint32_t* __restrict__ states, int S, int steal_after, int h
             if (r == kLadderValue1)
                 atomicOr(ws.planes + (size_t)pos * kPlaneWords + (kPlaneLadderCapture + kind) * 32 + (q >> 5), 1u << (q & 31));
             if (r == kLadderBudget) atomicAdd(&ws.counters[kCtlCutoffs], 1u);
+            const unsigned spent = ld_vol(&ws.queue[idx]);
+            if (spent > ld_vol(&ws.counters[kCtlMaxNodes])) atomicMax(&ws.counters[kCtlMaxNodes], spent);
             __threadfence();
             atomicSub(&ws.counters[kCtlBusy], 1u);
         }
@@ -473,8 +480,8 @@ ladder_kernel(const uint32_t* __restrict__ states, int S, int steal_after, int h
         const BB H{__ldcg(&t->H[g.lane])}, P{__ldcg(&t->P[g.lane])}, G{__ldcg(&t->G[g.lane])};
         const int ko = LANE0_INT(ld_vol(&t->ko)), move = LANE0_INT(ld_vol(&t->move));
         const int is_capture = LANE0_INT(ld_vol(&t->is_capture)), remaining = LANE0_INT(ld_vol(&t->remaining));
-        const int nodes0 = LANE0_INT(ld_vol(&t->nodes));
-        const int r = ladder_search_steal(ws, g, H, P, G, ko, move, is_capture != 0, remaining, nodes0, steal_after, st, sf, tstat, t_deadline);
+        const int root = LANE0_INT(ld_vol(&t->root));
+        const int r = ladder_search_steal(ws, g, H, P, G, ko, move, is_capture != 0, remaining, 0, steal_after, st, sf, tstat, t_deadline, root);
         if (g.lane == 0) {
             __threadfence();
             if (r == kLadderAborted) atomicExch(tstat, kTaskFree);
@@ -1248,6 +1255,15 @@ int rag_features_status(const void* d_workspace, void* stream)
     if (flag) return fail(RAG_ECUDA, "the ladder reader gave up waiting for handed-over work (watchdog of %lld cycles): the ladder planes of this "
                                      "workspace are incomplete; run the batch again", g_ladder_watchdog);
     return RAG_OK;
+}
+
+int rag_features_ladder_longest(const void* d_workspace, void* stream)
+{
+    if (!d_workspace) return fail(RAG_EINVAL, "null argument");
+    unsigned count = 0;
+    RAG_CUDA_CHECK(cudaMemcpyAsync(&count, (const char*)d_workspace + kCtlMaxNodes * sizeof(unsigned), sizeof count, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    RAG_CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream));
+    return (int)(count > 0x7fffffffu ? 0x7fffffffu : count);
 }
 
 int rag_features_ladder_cutoffs(const void* d_workspace, void* stream)
