@@ -561,8 +561,19 @@ def run_features(args):
     t0, t1 = E(), E()
     t0.record()
     for s_ in streams: s_.wait_event(t0)
+    # the next batch goes to the lane with the fewest unfinished steps (at most two queued per lane): one batch with
+    # an exceptionally long ladder search then delays the batches behind it on ITS lane only, not a fixed quarter of the sweep
+    pending = [[] for _ in range(lanes)]
     for k in range(K):
-        step(pool[k % npool].packed, k % lanes, evs[k])
+        while True:
+            for q in pending:
+                while q and q[0].query():
+                    q.pop(0)
+            lane = min(range(lanes), key=lambda i: len(pending[i]))
+            if len(pending[lane]) < 2:
+                break
+        step(pool[k % npool].packed, lane, evs[k])
+        pending[lane].append(evs[k][1])
     for s_ in streams: torch.cuda.current_stream().wait_stream(s_)
     t1.record()
     torch.cuda.synchronize()
@@ -631,7 +642,7 @@ def run_features(args):
                                    "%d steps x %d = %d positions per GPU, %d distinct device-generated random-playout batches"
                                    % (K, n, K * n, npool),
                        "batch_per_gpu": n, "positions_per_gpu": K * n,
-                       "schedule": "%d batches in flight on their own streams" % lanes,
+                       "schedule": "%d lanes (streams), at most two steps queued per lane, the next batch goes to the least loaded lane" % lanes,
                        "l2": "no flush needed: every step writes %.0f MB of planes (%.1fx the 126 MB L2) and every batch is new"
                              % (n * 17328 / 1e6, n * 17328 / 126e6),
                        "parallelism": "dp%d (independent positions, no collective)" % world},
