@@ -308,7 +308,7 @@ int rag_net_input_channels(const rag_net* net);
 /* Tuning/test knob (process-wide): 0 = one CTA per tile (default); 1 = convolutions run on CTA pairs
  * (tcgen05 cta_group::2: half the weight tile per CTA, one M=256 UMMA per pair; also RAG_CONV_PAIR=1 in the
  * environment).  Results are identical and the pair kernel is ~13 % faster, but beside the pipeline's persistent
- * ladder kernels its cluster launch sporadically never finishes on B200 / driver 580 (csrc/conv.cu): use 1
+ * feature kernels its cluster launch sporadically never finishes on B200 / driver 580 (csrc/conv.cu): use 1
  * only when nothing else shares the GPU with the forward.  Returns the previous setting. */
 int rag_set_conv_pair(int enable);
 /* No wait inside the convolution kernel is unbounded: a barrier that has not moved for ~4 s (a layer takes

@@ -741,12 +741,14 @@ static size_t conv_smem_bytes(int N, int stages) {
 // loads its own 128 rows of activations and HALF of the weight tile, one M=256 UMMA per pair reads both
 // halves -- 30 % less operand traffic into shared memory per flop, 0.735 instead of 0.843 ms per fp16
 // 3x3 layer.  OFF by default (RAG_CONV_PAIR=1 in the environment or rag_set_conv_pair(1) turns it on):
-// beside the persistent ladder kernels of the pipeline the cluster launch sporadically never finishes
-// on B200 / driver 580 -- about one process in eleven in this round's soak (tools/pair_soak.py: ten runs
-// of 1,200 pipelined steps completed, the next two hung), after 1,000-4,000-step runs at every batch
-// size had all completed.  The stall is not in any mbarrier wait of this kernel (those now record where
-// they stand and trap after ~4 s, rag_conv_stall_report; nothing was recorded), which leaves the
-// co-scheduling of the CTA pair itself or tcgen05.alloc.  Alone on the GPU the pair kernel never stalled.
+// beside the feature kernels of the pipeline the cluster launch sporadically never finishes on B200 /
+// driver 580: after 1,000-4,000-step runs at every batch size had all completed, soaks of the pipelined
+// path (tools/pair_soak.py, 1,200 steps per process) hung in 9 of 26 processes with this kernel -- in
+// eager launches and in graph replays alike, more often when the pipeline is drained and restarted every
+// 100 steps -- and in 0 of 22 with one CTA per tile.  The stall is not in any mbarrier wait of this kernel
+// (those record where they stand and trap after ~4 s, rag_conv_stall_report; nothing was ever recorded),
+// which leaves the co-scheduling of the CTA pair itself or tcgen05.alloc.  Alone on the GPU the pair
+// kernel never stalled.
 static int g_conv_pair = getenv("RAG_CONV_PAIR") ? atoi(getenv("RAG_CONV_PAIR")) != 0 : 0;
 
 static int pick_stages(int N) {

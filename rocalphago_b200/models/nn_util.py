@@ -412,10 +412,15 @@ class Network(object):
             # positional superko needs the analysis entry point that knows the move history; the rest
             # is what rag_eval_batch does: conv-layout emit, then the forward over pixel rows
             vp = ctypes.c_void_p
-            self._ws = fws = torch.empty(int(L.rag_features_workspace_bytes(n)), dtype=torch.uint8, device=batch.device)
-            rows = torch.empty((int(L.rag_net_input_rows(h, n)), int(L.rag_net_input_channels(h))), dtype=torch.float16,
-                               device=batch.device)
-            nws = torch.empty(int(L.rag_net_workspace_bytes(h, n)), dtype=torch.uint8, device=batch.device)
+            key = (n, batch.device)
+            if getattr(self, "_sk_key", None) != key:            # the three buffers of this branch are kept per batch size
+                self._sk_bufs = (torch.empty(int(L.rag_features_workspace_bytes(n)), dtype=torch.uint8, device=batch.device),
+                                 torch.empty((int(L.rag_net_input_rows(h, n)), int(L.rag_net_input_channels(h))), dtype=torch.float16,
+                                             device=batch.device),
+                                 torch.empty(int(L.rag_net_workspace_bytes(h, n)), dtype=torch.uint8, device=batch.device))
+                self._sk_key = key
+            fws, rows, nws = self._sk_bufs
+            self._ws = fws
             analyze_into(batch, fws, True)
             with torch.cuda.device(batch.device):
                 _cabi.check(L.rag_features_emit(_ptr(fws), n, batch.size, src.ctypes.data_as(vp), len(src), LAYOUT_CONV_IN,
