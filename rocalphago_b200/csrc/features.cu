@@ -1149,7 +1149,8 @@ int rag_features_ladders(const uint32_t* d_states, int n, int size, void* d_work
     RAG_CUDA_CHECK(cudaGetDevice(&dev));
     RAG_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     long long want = ((long long)n * 16 + kWarpsPerBlock - 1) / kWarpsPerBlock;
-    int blocks = (int)(want < (long long)sms * 4 ? (want < 1 ? 1 : want) : (long long)sms * 4);
+    static const int per_sm = getenv("RAG_LADDER_CTAS_PER_SM") ? atoi(getenv("RAG_LADDER_CTAS_PER_SM")) : 4;     // experiment knob
+    int blocks = (int)(want < (long long)sms * per_sm ? (want < 1 ? 1 : want) : (long long)sms * per_sm);
     ladder_kernel<1><<<blocks, kWarpsPerBlock * 32, 0, (cudaStream_t)stream>>>(d_states, size, g_steal_after, g_helper_ctas, g_ladder_watchdog, ws);
     RAG_CUDA_CHECK(cudaGetLastError());
     return RAG_OK;
