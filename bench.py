@@ -202,7 +202,10 @@ def reference_entries(cores, forward_pos_per_s):
     """cpu_baseline entries for the reference's own Python: its features (1 core / all cores) followed serially
     by the fp32 forward (policy.py:42-45 runs them one after the other; Keras cannot run here, so the forward
     is the torch restatement at `forward_pos_per_s`)."""
-    ref = reference_python_features(24, 4, cores)
+    try:
+        ref = reference_python_features(24, 4, cores)
+    except Exception as e:  # noqa: BLE001 -- a reported baseline must never cost the bench line
+        return {"reference_error": str(e)[:200]}
     if ref is None:
         return {}
     out = {}
@@ -675,7 +678,10 @@ def run_features(args):
                 tf = time.time() - c0
             line["cpu_baseline"] = {"value": sample / tf, "unit": "positions/s", "cores": cores, "kind": "port",
                                     "sample": "%d random-playout positions once: C feature oracle on %d processes, %.2f s" % (sample, cores, tf)}
-            ref = reference_python_features(24, 4, cores)
+            try:
+                ref = reference_python_features(24, 4, cores)
+            except Exception as e:  # noqa: BLE001
+                ref, line["cpu_baseline"]["reference_error"] = None, str(e)[:200]
             if ref:
                 line["cpu_baseline"]["reference"] = dict(ref["single"], kind="reference")
                 line["cpu_baseline"]["reference_all_cores"] = dict(ref["all_cores"], kind="reference")
