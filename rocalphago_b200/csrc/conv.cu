@@ -747,8 +747,10 @@ static size_t conv_smem_bytes(int N, int stages) {
 // eager launches and in graph replays alike, more often when the pipeline is drained and restarted every
 // 100 steps -- and in 0 of 22 with one CTA per tile.  The stall is not in any mbarrier wait of this kernel
 // (those record where they stand and trap after ~4 s, rag_conv_stall_report; nothing was ever recorded),
-// which leaves the co-scheduling of the CTA pair itself or tcgen05.alloc.  Alone on the GPU the pair
-// kernel never stalled.
+// which leaves the co-scheduling of the CTA pair itself or tcgen05.alloc.  It needs pair CTAs and
+// CTAs of another kernel on the same SM: with feature kernels that prefer a large L1 (RAG_FEATURE_CARVEOUT=0:
+// an SM drains before it takes a convolution CTA) 10 of 10 processes completed, with the all-shared or the
+// 196 KB split 12 of 36 hung.  Alone on the GPU the pair kernel never stalled.
 static int g_conv_pair = getenv("RAG_CONV_PAIR") ? atoi(getenv("RAG_CONV_PAIR")) != 0 : 0;
 
 static int pick_stages(int N) {
