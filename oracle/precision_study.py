@@ -51,6 +51,22 @@ def diffuse_round(W):
     return out
 
 
+# Expected mean of every canonical feature plane, as csrc/conv.cu's kPlaneDensity (rank="device" restates the
+# device's channel ranking: response of every filter to these means, bias included, propagated through ReLU)
+PLANE_DENSITY = [0.26, 0.26, 0.48, 1.00, 0.003, 0.003, 0.003, 0.003, 0.003, 0.003, 0.003, 0.50,
+                 0.052, 0.071, 0.085, 0.074, 0.048, 0.040, 0.029, 0.117,
+                 0.457, 0.009, 0.002, 0.001, 0.0005, 0.0003, 0.0002, 0.0006,
+                 0.013, 0.002, 0.001, 0.0006, 0.0004, 0.0003, 0.0002, 0.0007,
+                 0.018, 0.047, 0.107, 0.155, 0.041, 0.041, 0.020, 0.041,
+                 0.014, 0.007, 0.466, 0.0, 0.471, 0.50]
+
+
+def device_response(W, b, mean_in):
+    """float32 response of every filter to the mean input, computed like rag_net_load_weights does (double sums)."""
+    sw = W.double().sum(dim=(2, 3))                                   # (out, in): sum over taps
+    return (b.double() + (sw * mean_in.double()[None, :]).sum(1)).float()
+
+
 def rank_channels(W_prev, mean_in, how):
     """Order of a layer's OUTPUT channels, most energetic first.  `static`: by the filter's response
     to the mean input (sum over taps of W . mean_in) -- known at load time."""
@@ -64,6 +80,8 @@ def emulated_logits(weights, x, specs, schedule, diffuse=False, kernel_flip=True
     order = None
     with torch.no_grad():
         mean_in = h.mean(dim=(0, 2, 3)) if rank != 'uniform' else torch.full((h.shape[1],), 0.25)
+        if rank == "device":
+            mean_in = torch.tensor(PLANE_DENSITY[:h.shape[1]], dtype=torch.float32)
         for l, (nb, k) in enumerate(specs):
             mode = schedule[l]
             W = torch.from_numpy(np.asarray(weights[i], np.float32))
@@ -83,13 +101,23 @@ def emulated_logits(weights, x, specs, schedule, diffuse=False, kernel_flip=True
                 y = F.conv2d(a_hi, w_hi, b, padding=k // 2)
                 y = y + F.conv2d(a_lo[:, top], w_hi[:, top], None, padding=k // 2)
                 y = y + F.conv2d(a_hi[:, top], w_lo[:, top], None, padding=k // 2)
-                order = rank_channels(W, mean_in, rank)
+                if rank == "device":
+                    resp = device_response(W, b, mean_in)
+                    order = torch.sort(resp, descending=True, stable=True).indices
+                    mean_in = torch.relu(resp)
+                else:
+                    order = rank_channels(W, mean_in, rank)
+                    mean_in = h.mean(dim=(0, 2, 3)) if rank == "calib" else torch.relu((W.sum(dim=(2, 3)) * mean_in[None, :]).sum(1))
                 h = F.relu(y)
-                mean_in = h.mean(dim=(0, 2, 3)) if rank == "calib" else torch.relu((W.sum(dim=(2, 3)) * mean_in[None, :]).sum(1))
                 i += 2
                 continue
-            order = rank_channels(W, mean_in, rank)
-            mean_in_next = torch.relu((W.sum(dim=(2, 3)) * mean_in[None, :]).sum(1))
+            if rank == "device":
+                resp = device_response(W, b, mean_in)
+                order = torch.sort(resp, descending=True, stable=True).indices
+                mean_in_next = torch.relu(resp)
+            else:
+                order = rank_channels(W, mean_in, rank)
+                mean_in_next = torch.relu((W.sum(dim=(2, 3)) * mean_in[None, :]).sum(1))
             if mode == "f":
                 a_op, w_op = h, W
             elif mode == "b":
@@ -154,7 +182,7 @@ def main():
     ap.add_argument("--schedules", nargs="+", default=["h" * 12])
     ap.add_argument("--diffuse", action="store_true")
     ap.add_argument("--G", type=int, default=32)
-    ap.add_argument("--rank", default="static", choices=["static", "true", "calib", "uniform"])
+    ap.add_argument("--rank", default="static", choices=["static", "true", "calib", "uniform", "device"])
     ap.add_argument("--threads", type=int, default=os.cpu_count())
     a = ap.parse_args()
     torch.set_num_threads(a.threads)

@@ -135,6 +135,36 @@ def test_corrected_channel_modes_cut_the_rounding_noise(dtype, noise):
     assert np.array_equal(got3, got)
 
 
+@pytest.mark.parametrize("dtype,schedule,G", [("fp16", "h" * 12, 0), ("fp16c32", "h" + "p" * 11, 32), ("fp16c64", "h" + "p" * 11, 64)])
+def test_device_arithmetic_equals_its_cpu_emulation(dtype, schedule, G):
+    """oracle/precision_study.py restates the tensor-core arithmetic of every precision mode on the CPU -- fp16
+    operands, exact products, fp32 accumulation, and for fp16c32 / fp16c64 the same channel ranking as
+    rag_net_load_weights (response to the plane densities, bias included, stable order) with the lo terms of
+    exactly those channels.  Two things must hold.  The device's distance to the fp32 forward equals the
+    emulation's (the mode removes exactly the noise it is designed to remove).  And the two rounding-noise
+    patterns are correlated: the distance between device and emulation is below either's distance to fp32
+    (independent noise would give 1.41x) -- it cannot be much below, because a 12-layer random network
+    amplifies accumulation-order differences: the emulation differs from ITSELF by 0.78x when its sums are
+    taken in float64 or its channels in another order."""
+    from oracle import precision_study as ps
+    feats = go_oracle.DEFAULT_FEATURES
+    n = 192
+    b, a, ko, pl = _positions(n, seed=31)
+    planes = go_oracle.features(b, a, ko, pl, feats)
+    specs = cnn_oracle.layer_specs(input_dim=48, layers=12, filters_per_layer=192)
+    weights = cnn_oracle.uniform_weights(specs, 48, 19, seed=9)
+    want = cnn_oracle.forward(weights, planes, specs, threads=os.cpu_count(), return_logits=True)
+    emu = ps.emulated_logits(weights, planes, specs, schedule, G=G, rank="device")
+    net = CNNPolicy(feats, layers=12, filters_per_layer=192, dtype=dtype)
+    net.model.set_weights(weights)
+    got = _centered(net.model.eval_batch_device(BatchedGameState.from_arrays(b, a, ko, pl), net.preprocessor.plane_src).cpu().numpy())
+    rms = lambda x, y: float(np.sqrt((((x - x.mean(1, keepdims=True)) - (y - y.mean(1, keepdims=True))) ** 2).mean()))  # noqa: E731
+    to_fp32, to_emulation, emulation_to_fp32 = rms(got, want), rms(got, emu), rms(emu, want)
+    print(dtype, "device-fp32 %.3e  device-emulation %.3e  emulation-fp32 %.3e" % (to_fp32, to_emulation, emulation_to_fp32))
+    assert to_emulation <= 0.92 * to_fp32, (to_emulation, to_fp32)
+    assert 0.85 <= to_fp32 / emulation_to_fp32 <= 1.18, (to_fp32, emulation_to_fp32)
+
+
 @pytest.mark.parametrize("dtype", ["fp16c32", "fp16c64"])
 @pytest.mark.parametrize("arch,n", [
     (dict(layers=3, filters_per_layer=32), 16),
