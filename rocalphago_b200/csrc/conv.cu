@@ -823,15 +823,22 @@ static int output_map(rag_net* net, Layer& ly, const void* ptr, int n, int pitch
 
 static StallRecord* g_stall_host = nullptr;
 
+// one record in portable host-mapped memory for the process; every device that runs a forward gets its address
+// (the first forward on a device does this: make it before any stream capture, like every first call here)
 static int stall_record_ready() {
-    static bool done = false;
-    if (done) return RAG_OK;
+    static bool done[64] = {false};
+    int dev = 0;
+    RAG_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return fail(RAG_EUNSUPPORTED, "device ordinal %d not supported", dev);
+    if (done[dev]) return RAG_OK;
+    if (!g_stall_host) {
+        RAG_CUDA_CHECK(cudaHostAlloc((void**)&g_stall_host, sizeof(StallRecord), cudaHostAllocMapped | cudaHostAllocPortable));
+        memset(g_stall_host, 0, sizeof(StallRecord));
+    }
     StallRecord* dev_view = nullptr;
-    RAG_CUDA_CHECK(cudaHostAlloc((void**)&g_stall_host, sizeof(StallRecord), cudaHostAllocMapped | cudaHostAllocPortable));
-    memset(g_stall_host, 0, sizeof(StallRecord));
     RAG_CUDA_CHECK(cudaHostGetDevicePointer((void**)&dev_view, g_stall_host, 0));
     RAG_CUDA_CHECK(cudaMemcpyToSymbol(g_stall_record, &dev_view, sizeof dev_view));
-    done = true;
+    done[dev] = true;
     return RAG_OK;
 }
 
