@@ -223,6 +223,32 @@ int rag_select_moves(const float* d_probs, const void* d_workspace, int n, int s
 int rag_move_distributions(const float* d_probs, const void* d_workspace, int n, int size, int include_eyes,
                            int16_t* d_moves, float* d_out, int32_t* d_counts, void* stream);
 
+/* ------------------------------------------------------------------ search tree
+ *
+ * The tree of AlphaGo/mcts.py (TreeNode :11-92, MCTS._playout :137-169, update_with_move :208-217) as host-side
+ * native code, advanced in waves: `count` playouts move one ply per rag_tree_wave_step; between steps the caller
+ * evaluates the positions standing on unexpanded nodes (rag_tree_wave_leaves -> policy batch -> rag_tree_wave_expand)
+ * and plays the chosen moves (rag_do_move); rag_tree_wave_backup adds the leaf values (mcts.py:72-80; virtual visits of
+ * the wave, `virtual_loss` per visit, are taken back).  With count = 1 the arithmetic is the reference's, bit for bit.
+ * Moves are flat points x*S+y.  Host memory only; one thread at a time per tree. */
+typedef struct rag_tree rag_tree;
+int rag_tree_create(double c_puct, rag_tree** out);
+int rag_tree_destroy(rag_tree* tree);
+int rag_tree_reset(rag_tree* tree);
+int rag_tree_wave_begin(rag_tree* tree, int count, double virtual_loss);
+int rag_tree_wave_leaves(rag_tree* tree, int32_t* rows);                     /* returns k <= count */
+int rag_tree_wave_expand(rag_tree* tree, int k, const int32_t* rows, const int64_t* counts, const int64_t* moves,
+                         const float* priors);
+int rag_tree_wave_step(rag_tree* tree, int32_t* moves_out);                  /* returns playouts alive; -2 = no move */
+int rag_tree_wave_backup(rag_tree* tree, const double* values);
+int rag_tree_advance(rag_tree* tree, int action);                            /* 1: subtree kept, 0: new tree */
+int rag_tree_root(const rag_tree* tree);
+long long rag_tree_size(const rag_tree* tree);
+int rag_tree_node_children(const rag_tree* tree, int node);
+int rag_tree_node_stats(const rag_tree* tree, int node, long long* visits, double* q, int32_t* parent, int32_t* index);
+int rag_tree_node_arrays(const rag_tree* tree, int node, int32_t* actions, double* P, double* Q, double* u, int64_t* n,
+                         int64_t* virt, int32_t* child);
+
 /* ------------------------------------------------------------------ state updates
  *
  * GameState.do_move (go.py:521-581) on packed states, in place, one move per

@@ -67,6 +67,20 @@ def lib():
         "rag_features_static": (i32, [vp, i32, i32, vp, i32, i32, i32, i32, vp, vp]),
         "rag_features_static_max_positions": (i32, []),
         "rag_conv_rows": (i64, [i32, i32]),
+        "rag_tree_create": (i32, [c.c_double, vp]),
+        "rag_tree_destroy": (i32, [vp]),
+        "rag_tree_reset": (i32, [vp]),
+        "rag_tree_wave_begin": (i32, [vp, i32, c.c_double]),
+        "rag_tree_wave_leaves": (i32, [vp, vp]),
+        "rag_tree_wave_expand": (i32, [vp, i32, vp, vp, vp, vp]),
+        "rag_tree_wave_step": (i32, [vp, vp]),
+        "rag_tree_wave_backup": (i32, [vp, vp]),
+        "rag_tree_advance": (i32, [vp, i32]),
+        "rag_tree_root": (i32, [vp]),
+        "rag_tree_size": (i64, [vp]),
+        "rag_tree_node_children": (i32, [vp, i32]),
+        "rag_tree_node_stats": (i32, [vp, i32, vp, vp, vp, vp]),
+        "rag_tree_node_arrays": (i32, [vp, i32, vp, vp, vp, vp, vp, vp, vp]),
         "rag_select_moves": (i32, [vp, vp, i32, i32, c.c_float, i32, u64, vp, vp]),
         "rag_move_distributions": (i32, [vp, vp, i32, i32, i32, vp, vp, vp, vp]),
         "rag_do_move": (i32, [vp, i32, i32, vp, vp, vp]),

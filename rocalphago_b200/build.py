@@ -7,7 +7,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_DIR = os.path.join(HERE, "_lib")
 LIB_PATH = os.path.join(LIB_DIR, "librocalphago_b200.so")
-SOURCES = ["features.cu", "conv.cu"]
+SOURCES = ["features.cu", "conv.cu", "tree.cpp"]
 HEADERS = ["go_bb.cuh", "rag_common.h", "../../include/rocalphago_b200.h"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "--use_fast_math"]
@@ -51,7 +51,7 @@ def build_library(force=False, verbose=False):
         path = os.path.join(CSRC, src)
         if not os.path.exists(path):
             continue
-        obj = os.path.join(LIB_DIR, src.replace(".cu", ".o"))
+        obj = os.path.join(LIB_DIR, os.path.splitext(src)[0] + ".o")
         cmd = [_nvcc()] + NVCC_FLAGS + ["-c", path, "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")

@@ -23,69 +23,81 @@ playout for playout (tests/test_gpu_mcts.py compares visit counts with the refer
 `state.copy()`, and GameState.copy() does not copy stone_ages (go.py:186-217), so the networks see the
 stones of the root position without any turns_since bit.  Pass False to search with the real ages.
 
+The tree itself is native host code (csrc/tree.cpp behind rag_tree_*): a wave costs a handful of calls per ply
+instead of a Python loop over its playouts; `TreeNode` below is a read-only view of one of its nodes.
+
 Rollouts (lmbda > 0) use uniformly random sensible moves to the end of the game on the device
 (`rollout_limit` plies) and area scoring as go.py:482-506; the reference's greedy-policy rollout
 (one network call per ply) is not offered.
 """
+import ctypes
+
 import numpy as np
 import torch
 
+from . import _cabi
 from .state import BatchedGameState, STATE_WORDS
 
 
+def _p(a):
+    return a.ctypes.data_as(ctypes.c_void_p)
+
+
 class TreeNode(object):
-    """A node and its children's statistics as arrays (mcts.py:11-92 keeps one object per child)."""
+    """Read-only view of one node of the native tree and of its children's statistics (mcts.py:11-92 keeps one
+    object per child): `actions` (flat moves x*S+y), `P`, `Q`, `u`, `n`, `virtual` as arrays over the children,
+    `children` (views, None where a child was never walked into), `visits` / `q` of the node itself."""
 
-    __slots__ = ("parent", "index", "actions", "P", "Q", "u", "n", "virtual", "children", "visits", "q")
+    def __init__(self, search, node):
+        self._search, self._node = search, int(node)
 
-    def __init__(self, parent, index):
-        self.parent, self.index = parent, index          # `index`: which child of `parent` this node is
-        self.actions = None                              # flat moves x*S+y of the children, None while a leaf
-        self.P = self.Q = self.u = self.n = self.virtual = None
-        self.children = None                             # TreeNode or None per child, made when first walked into
-        self.visits, self.q = 0, 0.0                     # the root's own counters (a child's live in its parent's arrays)
+    def _arrays(self):
+        L, h = _cabi.lib(), self._search._tree
+        k = _cabi_check_count(L.rag_tree_node_children(h, self._node))
+        out = (np.empty(k, np.int32), np.empty(k), np.empty(k), np.empty(k), np.empty(k, np.int64), np.empty(k, np.int64),
+               np.empty(k, np.int32))
+        _cabi.check(L.rag_tree_node_arrays(h, self._node, *[_p(a) for a in out]))
+        return out
+
+    def _stats(self):
+        L, h = _cabi.lib(), self._search._tree
+        visits, q, parent, index = ctypes.c_longlong(), ctypes.c_double(), ctypes.c_int32(), ctypes.c_int32()
+        _cabi.check(L.rag_tree_node_stats(h, self._node, ctypes.byref(visits), ctypes.byref(q), ctypes.byref(parent), ctypes.byref(index)))
+        return int(visits.value), float(q.value), int(parent.value), int(index.value)
+
+    actions = property(lambda self: self._arrays()[0] if not self.is_leaf() else None)
+    P = property(lambda self: self._arrays()[1])
+    Q = property(lambda self: self._arrays()[2])
+    u = property(lambda self: self._arrays()[3])
+    n = property(lambda self: self._arrays()[4])
+    virtual = property(lambda self: self._arrays()[5])
+    visits = property(lambda self: self._stats()[0])
+    q = property(lambda self: self._stats()[1])
+    index = property(lambda self: self._stats()[3])
+
+    @property
+    def parent(self):
+        p = self._stats()[2]
+        return None if p < 0 else TreeNode(self._search, p)
+
+    @property
+    def children(self):
+        return [None if c < 0 else TreeNode(self._search, c) for c in self._arrays()[6].tolist()]
 
     def is_leaf(self):
-        return self.actions is None
+        return _cabi_check_count(_cabi.lib().rag_tree_node_children(self._search._tree, self._node)) == 0
 
     def is_root(self):
-        return self.parent is None
-
-    def expand(self, actions, priors):
-        """mcts.py:26-38: one child per (action, prior); u starts as the prior (mcts.py:22)."""
-        k = len(actions)
-        self.actions = np.asarray(actions, np.int32)
-        self.P = np.asarray(priors, np.float64)
-        self.u = self.P.copy()
-        self.Q, self.n, self.virtual = np.zeros(k), np.zeros(k, np.int64), np.zeros(k, np.int64)
-        self.children = [None] * k
-
-    def select(self, virtual_loss):
-        """mcts.py:40-46: the child of largest Q + u (the first one on ties, as max() over the
-        children in insertion order gives); virtual visits of the wave in flight count against it."""
-        score = self.Q + self.u
-        if virtual_loss:
-            score = score - virtual_loss * self.virtual
-        return int(np.argmax(score))
-
-    def child(self, i):
-        if self.children[i] is None:
-            self.children[i] = TreeNode(self, i)
-        return self.children[i]
+        return self._stats()[2] < 0
 
     def n_visits(self):
-        return self.visits if self.parent is None else int(self.parent.n[self.index])
+        return self.visits
 
 
-def _update_path(path, leaf_value, c_puct, root):
-    """update_recursive (mcts.py:72-80) along `path` = [(node, child index), ...] from the root down."""
-    root.visits += 1
-    root.q += (leaf_value - root.q) / root.visits
-    for node, i in path:
-        node.n[i] += 1
-        node.Q[i] += (leaf_value - node.Q[i]) / node.n[i]
-        parent_visits = node.visits if node.parent is None else node.parent.n[node.index]
-        node.u[i] = c_puct * node.P[i] * np.sqrt(parent_visits) / (1 + node.n[i])
+def _cabi_check_count(rc):
+    if rc < 0:
+        _cabi.check(rc)
+    return rc
 
 
 class BatchedMCTS(object):
@@ -108,49 +120,44 @@ class BatchedMCTS(object):
         self._batch, self._vl = max(1, int(batch)), float(virtual_loss)
         self._seed = int(seed)
         self._forget_ages = bool(forget_ages)
-        self._root = TreeNode(None, 0)
+        self._tree = ctypes.c_void_p()
+        _cabi.check(_cabi.lib().rag_tree_create(ctypes.c_double(self._c_puct), ctypes.byref(self._tree)))
+        self._size = None
         self.evaluations = 0            # positions sent through the policy network (for reports)
+
+    def __del__(self):
+        try:
+            if self._tree:
+                _cabi.lib().rag_tree_destroy(self._tree)
+        except Exception:  # noqa: BLE001
+            pass
+
+    @property
+    def _root(self):
+        return TreeNode(self, _cabi.lib().rag_tree_root(self._tree))
 
     # ------------------------------------------------------------------ one wave of playouts
     def _wave(self, root_packed, size, count):
-        dev = root_packed.device
+        L, h, dev = _cabi.lib(), self._tree, root_packed.device
         states = BatchedGameState(root_packed.expand(count, STATE_WORDS).clone(), size)       # a fresh copy even for count == 1
         if self._forget_ages:
             states.forget_ages()         # every playout starts from state.copy() (mcts.py:201), which drops stone_ages
-        nodes = [self._root] * count
-        paths = [[] for _ in range(count)]
-        alive = np.ones(count, bool)
-        vl = self._vl if count > 1 else 0.0
+        _cabi.check(L.rag_tree_wave_begin(h, count, ctypes.c_double(self._vl)))
+        rows, moves = np.empty(count, np.int32), np.empty(count, np.int32)
         for _ in range(self._L):
-            # expand the leaves among the nodes the live playouts stand on -- each node once
-            need = {}
-            for j in range(count):
-                if alive[j] and nodes[j].is_leaf():
-                    need.setdefault(id(nodes[j]), j)
-            if need:
-                rows = sorted(need.values())
-                sub = BatchedGameState(states.packed[torch.as_tensor(rows, device=dev)].contiguous(), size)
+            # expand the leaves among the nodes the live playouts stand on -- each node once, in one policy batch
+            k = _cabi_check_count(L.rag_tree_wave_leaves(h, _p(rows)))
+            if k:
+                sub = BatchedGameState(states.packed[torch.as_tensor(rows[:k].astype(np.int64), device=dev)].contiguous(), size)
                 _, flat, counts, probs = self._policy.eval_arrays(sub)
-                self.evaluations += len(rows)
-                ends = np.cumsum(counts)
-                for k, j in enumerate(rows):
-                    a, b = ends[k] - counts[k], ends[k]
-                    if b > a:
-                        nodes[j].expand(flat[a:b], probs[a:b])
-            moves = np.full(count, -2, np.int32)               # -2: this playout does not move
-            for j in range(count):
-                if not alive[j]:
-                    continue
-                node = nodes[j]
-                if node.is_leaf():                             # no legal move: end of game (mcts.py:154-156)
-                    alive[j] = False
-                    continue
-                i = node.select(vl)
-                node.virtual[i] += 1
-                paths[j].append((node, i))
-                moves[j] = node.actions[i]
-                nodes[j] = node.child(i)
-            if not alive.any():
+                self.evaluations += k
+                flat = np.ascontiguousarray(flat, np.int64)
+                counts = np.ascontiguousarray(counts, np.int64)
+                probs = np.ascontiguousarray(probs, np.float32)
+                _cabi.check(L.rag_tree_wave_expand(h, k, _p(rows), _p(counts), _p(flat), _p(probs)))
+            # every live playout takes the child of largest Q + u; one without children is at the end of the game (mcts.py:154-156)
+            alive = _cabi_check_count(L.rag_tree_wave_step(h, _p(moves)))
+            if alive == 0:
                 break
             moving = torch.as_tensor(moves >= 0, device=dev)
             before = states.packed.clone()
@@ -163,10 +170,8 @@ class BatchedMCTS(object):
         if self._lmbda > 0.0:
             z = self._rollouts(states)
             v = (1.0 - self._lmbda) * v + self._lmbda * z
-        for j in range(count):
-            for node, i in paths[j]:
-                node.virtual[i] -= 1
-            _update_path(paths[j], float(v[j]), self._c_puct, self._root)
+        v = np.ascontiguousarray(v, np.float64)
+        _cabi.check(L.rag_tree_wave_backup(h, _p(v)))
 
     def _rollouts(self, states):
         """+1 / -1 / 0 for the player to move at each leaf after a random playout to the end (mcts.py:171-189,
@@ -181,6 +186,7 @@ class BatchedMCTS(object):
         batch = state if isinstance(state, BatchedGameState) else BatchedGameState.from_states([state])
         if len(batch) != 1:
             raise ValueError("get_move takes one position")
+        self._size = batch.size
         done = 0
         while done < self._n_playout:
             count = min(self._batch, self._n_playout - done)
@@ -201,22 +207,18 @@ class BatchedMCTS(object):
 
     def update_with_move(self, last_move, size=None):
         """Steps the root to the child for `last_move`, keeping its subtree (mcts.py:208-217)."""
-        r = self._root
-        if last_move is not None and not r.is_leaf():
-            s = size if size is not None else None
-            flat = last_move if np.isscalar(last_move) else None
-            if flat is None:
-                if s is None:
-                    raise ValueError("pass size= with an (x, y) move")
-                flat = last_move[0] * s + last_move[1]
-            hit = np.flatnonzero(r.actions == flat)
-            if len(hit):
-                child = r.child(int(hit[0]))
-                child.visits, child.q = int(r.n[hit[0]]), float(r.Q[hit[0]])
-                child.parent = None
-                self._root = child
-                return
-        self._root = TreeNode(None, 0)
+        L = _cabi.lib()
+        if last_move is None:
+            _cabi.check(L.rag_tree_reset(self._tree))
+            return
+        if np.isscalar(last_move):
+            flat = int(last_move)
+        else:
+            s = size if size is not None else self._size
+            if s is None:
+                raise ValueError("pass size= with an (x, y) move")
+            flat = last_move[0] * s + last_move[1]
+        _cabi_check_count(L.rag_tree_advance(self._tree, flat))
 
 
 def _network_of(fn, what):
