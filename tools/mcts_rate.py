@@ -12,7 +12,7 @@ pol = CNNPolicy(DEFAULT_FEATURES, layers=12, filters_per_layer=192, seed=1)
 val = CNNValue(DEFAULT_FEATURES + ["color"], layers=12, filters_per_layer=192, seed=2)
 pos = BatchedGameState.random_playouts(64, seed=11, max_ply=120, stride=8)
 root = BatchedGameState(pos.packed[40:41].clone(), 19)
-for batch, n in ((1, 16), (16, 128), (64, 512), (256, 2048)):
+for batch, n in ((1, 16), (16, 128), (64, 512), (256, 2048), (1024, 8192)):
     s = BatchedMCTS(pol, val, playout_depth=20, n_playout=n, batch=batch)
     s.get_move(root); torch.cuda.synchronize()                     # warm-up (also grows the tree: a second search is the steady state)
     s = BatchedMCTS(pol, val, playout_depth=20, n_playout=n, batch=batch)
