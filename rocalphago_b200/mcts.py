@@ -221,6 +221,103 @@ class BatchedMCTS(object):
         _cabi_check_count(L.rag_tree_advance(self._tree, flat))
 
 
+class ParallelMCTS(object):
+    """Several searches at once (the reference's `ParallelMCTS`, mcts.py:219-220, is an empty subclass): one
+    BatchedMCTS tree per position, all advanced in lock step, so that every ply costs ONE policy batch over the
+    unexpanded nodes of all trees, one rag_do_move launch and, at the end of the wave, one value batch -- the
+    leaf-evaluation pattern of BASELINE config 5.  Each tree ends up exactly as if it had been searched alone
+    with the same settings (the device evaluates every position independently of its batch).
+
+        par = ParallelMCTS(policy, value, games=16, n_playout=1600, batch=64)
+        moves = par.get_moves(states)                  # list of (x, y) / None, one per state
+        par.update_with_moves(moves)
+    """
+
+    def __init__(self, policy, value=None, games=16, **kw):
+        self.searches = [BatchedMCTS(policy, value, **kw) for _ in range(int(games))]
+        self._policy, self._value = policy, value
+
+    def _wave(self, roots, size, count):
+        L = _cabi.lib()
+        S = self.searches[:len(roots)]
+        G, dev = len(S), roots.device
+        first = S[0]
+        states = BatchedGameState(roots[:, None, :].expand(G, count, STATE_WORDS).reshape(G * count, STATE_WORDS).clone(), size)
+        if first._forget_ages:
+            states.forget_ages()
+        for s in S:
+            _cabi.check(L.rag_tree_wave_begin(s._tree, count, ctypes.c_double(s._vl)))
+        rows, moves = np.empty(count, np.int32), np.empty(G * count, np.int32)
+        for _ in range(first._L):
+            need, per_tree = [], []
+            for g, s in enumerate(S):
+                k = _cabi_check_count(L.rag_tree_wave_leaves(s._tree, _p(rows)))
+                per_tree.append(rows[:k].copy())
+                need.append(rows[:k].astype(np.int64) + g * count)
+            need = np.concatenate(need)
+            if len(need):
+                sub = BatchedGameState(states.packed[torch.as_tensor(need, device=dev)].contiguous(), size)
+                _, flat, counts, probs = self._policy.eval_arrays(sub)
+                flat, counts = np.ascontiguousarray(flat, np.int64), np.ascontiguousarray(counts, np.int64)
+                probs = np.ascontiguousarray(probs, np.float32)
+                ends = np.concatenate([[0], np.cumsum(counts)])
+                at = 0
+                for g, s in enumerate(S):
+                    k = len(per_tree[g])
+                    if k:
+                        a, b = int(ends[at]), int(ends[at + k])
+                        r = np.ascontiguousarray(per_tree[g])
+                        c, f, pr = np.ascontiguousarray(counts[at:at + k]), np.ascontiguousarray(flat[a:b]), np.ascontiguousarray(probs[a:b])
+                        _cabi.check(L.rag_tree_wave_expand(s._tree, k, _p(r), _p(c), _p(f), _p(pr)))
+                        s.evaluations += k
+                        at += k
+            alive = 0
+            for g, s in enumerate(S):
+                mv = np.empty(count, np.int32)
+                alive += _cabi_check_count(L.rag_tree_wave_step(s._tree, _p(mv)))
+                moves[g * count:(g + 1) * count] = mv
+            if alive == 0:
+                break
+            moving = torch.as_tensor(moves >= 0, device=dev)
+            before = states.packed.clone()
+            states.do_move(np.where(moves >= 0, moves, -1))
+            states.packed = torch.where(moving[:, None], states.packed, before)
+        v = np.zeros(G * count)
+        if first._lmbda < 1.0:
+            v = np.asarray(self._value.batch_eval_state(states), np.float64)
+        if first._lmbda > 0.0:
+            v = (1.0 - first._lmbda) * v + first._lmbda * first._rollouts(states)
+        for g, s in enumerate(S):
+            _cabi.check(L.rag_tree_wave_backup(s._tree, _p(np.ascontiguousarray(v[g * count:(g + 1) * count], np.float64))))
+
+    def get_moves(self, states):
+        """Runs n_playout playouts in every tree (waves of `batch` per tree) and returns the most visited move of each."""
+        batch = states if isinstance(states, BatchedGameState) else BatchedGameState.from_states(states)
+        G = len(batch)
+        if G > len(self.searches):
+            raise ValueError("%d positions for %d trees" % (G, len(self.searches)))
+        first = self.searches[0]
+        done = 0
+        while done < first._n_playout:
+            count = min(first._batch, first._n_playout - done)
+            self._wave(batch.packed, batch.size, count)
+            done += count
+        out = []
+        for s in self.searches[:G]:
+            s._size = batch.size
+            root = s._root
+            if root.is_leaf():
+                out.append(None)
+            else:
+                a = int(root.actions[int(np.argmax(root.n))])
+                out.append((a // batch.size, a % batch.size))
+        return out
+
+    def update_with_moves(self, moves, size=None):
+        for s, m in zip(self.searches, moves):
+            s.update_with_move(m, size=size)
+
+
 def _network_of(fn, what):
     """The CNNPolicy / CNNValue behind a reference-style callable (the object itself, or its bound
     eval_state / __call__)."""

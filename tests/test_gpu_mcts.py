@@ -120,3 +120,26 @@ def test_winners_match_the_reference_and_rollouts_match_the_oracle():
             want = go_oracle.rollout_winners(b, a, ko, pl, limit=limit, seed=seed)
             assert np.array_equal(got.astype(np.int32), want), (size, limit)
         assert torch.equal(batch.packed, before)                              # inputs are not modified
+
+
+def test_parallel_search_builds_the_same_trees_as_searching_each_position_alone():
+    """ParallelMCTS advances one tree per position in lock step (one policy batch per ply over all trees); since
+    the device evaluates every position independently of its batch, each tree must equal the single search's."""
+    from rocalphago_b200.mcts import ParallelMCTS
+    z = np.load(os.path.join(gu.GOLDEN, "mcts_reference.npz"))
+    S = int(z["size"])
+    pol, val = _nets(z, dtype="fp16")
+    setups = [z["fight_setup"].tolist(), z["open_setup"].tolist(), z["fight_setup"].tolist()[:-2]]
+    roots = BatchedGameState(torch.cat([_position(S, s).packed for s in setups]), S)
+    kw = dict(c_puct=2, playout_depth=5, n_playout=96, batch=16)
+    par = ParallelMCTS(pol, val, games=3, **kw)
+    moves = par.get_moves(roots)
+    for g, setup in enumerate(setups):
+        alone = BatchedMCTS(pol, val, **kw)
+        mv = alone.get_move(_position(S, setup))
+        assert mv == moves[g]
+        assert alone.visit_counts(S) == par.searches[g].visit_counts(S)
+        assert np.array_equal(alone._root.Q, par.searches[g]._root.Q)
+    chosen = [par.searches[g].visit_counts(S)[moves[g]] for g in range(3)]
+    par.update_with_moves(moves, size=S)
+    assert [s._root.visits for s in par.searches] == chosen           # every tree re-rooted on its own move

@@ -18,3 +18,15 @@ for batch, n in ((1, 16), (16, 128), (64, 512), (256, 2048), (1024, 8192)):
     s = BatchedMCTS(pol, val, playout_depth=20, n_playout=n, batch=batch)
     t0 = time.perf_counter(); mv = s.get_move(root); torch.cuda.synchronize(); dt = time.perf_counter() - t0
     print("batch %4d: %5d playouts in %6.2f s = %7.1f playouts/s, %6d policy evaluations, move %s" % (batch, n, dt, n / dt, s.evaluations, mv))
+
+from rocalphago_b200.mcts import ParallelMCTS
+roots = BatchedGameState(pos.packed[16:48].clone(), 19)
+for games, batch, n in ((16, 64, 512), (32, 128, 1024)):
+    sub = BatchedGameState(roots.packed[:games].clone(), 19)
+    par = ParallelMCTS(pol, val, games=games, playout_depth=20, n_playout=n, batch=batch)
+    par.get_moves(sub); torch.cuda.synchronize()
+    par = ParallelMCTS(pol, val, games=games, playout_depth=20, n_playout=n, batch=batch)
+    t0 = time.perf_counter(); mv = par.get_moves(sub); torch.cuda.synchronize(); dt = time.perf_counter() - t0
+    ev = sum(s.evaluations for s in par.searches)
+    print("parallel %2d trees x batch %3d: %6d playouts in %6.2f s = %8.1f playouts/s, %7d policy evaluations (%.0f /s)" % (
+        games, batch, games * n, dt, games * n / dt, ev, ev / dt))
