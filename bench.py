@@ -464,6 +464,7 @@ def run_gpu(args):
                          "traffic": ncu_traffic("conv_umma/" + args.dtype, n, n * 361 * 2 * 2 * {"fp16c32": 256, "fp16c64": 256, "fp16x3": 384}.get(args.dtype, 192)),
                          "issued_over_algorithmic": ISSUED[args.dtype],
                          "issued_tflops": achieved * ISSUED[args.dtype],
+                         "frac_issued": achieved * ISSUED[args.dtype] / peaks["tf_sustained"],
                          "note": "CUDA events recorded by the library on the launching stream, sampled %d time(s) inside "
                                  "the timed region while the next batch's feature kernels share the SMs" % samples
                                  + ("; `achieved` counts ALGORITHMIC flops (2*361*192*192*9 per position): this precision issues "
