@@ -749,8 +749,9 @@ static size_t conv_smem_bytes(int N, int stages) {
 // (those record where they stand and trap after ~4 s, rag_conv_stall_report; nothing was ever recorded),
 // which leaves the co-scheduling of the CTA pair itself or tcgen05.alloc.  It needs pair CTAs and
 // CTAs of another kernel on the same SM: with feature kernels that prefer a large L1 (RAG_FEATURE_CARVEOUT=0:
-// an SM drains before it takes a convolution CTA) 10 of 10 processes completed, with the all-shared or the
-// 196 KB split 12 of 36 hung.  Alone on the GPU the pair kernel never stalled.
+// an SM drains before it takes a convolution CTA) 20 of 20 processes completed -- at the throughput of one CTA
+// per tile, because the two kinds of kernels then take turns -- with the all-shared or the 196 KB split 12 of 36
+// hung.  Alone on the GPU the pair kernel never stalled.
 static int g_conv_pair = getenv("RAG_CONV_PAIR") ? atoi(getenv("RAG_CONV_PAIR")) != 0 : 0;
 
 static int pick_stages(int N) {
