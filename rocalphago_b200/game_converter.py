@@ -13,8 +13,9 @@ verbose)` and `run_game_converter(argv)` keep their names, arguments, warnings a
 What differs is how the work is done: the games of a batch are replayed in lock step by
 `rag_do_move` (one warp per game), every position before a move is kept in HBM, and the planes of
 all of them come from one pass of the feature kernels.  The HDF5 file is written by
-`hdf5_lite.Writer` (contiguous, uncompressed datasets -- h5py reads them like the reference's
-chunked LZF ones).
+`hdf5_lite.Writer` (contiguous, uncompressed datasets in the layout libhdf5 1.8 gives a new file; read
+back here by `hdf5_lite.File`, which also reads the reference's chunked LZF files -- no libhdf5 / h5py is
+on this image to cross-check the writer with).
 """
 import os
 import warnings
